@@ -1,0 +1,175 @@
+/* include/sdr_b200.h — C-ABI of the B200-native IQ hot path.
+ *
+ * This is the drop-in boundary for the reference's per-reading DSP path.  The
+ * reference (alexandreGellibert/SDR-for-Android-lib) has no FFI table for this
+ * path: its JNI bridge owns three C++ globals and calls them directly
+ *     FFTProcessor fftProcessor; SSBProcessor ssbProcessor;        src/sdr-bridge-java-soapy.cpp:101-108
+ *     fftProcessor.process(buf,len) / ssbProcessor.enqueueData()    src/sdr-bridge-java-soapy.cpp:441-444
+ * so the entry points below are what a cgo/JNI/ctypes binding of those objects
+ * would bind, batch-first: S independent streams x B readings per call.
+ * Header-compatible C++ front ends (FFTProcessor / SSBProcessor / processSSB_opt,
+ * batch of one) live in sdr-for-android-lib_b200/host/ and call only this ABI.
+ *
+ * Conventions: plain pointers and sizes, no C++/torch types.  Every function
+ * returns SDRB_OK (0) or a negative sdrb_status; sdrb_last_error() gives text.
+ * The reference's DSP has no error channel at all (all void), so
+ * status codes are additive.  There is NO CPU fallback: without a CUDA device or
+ * with an unsupported shape the call fails loudly.
+ *
+ * Paths cited as file:line are relative to the reference repository root. */
+#ifndef SDR_B200_H
+#define SDR_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SDRB_ABI_VERSION 1
+
+typedef enum {
+    SDRB_OK = 0,
+    SDRB_ERR_ARG = -1,        /* bad argument / shape */
+    SDRB_ERR_CUDA = -2,       /* CUDA runtime error (text in sdrb_last_error) */
+    SDRB_ERR_UNSUPPORTED = -3,/* valid in the reference, not built here (e.g. non power-of-two N) */
+    SDRB_ERR_STATE = -4,      /* call order (not configured, nothing processed, ...) */
+    SDRB_ERR_NOMEM = -5
+} sdrb_status;
+
+/* Wire formats of one complex sample (interleaved I,Q).
+ *  CU8 : RTL-SDR offset binary; f = (b - 127.4f) * (1/128.f)     src/ssb/ssb_demod_opt.cpp:33-44
+ *  CS16: LimeSDR-style; f = s * 2^-15  (LimeSuite is a missing submodule: convention, parity unpinned)
+ *  CF32: what SoapySDR hands the reference today ("CF32")        src/sdr-bridge-java-soapy.cpp:262-263 */
+typedef enum { SDRB_CU8 = 0, SDRB_CS16 = 1, SDRB_CF32 = 2 } sdrb_format;
+
+#define SDRB_STAGE_FFT 1u   /* FFTProcessor::process       src/dsp/fft_process.cpp:42-105 */
+#define SDRB_STAGE_SSB 2u   /* processSSB_opt              src/ssb/ssb_demod_opt.cpp:221-296 */
+
+/* Per-context configuration, shared by all streams of the context.
+ * First block = FftProcessorConfig (src/dsp/fft_process.h:20-26) + the BridgeConfig
+ * fields the path reads (src/bridge-config.h:41-49).  Per-stream centre
+ * frequencies can be changed afterwards with sdrb_set_center_frequency. */
+typedef struct {
+    uint32_t centerFrequency;     /* Hz */
+    uint32_t sampleRate;          /* Hz */
+    int32_t  samplesPerReading;   /* N = block length = FFT length */
+    int32_t  freqFocusRangeKhz;
+    int32_t  soundMode;           /* 0,1,2: src/ssb/ssb_demod_opt.cpp:230-255 */
+    int32_t  inputFormat;         /* sdrb_format */
+    int32_t  upperSideband;       /* the reference always passes true: src/ssb/ssb_processor.cpp:103 */
+    /* Extension stages the reference does not have; 0 = identity = reference behaviour. */
+    int32_t  fftWindow;           /* 0 rectangular (reference), 1 Hann */
+    int32_t  fftRemoveDc;         /* 0 off (reference), 1 subtract the block mean before the FFT */
+    int32_t  ssbTrueSideband;     /* 0 reference quirk (USB=2y, LSB=0), 1 phasing-method USB/LSB */
+    int32_t  ssbChannels;         /* 0/1 = one channel at the tuned centre (reference); >1 = NCO bank */
+    float    ssbChannelOffsetHz;  /* NCO offset of channel 0 from centre */
+    float    ssbChannelSpacingHz; /* raster between channels */
+    int32_t  reserved[3];
+} sdrb_config;
+
+/* One record per (stream, reading): everything soapyCallback reads back through the
+ * getters (src/dsp/fft_process.h:38-55; use at src/sdr-bridge-java-soapy.cpp:446-455)
+ * plus the frame-local internals the parity tests compare. */
+typedef struct {
+    float   meanSnrDb;              /* (F)V "signal strength" */
+    float   meanSnrSigma;
+    float   peakAboveNoiseMeanDb;   /* (F)V */
+    float   maxBinSnrDb;            /* (FF)V */
+    float   maxBinSnrSigma;
+    float   best1kHzSnrDb;          /* (FF)V */
+    float   best1kHzSnrSigma;
+    float   best1kHzCenterFreqHz;
+    float   perBinMean;             /* noise level (F)V */
+    float   trackingFrequencyHz;    /* float state behind getTrackingFrequency() */
+    int64_t trackingFrequency;      /* std::round of the above, (J)V */
+    int32_t detectionFlag;          /* 0 or 3, (I)V */
+    /* frame-local internals (src/dsp/fft_process.cpp:142-155,344-348) */
+    float   absPeakDb;
+    float   signalPowerDb;
+    float   peakFrequencyHz;        /* candidate computed for this frame's peak bin */
+    int32_t peakBin;                /* focusLo + peakBinInFocus in the shifted spectrum; -1 if skipped */
+    int32_t valid;                  /* nRef >= 2 */
+    int32_t nRef;
+    int32_t reserved;
+} sdrb_frame_result;
+
+typedef struct sdrb_ctx sdrb_ctx;
+
+/* ---- lifecycle ---------------------------------------------------------- */
+int  sdrb_abi_version(void);
+/* Creates a context on CUDA device `device` (one context per GPU; one process per GPU when sharded). */
+int  sdrb_create(int device, sdrb_ctx** out);
+int  sdrb_destroy(sdrb_ctx* ctx);
+/* Text of the last error on this context (ctx may be NULL for create-time errors). */
+const char* sdrb_last_error(const sdrb_ctx* ctx);
+/* Run all work of this context on a caller-owned cudaStream_t (NULL = the context's own stream). */
+int  sdrb_set_cuda_stream(sdrb_ctx* ctx, void* cuda_stream);
+
+/* ---- configuration (FFTProcessor::configure, BridgeConfig) -------------- */
+/* src/dsp/fft_process.cpp:20-39, src/sdr-bridge-java-soapy.cpp:1123-1128.
+ * Allocates device buffers for n_streams x max_blocks readings and resets all per-stream state. */
+int  sdrb_configure(sdrb_ctx* ctx, const sdrb_config* cfg, int n_streams, int max_blocks);
+/* setFrequency: new centre for one stream (or all with stream = -1) and raise the
+ * isCenterFrequencyChanged side channel (src/sdr-bridge-java-soapy.cpp:897-905, src/sdr-bridge-internal.h:9). */
+int  sdrb_set_center_frequency(sdrb_ctx* ctx, int stream, uint32_t center_hz);
+/* setFrequencyFocusRange (src/sdr-bridge-java-soapy.cpp:1031-1036) */
+int  sdrb_set_focus_range(sdrb_ctx* ctx, int focus_khz);
+/* BridgeConfig::setSoundMode (src/bridge-config.h:61); only gains/AGC/boost follow the new mode,
+ * the RF low-pass keeps the first mode like the reference's static rfFilter (src/ssb/ssb_demod_opt.cpp:261-263). */
+int  sdrb_set_sound_mode(sdrb_ctx* ctx, int mode);
+/* Number of int16 PCM samples produced per reading: floor((N-255)/decim)+1 (src/ssb/ssb_demod_opt.cpp:137). */
+int  sdrb_pcm_per_block(const sdrb_ctx* ctx);
+
+/* ---- the hot path -------------------------------------------------------- */
+/* One batched submit = soapyCallback for every (stream, reading)
+ * (src/sdr-bridge-java-soapy.cpp:424-493): iq is [n_streams][n_blocks][N] samples of
+ * cfg.inputFormat, in device memory (on_device=1) or host memory (on_device=0; copied
+ * inside the call).  Borrowed until the call returns (host) / until sdrb_sync (device).
+ * stages: SDRB_STAGE_FFT | SDRB_STAGE_SSB.  Asynchronous on the context's stream. */
+int  sdrb_process(sdrb_ctx* ctx, const void* iq, int on_device, int n_blocks, unsigned stages);
+int  sdrb_sync(sdrb_ctx* ctx);
+
+/* Results of the last sdrb_process, [n_streams][n_blocks] records (synchronises). */
+int  sdrb_get_results(sdrb_ctx* ctx, sdrb_frame_result* host_out, size_t capacity_records);
+/* Device-resident records (same layout), valid until the next sdrb_process. */
+int  sdrb_results_device(sdrb_ctx* ctx, const sdrb_frame_result** dev_ptr);
+/* Linear, fft-shifted, un-normalised power spectrum = the ([F)V payload
+ * (src/dsp/fft_process.cpp:83-97).  Device layout [n_streams][n_blocks][N]. */
+int  sdrb_power_device(sdrb_ctx* ctx, const float** dev_ptr);
+int  sdrb_get_power(sdrb_ctx* ctx, int stream, int block, float* host_out);
+/* int16 PCM = the ([S)V payload; layout [n_streams][n_blocks][pcm_per_block]
+ * (x ssbChannels when the NCO bank is on: [stream][channel][block][m]). */
+int  sdrb_pcm_device(sdrb_ctx* ctx, const int16_t** dev_ptr);
+int  sdrb_get_pcm(sdrb_ctx* ctx, int16_t* host_out, size_t capacity_samples);
+
+/* ---- per-stream state (checkpoint / resume) ----------------------------- */
+/* Opaque blob: three biquad states, tracking memory, detection ring, frame counter. */
+size_t sdrb_state_bytes(const sdrb_ctx* ctx);
+int  sdrb_save_state(sdrb_ctx* ctx, void* host_blob, size_t bytes);
+int  sdrb_load_state(sdrb_ctx* ctx, const void* host_blob, size_t bytes);
+int  sdrb_reset_state(sdrb_ctx* ctx);
+
+/* ---- deterministic synthetic IQ source (replaces Soapy/USB capture on the box) ---- */
+/* Integer-only generator, bit-identical on host and device.  Stream s (global id) uses
+ * seed 0x5D120000+s: keyed CW tone inside the default focus band, a static tone in a
+ * reference window, approximately Gaussian noise.  Fills [n_streams][n_samples]. */
+int  sdrb_synth_host(int format, uint32_t sample_rate, int first_stream, int n_streams,
+                     int64_t first_sample, int64_t n_samples, void* host_out);
+int  sdrb_synth_device(sdrb_ctx* ctx, int format, uint32_t sample_rate, int first_stream, int n_streams,
+                       int64_t first_sample, int64_t n_samples, void* dev_out);
+size_t sdrb_format_bytes(int format); /* bytes per complex sample */
+
+/* ---- introspection -------------------------------------------------------- */
+/* Kernels launched by this context since creation (bench.py's gpu_launches). */
+uint64_t sdrb_launch_count(const sdrb_ctx* ctx);
+/* Device time in ms of the dominant (FFT) kernel launches of the last sdrb_process, measured
+ * with CUDA events on the launching stream; returns count of launches timed. */
+int  sdrb_last_fft_kernel_ms(sdrb_ctx* ctx, float* ms_total);
+int  sdrb_enable_kernel_timing(sdrb_ctx* ctx, int on);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SDR_B200_H */

@@ -1,0 +1,35 @@
+// fft_tables.h — host-side twiddle table generation (double precision, rounded once).
+#pragma once
+#include <cmath>
+#include <vector>
+
+#include "fft16k.cuh"
+
+namespace sdrb {
+
+inline cpx twiddle(long long num, long long den) {
+    // W_den^num = exp(-2 pi i num / den), reduced first so the angle stays small and exact
+    num %= den;
+    const double a = -2.0 * 3.14159265358979323846264338327950288 * (double)num / (double)den;
+    return mk((float)std::cos(a), (float)std::sin(a));
+}
+
+// Layout: TA | TB | T2 | T3  (F16K_TW_ELEMS entries), see fft16k.cuh
+inline std::vector<cpx> make_f16k_tables() {
+    std::vector<cpx> t(F16K_TW_ELEMS);
+    cpx* TA = t.data();
+    cpx* TB = TA + F16K_TA;
+    cpx* T2 = TB + F16K_TB;
+    cpx* T3 = T2 + F16K_T2;
+    for (int w = 0; w < 32; w++)
+        for (int k = 0; k < 16; k++) TA[w * 16 + k] = twiddle(32LL * w * k, F16K_N);
+    for (int k = 0; k < 16; k++)
+        for (int l = 0; l < 32; l++) TB[k * 32 + l] = twiddle((long long)l * k, F16K_N);
+    for (int k = 0; k < 16; k++)
+        for (int s = 0; s < 64; s++) T2[k * 64 + s] = twiddle((long long)s * k, 1024);
+    for (int k = 0; k < 16; k++)
+        for (int d = 0; d < 4; d++) T3[k * 4 + d] = twiddle((long long)d * k, 64);
+    return t;
+}
+
+}  // namespace sdrb

@@ -1,0 +1,106 @@
+// internal.h — structures shared between the C-ABI (api.cu) and the kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/sdr_b200.h"
+#include "fft_core.cuh"
+
+namespace sdrb {
+
+// ---------------------------------------------------------------- estimator
+// Bin geometry of evaluateSignalStrength (src/dsp/fft_process.cpp:125-139,160,191-216),
+// evaluated ONCE on the host in the reference's float expressions (no FMA contraction on
+// the x86-64 baseline) so that every bin bound is bit-identical to the reference's.
+struct EstGeometry {
+    int n;                 // samplesPerReading
+    int focusLo, focusHi, focusLen;   // focusLen <= 0: the reference returns early (:139)
+    int winBins1k;
+    int nWin;              // reference windows in push order (+k then -k), <= 10
+    int winLo[10], winHi[10];
+    int nBottom;           // max(1, int(nWin*0.4f))
+    float freqPerBin;
+    float nyquist;
+    float sampleRateF;
+};
+
+// Frame-local result of the estimator kernel, before the per-stream sequential part.
+struct FrameLocal {
+    float absPeakDb, signalPowerDb;
+    float meanSnrDb, meanSnrSigma;
+    float perBinMean, peakAboveNoiseMeanDb;
+    float maxBinSnrDb, maxBinSnrSigma;
+    float best1kHzSnrDb, best1kHzSnrSigma;
+    int best1kStart;       // bestStart bin, -1 when focusBest1kLinear <= 0 (:303,324-326)
+    int peakBin;           // focusLo + peakBinInFocus
+    int valid;             // nRef >= 2
+    int pad;
+};
+
+// Carried per-stream state of FFTProcessor (src/dsp/fft_process.h:62-109) + hold-over outputs.
+struct FftStreamState {
+    uint32_t centerFrequency;
+    int32_t centerChanged;           // sdr_bridge_internal::isCenterFrequencyChanged
+    float trackingFrequency;
+    float maxPeakDb, maxPeakHz;      // maxPeakAndFrequency
+    int64_t timeOfLastMaxPeak_ns, timeOfLastMaxPeakUpdate_ns;
+    int64_t frameCounter;            // frames processed so far (frame clock)
+    int32_t peakConfirmed;
+    int32_t flagRing[3];
+    int32_t flagIndex;
+    // outputs that persist when a frame does not overwrite them
+    float meanSnrDb, meanSnrSigma, peakAboveNoiseMeanDb, maxBinSnrDb, maxBinSnrSigma;
+    float best1kHzSnrDb, best1kHzSnrSigma, best1kHzCenterFreqHz, perBinMean;
+    int32_t detectionFlag;
+    int32_t pad;
+};
+
+// ---------------------------------------------------------------- SSB
+// Per-stream carried filter state (the reference's function statics,
+// src/ssb/ssb_demod_opt.cpp:261,277): previous two OUTPUTS of each section.
+struct SsbStreamState {
+    float rf_z1, rf_z2;
+    float hp_z1, hp_z2;
+    float bp_z1, bp_z2;
+    float pad0, pad1;
+};
+
+struct BiquadCoef {
+    float a0, a1, a2, b1, b2;
+};
+
+constexpr int SSB_MAX_TAPS = 255;
+
+struct SsbParams {
+    int n;                 // samples per block
+    int decim;             // max(1, int(fs/48000.f))
+    int nTaps;             // 255 (or n|1 when n < 255)
+    int m;                 // PCM samples per block
+    int upper;             // sideband flag passed to demodSSB
+    float dcAlpha;         // 0.9995
+    float agcTarget, agcFast, agcSlow;
+    float gain, transientCoeff;
+    BiquadCoef rf, hp, bp;
+};
+
+// ---------------------------------------------------------------- launchers
+// fft16k.cu
+cudaError_t launch_fft16k(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
+                          int sm_count, cudaStream_t st);
+cudaError_t fft16k_prepare();  // sets max dynamic shared memory attributes once per process
+// fft_any.cu : generic power-of-two path (N != 16384)
+cudaError_t launch_fft_generic(int fmt, const void* iq, float* power, cpx* scratch_a, cpx* scratch_b,
+                               const cpx* twiddles, int n, int n_frames, cudaStream_t st);
+// estimator.cu
+cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, FrameLocal* d_local,
+                             int n, int n_frames, cudaStream_t st);
+cudaError_t launch_tracker(const FrameLocal* d_local, const EstGeometry* d_geo, FftStreamState* d_state,
+                           sdrb_frame_result* d_results, int n_streams, int n_blocks, cudaStream_t st);
+// synth.cu
+cudaError_t launch_synth(int fmt, uint32_t fs, int first_stream, int n_streams, int64_t first_sample,
+                         int64_t n_samples, void* d_out, const int16_t* d_sine, cudaStream_t st);
+void synth_host(int fmt, uint32_t fs, int first_stream, int n_streams, int64_t first_sample,
+                int64_t n_samples, void* out);
+const int16_t* synth_sine_table();  // 4096-entry Q15 sine, host memory
+
+}  // namespace sdrb

@@ -1,0 +1,118 @@
+// tests/cpp/fft_sim.cpp — CPU execution of the FFT kernels' phase functions, thread by
+// thread, against a double-precision DFT.  Validates index algebra, twiddle tables and the
+// shared-memory layout (including a bank-conflict audit) without a GPU.
+// Build: g++ -O2 -std=c++17 -I<csrc> fft_sim.cpp -o fft_sim ; exit code 0 = pass.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include "fft_tables.h"
+
+using namespace sdrb;
+
+static void dft_ref(const std::vector<double>& re, const std::vector<double>& im, std::vector<double>& Xr,
+                    std::vector<double>& Xi) {
+    int n = (int)re.size(), bits = 0;
+    while ((1 << bits) < n) bits++;
+    Xr.assign(n, 0); Xi.assign(n, 0);
+    for (int i = 0; i < n; i++) {
+        unsigned r = 0;
+        for (int b = 0; b < bits; b++) if (i & (1 << b)) r |= 1u << (bits - 1 - b);
+        Xr[r] = re[i]; Xi[r] = im[i];
+    }
+    for (int len = 2; len <= n; len <<= 1) {
+        int half = len / 2;
+        for (int base = 0; base < n; base += len)
+            for (int j = 0; j < half; j++) {
+                double a = -2.0 * M_PI * j / len, c = cos(a), s = sin(a);
+                double xr = Xr[base + j + half], xi = Xi[base + j + half];
+                double tr = xr * c - xi * s, ti = xr * s + xi * c;
+                Xr[base + j + half] = Xr[base + j] - tr; Xi[base + j + half] = Xi[base + j] - ti;
+                Xr[base + j] += tr; Xi[base + j] += ti;
+            }
+    }
+}
+
+int main() {
+    const int N = F16K_N;
+    std::vector<cpx> tw = make_f16k_tables();
+    const cpx* TA = tw.data();
+    const cpx* TB = TA + F16K_TA;
+    const cpx* T2 = TB + F16K_TB;
+    const cpx* T3 = T2 + F16K_T2;
+
+    // u8 input: tone + pseudo noise
+    std::vector<uint16_t> raw(N);
+    std::vector<double> re(N), im(N);
+    unsigned lcg = 12345;
+    for (int i = 0; i < N; i++) {
+        lcg = lcg * 1664525u + 1013904223u;
+        int nI = (int)((lcg >> 24) & 7) - 3, nQ = (int)((lcg >> 16) & 7) - 3;
+        int I = 127 + (int)lrint(38 * cos(2 * M_PI * 1000.25 * i / N)) + nI;
+        int Q = 127 + (int)lrint(38 * sin(2 * M_PI * 1000.25 * i / N)) + nQ;
+        raw[i] = (uint16_t)(I | (Q << 8));
+        re[i] = ((double)(float)(I - 127.4f)) / 128.0;
+        im[i] = ((double)(float)(Q - 127.4f)) / 128.0;
+    }
+    std::vector<double> Xr, Xi;
+    dft_ref(re, im, Xr, Xi);
+
+    std::vector<cpx> E(F16K_E_ELEMS, mk(0, 0));
+    std::vector<float> out(N, -1.0f);
+    for (int t = 0; t < F16K_THREADS; t++) f16k_phase1<FMT_CU8>(t, raw.data(), E.data(), TA, TB);
+    for (int t = 0; t < F16K_THREADS; t++) f16k_phase2(t, E.data(), T2);
+    for (int t = 0; t < F16K_THREADS; t++) f16k_phase3(t, E.data(), T3);
+    for (int t = 0; t < F16K_THREADS; t++) f16k_phase4(t, E.data(), out.data(), Ingest<FMT_CU8>::kPowerScale);
+
+    double total = 0, maxrel = 0, maxabs = 0;
+    for (int k = 0; k < N; k++) total += Xr[k] * Xr[k] + Xi[k] * Xi[k];
+    int bad = 0;
+    for (int k = 0; k < N; k++) {
+        double p = Xr[k] * Xr[k] + Xi[k] * Xi[k];
+        double g = out[(k + N / 2) % N];
+        double err = fabs(g - p);
+        // float32 FFT error floor: amplitude error ~ eps * sqrt(total energy)
+        double tol = 1e-5 * p + 2.0 * sqrt(p) * 3e-7 * sqrt(total) + 1e-9 * total / N;
+        if (err > tol) { if (bad < 10) printf("bin %d ref %.6g got %.6g\n", k, p, g); bad++; }
+        if (p > 1e-3 * total / N) maxrel = fmax(maxrel, err / p);
+        maxabs = fmax(maxabs, err);
+    }
+    printf("fft16k sim: bad=%d maxrel=%.3g maxabs=%.3g total=%.4g\n", bad, maxrel, maxabs, total);
+
+    // bank-conflict audit of the slot function: every warp access must touch 16 distinct
+    // 8-byte banks per half-warp.
+    int conflicts = 0;
+    auto audit = [&](auto addr_of /* (t, j) -> element index */, const char* name) {
+        for (int w = 0; w < 32; w++)
+            for (int j = 0; j < 16; j++)
+                for (int h = 0; h < 2; h++) {
+                    int seen[16] = {0};
+                    for (int l = 0; l < 16; l++) {
+                        int t = w * 32 + h * 16 + l;
+                        int bank = addr_of(t, j) & 15;
+                        if (seen[bank]++) { conflicts++; if (conflicts < 5) printf("conflict %s w%d j%d\n", name, w, j); }
+                    }
+                }
+    };
+    audit([](int t, int k) { return f16k_slot(k, t >> 6, t & 63); }, "p1 store");
+    audit([](int t, int b) { return f16k_slot(t >> 6, b, t & 63); }, "p2 ld/st");
+    audit([](int t, int c) { return f16k_slot(t >> 6, (t >> 2) & 15, 4 * c + (t & 3)); }, "p3 ld/st");
+    // phase 4: LDS.128 pairs; quarter-warp (8 lanes) must cover 8 distinct 16-byte banks
+    for (int w = 0; w < 32; w++)
+        for (int m = 0; m < 4; m++)
+            for (int q = 0; q < 4; q++)
+                for (int pair = 0; pair < 2; pair++) {
+                    int seen[8] = {0};
+                    for (int l = 0; l < 8; l++) {
+                        int t = w * 32 + q * 8 + l;
+                        int ka = t & 15, kb = (t >> 4) & 15, kc = (t >> 8) + 4 * m;
+                        int e = f16k_slot(ka, kb, 4 * kc) + 2 * pair;
+                        if (e & 1) { conflicts++; printf("misaligned p4\n"); }
+                        int bank = (e >> 1) & 7;
+                        if (seen[bank]++) { conflicts++; if (conflicts < 5) printf("conflict p4 w%d m%d\n", w, m); }
+                    }
+                }
+    printf("bank conflicts: %d\n", conflicts);
+    return (bad || conflicts) ? 1 : 0;
+}
