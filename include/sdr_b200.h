@@ -95,6 +95,20 @@ typedef struct {
     int32_t reserved;
 } sdrb_frame_result;
 
+/* What the configuration resolves to: bin geometry of evaluateSignalStrength
+ * (src/dsp/fft_process.cpp:125-139,160,191-216,232) and the SSB chain's parameters
+ * (src/ssb/ssb_demod_opt.cpp:60-73,122-134,148-175,230-255,273).  Pure host computation. */
+typedef struct {
+    int32_t n, focusLo, focusHi, focusLen, winBins1k, nWin, nBottom;
+    int32_t winLo[10], winHi[10];
+    float   freqPerBin, nyquist;
+    int32_t decim, nTaps, pcmPerBlock;
+    int32_t fftPath;               /* 0 generic multi-pass, 1 single-CTA 16K kernel, 2 four-step */
+    float   rf[5], hp[5], bp[5];   /* a0,a1,a2,b1,b2 of struct IIR2 / Biquad (src/ssb/ssb_demod_opt.h:14-26) */
+    float   agcTarget, agcFast, agcSlow, gain, transientCoeff, dcAlpha;
+    float   firTaps[255];
+} sdrb_plan;
+
 typedef struct sdrb_ctx sdrb_ctx;
 
 /* ---- lifecycle ---------------------------------------------------------- */
@@ -121,6 +135,9 @@ int  sdrb_set_focus_range(sdrb_ctx* ctx, int focus_khz);
 int  sdrb_set_sound_mode(sdrb_ctx* ctx, int mode);
 /* Number of int16 PCM samples produced per reading: floor((N-255)/decim)+1 (src/ssb/ssb_demod_opt.cpp:137). */
 int  sdrb_pcm_per_block(const sdrb_ctx* ctx);
+
+/* Resolve a configuration without touching a GPU (used by host-side tests and tools). */
+int  sdrb_plan_config(const sdrb_config* cfg, sdrb_plan* out);
 
 /* ---- the hot path -------------------------------------------------------- */
 /* One batched submit = soapyCallback for every (stream, reading)

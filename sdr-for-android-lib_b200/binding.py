@@ -1,0 +1,248 @@
+"""ctypes binding of include/sdr_b200.h (the drop-in C-ABI of the reference's DSP objects,
+src/sdr-bridge-java-soapy.cpp:101-108,441-455).  One-to-one with the header; no arithmetic here."""
+import ctypes as C
+import os
+
+import numpy as np
+
+CU8, CS16, CF32 = 0, 1, 2
+STAGE_FFT, STAGE_SSB = 1, 2
+_HERE = os.path.dirname(os.path.abspath(__file__))
+lib_path = os.path.join(_HERE, "libsdr_b200.so")
+
+
+class SdrbError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__(f"sdrb error {code}: {text}")
+        self.code = code
+
+
+class Config(C.Structure):
+    _fields_ = [("centerFrequency", C.c_uint32), ("sampleRate", C.c_uint32),
+                ("samplesPerReading", C.c_int32), ("freqFocusRangeKhz", C.c_int32),
+                ("soundMode", C.c_int32), ("inputFormat", C.c_int32), ("upperSideband", C.c_int32),
+                ("fftWindow", C.c_int32), ("fftRemoveDc", C.c_int32), ("ssbTrueSideband", C.c_int32),
+                ("ssbChannels", C.c_int32), ("ssbChannelOffsetHz", C.c_float),
+                ("ssbChannelSpacingHz", C.c_float), ("reserved", C.c_int32 * 3)]
+
+    def __init__(self, centerFrequency=430_000_000, sampleRate=2_000_000, samplesPerReading=16384,
+                 freqFocusRangeKhz=5, soundMode=1, inputFormat=CU8, upperSideband=1, **kw):
+        super().__init__(centerFrequency=centerFrequency, sampleRate=sampleRate,
+                         samplesPerReading=samplesPerReading, freqFocusRangeKhz=freqFocusRangeKhz,
+                         soundMode=soundMode, inputFormat=inputFormat, upperSideband=upperSideband, **kw)
+
+
+class FrameResult(C.Structure):
+    _fields_ = [("meanSnrDb", C.c_float), ("meanSnrSigma", C.c_float), ("peakAboveNoiseMeanDb", C.c_float),
+                ("maxBinSnrDb", C.c_float), ("maxBinSnrSigma", C.c_float), ("best1kHzSnrDb", C.c_float),
+                ("best1kHzSnrSigma", C.c_float), ("best1kHzCenterFreqHz", C.c_float),
+                ("perBinMean", C.c_float), ("trackingFrequencyHz", C.c_float),
+                ("trackingFrequency", C.c_int64), ("detectionFlag", C.c_int32),
+                ("absPeakDb", C.c_float), ("signalPowerDb", C.c_float), ("peakFrequencyHz", C.c_float),
+                ("peakBin", C.c_int32), ("valid", C.c_int32), ("nRef", C.c_int32), ("reserved", C.c_int32)]
+
+
+RESULT_DTYPE = np.dtype(FrameResult)
+
+
+class Plan(C.Structure):
+    _fields_ = [("n", C.c_int32), ("focusLo", C.c_int32), ("focusHi", C.c_int32), ("focusLen", C.c_int32),
+                ("winBins1k", C.c_int32), ("nWin", C.c_int32), ("nBottom", C.c_int32),
+                ("winLo", C.c_int32 * 10), ("winHi", C.c_int32 * 10),
+                ("freqPerBin", C.c_float), ("nyquist", C.c_float),
+                ("decim", C.c_int32), ("nTaps", C.c_int32), ("pcmPerBlock", C.c_int32), ("fftPath", C.c_int32),
+                ("rf", C.c_float * 5), ("hp", C.c_float * 5), ("bp", C.c_float * 5),
+                ("agcTarget", C.c_float), ("agcFast", C.c_float), ("agcSlow", C.c_float), ("gain", C.c_float),
+                ("transientCoeff", C.c_float), ("dcAlpha", C.c_float), ("firTaps", C.c_float * 255)]
+
+
+EXPORTS = {
+    "sdrb_abi_version": (C.c_int, []),
+    "sdrb_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
+    "sdrb_destroy": (C.c_int, [C.c_void_p]),
+    "sdrb_last_error": (C.c_char_p, [C.c_void_p]),
+    "sdrb_set_cuda_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "sdrb_configure": (C.c_int, [C.c_void_p, C.POINTER(Config), C.c_int, C.c_int]),
+    "sdrb_set_center_frequency": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32]),
+    "sdrb_set_focus_range": (C.c_int, [C.c_void_p, C.c_int]),
+    "sdrb_set_sound_mode": (C.c_int, [C.c_void_p, C.c_int]),
+    "sdrb_pcm_per_block": (C.c_int, [C.c_void_p]),
+    "sdrb_plan_config": (C.c_int, [C.POINTER(Config), C.POINTER(Plan)]),
+    "sdrb_process": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint]),
+    "sdrb_sync": (C.c_int, [C.c_void_p]),
+    "sdrb_get_results": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    "sdrb_results_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "sdrb_power_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "sdrb_get_power": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "sdrb_pcm_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "sdrb_get_pcm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    "sdrb_state_bytes": (C.c_size_t, [C.c_void_p]),
+    "sdrb_save_state": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    "sdrb_load_state": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    "sdrb_reset_state": (C.c_int, [C.c_void_p]),
+    "sdrb_synth_host": (C.c_int, [C.c_int, C.c_uint32, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p]),
+    "sdrb_synth_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_int, C.c_int, C.c_int64, C.c_int64,
+                                    C.c_void_p]),
+    "sdrb_format_bytes": (C.c_size_t, [C.c_int]),
+    "sdrb_launch_count": (C.c_uint64, [C.c_void_p]),
+    "sdrb_last_fft_kernel_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "sdrb_enable_kernel_timing": (C.c_int, [C.c_void_p, C.c_int]),
+}
+
+if not os.path.exists(lib_path):
+    raise ImportError(f"{lib_path} is missing: build it with `make -C sdr-for-android-lib_b200/csrc` "
+                      "(or __graft_entry__.build()); there is no CPU fallback")
+lib = C.CDLL(lib_path)
+for _name, (_res, _args) in EXPORTS.items():
+    _f = getattr(lib, _name)
+    _f.restype, _f.argtypes = _res, _args
+
+
+def format_bytes(fmt):
+    return int(lib.sdrb_format_bytes(fmt))
+
+
+def format_dtype(fmt):
+    """numpy dtype and per-sample width of a wire format: [.., n, 2] of u8 / i16 / f32."""
+    return {CU8: np.uint8, CS16: np.int16, CF32: np.float32}[fmt]
+
+
+def _check(rc, ctx=None):
+    if rc < 0:
+        raise SdrbError(rc, (lib.sdrb_last_error(ctx) or b"").decode())
+    return rc
+
+
+def plan_config(cfg):
+    p = Plan()
+    _check(lib.sdrb_plan_config(C.byref(cfg), C.byref(p)))
+    return p
+
+
+def synth_host(fmt, sample_rate, first_stream, n_streams, first_sample, n_samples):
+    """Deterministic synthetic IQ, [n_streams, n_samples, 2] in the wire dtype (host generator)."""
+    out = np.empty((n_streams, n_samples, 2), dtype=format_dtype(fmt))
+    _check(lib.sdrb_synth_host(fmt, sample_rate, first_stream, n_streams, first_sample, n_samples,
+                               out.ctypes.data_as(C.c_void_p)))
+    return out
+
+
+def _ptr(x):
+    """Device or host address of a numpy array / torch tensor / int."""
+    if isinstance(x, (int, np.integer)):
+        return int(x), None
+    if isinstance(x, np.ndarray):
+        return x.ctypes.data, False
+    return x.data_ptr(), bool(x.is_cuda)
+
+
+class Context:
+    """One GPU context = the reference's FFTProcessor + SSBProcessor globals for S streams."""
+
+    def __init__(self, device=0):
+        h = C.c_void_p()
+        _check(lib.sdrb_create(device, C.byref(h)))
+        self._h = h
+        self.cfg = None
+        self.n_streams = 0
+        self.last_blocks = 0
+
+    def close(self):
+        if self._h:
+            lib.sdrb_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def configure(self, cfg, n_streams, max_blocks):
+        _check(lib.sdrb_configure(self._h, C.byref(cfg), n_streams, max_blocks), self._h)
+        self.cfg, self.n_streams, self.max_blocks = cfg, n_streams, max_blocks
+
+    def set_cuda_stream(self, stream_ptr):
+        _check(lib.sdrb_set_cuda_stream(self._h, C.c_void_p(stream_ptr)), self._h)
+
+    def set_center_frequency(self, stream, hz):
+        _check(lib.sdrb_set_center_frequency(self._h, stream, hz), self._h)
+
+    def set_focus_range(self, khz):
+        _check(lib.sdrb_set_focus_range(self._h, khz), self._h)
+
+    def set_sound_mode(self, mode):
+        _check(lib.sdrb_set_sound_mode(self._h, mode), self._h)
+
+    @property
+    def pcm_per_block(self):
+        return _check(lib.sdrb_pcm_per_block(self._h), self._h)
+
+    def process(self, iq, n_blocks, stages=STAGE_FFT | STAGE_SSB, on_device=None):
+        addr, is_cuda = _ptr(iq)
+        if on_device is None:
+            on_device = bool(is_cuda)
+        _check(lib.sdrb_process(self._h, C.c_void_p(addr), 1 if on_device else 0, n_blocks, stages), self._h)
+        self.last_blocks = n_blocks
+
+    def sync(self):
+        _check(lib.sdrb_sync(self._h), self._h)
+
+    def results(self):
+        out = np.zeros((self.n_streams, self.last_blocks), dtype=RESULT_DTYPE)
+        _check(lib.sdrb_get_results(self._h, out.ctypes.data_as(C.c_void_p), out.size), self._h)
+        return out
+
+    def power(self, stream, block):
+        out = np.empty(self.cfg.samplesPerReading, dtype=np.float32)
+        _check(lib.sdrb_get_power(self._h, stream, block, out.ctypes.data_as(C.c_void_p)), self._h)
+        return out
+
+    def power_device_ptr(self):
+        p = C.c_void_p()
+        _check(lib.sdrb_power_device(self._h, C.byref(p)), self._h)
+        return p.value
+
+    def results_device_ptr(self):
+        p = C.c_void_p()
+        _check(lib.sdrb_results_device(self._h, C.byref(p)), self._h)
+        return p.value
+
+    def pcm_device_ptr(self):
+        p = C.c_void_p()
+        _check(lib.sdrb_pcm_device(self._h, C.byref(p)), self._h)
+        return p.value
+
+    def pcm(self):
+        m = self.pcm_per_block
+        out = np.zeros((self.n_streams, self.last_blocks, m), dtype=np.int16)
+        _check(lib.sdrb_get_pcm(self._h, out.ctypes.data_as(C.c_void_p), out.size), self._h)
+        return out
+
+    def save_state(self):
+        n = lib.sdrb_state_bytes(self._h)
+        buf = np.zeros(n, dtype=np.uint8)
+        _check(lib.sdrb_save_state(self._h, buf.ctypes.data_as(C.c_void_p), n), self._h)
+        return buf
+
+    def load_state(self, buf):
+        _check(lib.sdrb_load_state(self._h, buf.ctypes.data_as(C.c_void_p), buf.size), self._h)
+
+    def reset_state(self):
+        _check(lib.sdrb_reset_state(self._h), self._h)
+
+    def synth_device(self, fmt, sample_rate, first_stream, n_streams, first_sample, n_samples, dev_ptr):
+        _check(lib.sdrb_synth_device(self._h, fmt, sample_rate, first_stream, n_streams, first_sample, n_samples,
+                                     C.c_void_p(dev_ptr)), self._h)
+
+    @property
+    def launch_count(self):
+        return int(lib.sdrb_launch_count(self._h))
+
+    def enable_kernel_timing(self, on=True):
+        _check(lib.sdrb_enable_kernel_timing(self._h, 1 if on else 0), self._h)
+
+    def last_fft_kernel_ms(self):
+        ms = C.c_float()
+        n = _check(lib.sdrb_last_fft_kernel_ms(self._h, C.byref(ms)), self._h)
+        return ms.value, n

@@ -1,0 +1,568 @@
+// api.cu — the C-ABI of include/sdr_b200.h over the CUDA kernels.  No CPU fallback: every
+// compute entry point needs a CUDA device and fails with SDRB_ERR_CUDA otherwise.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "fft_tables.h"
+#include "host_design.h"
+#include "internal.h"
+#include "synth.cuh"
+
+using namespace sdrb;
+
+namespace {
+thread_local std::string g_create_error;
+
+constexpr size_t kGenericScratchBytes = 256u << 20;  // per ping-pong buffer of the generic FFT
+
+struct StateBlobHeader {
+    uint32_t magic, version;
+    int32_t n_streams, rfMode;
+};
+constexpr uint32_t kBlobMagic = 0x53445242u;  // "SDRB"
+}  // namespace
+
+struct sdrb_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    std::string err;
+    bool configured = false;
+    sdrb_config cfg = {};
+    int n_streams = 0, max_blocks = 0;
+    int rfMode = -1;            // latched by the first SSB call (static rfFilter, ssb_demod_opt.cpp:261-263)
+    int fftPath = 0;
+    EstGeometry geo = {};
+    SsbParams ssb = {};
+    float taps255[256] = {};
+    float M[4] = {};
+    int smax = 1;
+    // device buffers
+    EstGeometry* d_geo = nullptr;
+    void* d_in = nullptr;
+    float* d_power = nullptr;
+    FrameLocal* d_local = nullptr;
+    sdrb_frame_result* d_results = nullptr;
+    FftStreamState* d_fft_state = nullptr;
+    SsbStreamState* d_ssb_state = nullptr;
+    float2 *d_zs = nullptr, *d_start = nullptr;
+    float* d_a48 = nullptr;
+    int16_t* d_pcm = nullptr;
+    float* d_taps = nullptr;
+    cpx* d_tables16k = nullptr;
+    cpx* d_tw = nullptr;
+    cpx *d_sa = nullptr, *d_sb = nullptr;
+    float* d_est_scratch = nullptr;
+    int16_t* d_sine = nullptr;
+    // last call
+    int last_blocks = 0;
+    unsigned last_stages = 0;
+    uint64_t launches = 0;
+    bool timing = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool ev_valid = false;
+    int last_fft_launches = 0;
+};
+
+static int fail(sdrb_ctx* c, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf; else g_create_error = buf;
+    return code;
+}
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(ctx, e_ == cudaErrorMemoryAllocation ? SDRB_ERR_NOMEM : SDRB_ERR_CUDA,     \
+                        "%s: %s", #call, cudaGetErrorString(e_));                                  \
+    } while (0)
+
+static void free_buffers(sdrb_ctx* c) {
+    void** ptrs[] = {(void**)&c->d_geo, &c->d_in, (void**)&c->d_power, (void**)&c->d_local, (void**)&c->d_results,
+                     (void**)&c->d_fft_state, (void**)&c->d_ssb_state, (void**)&c->d_zs, (void**)&c->d_start,
+                     (void**)&c->d_a48, (void**)&c->d_pcm, (void**)&c->d_taps, (void**)&c->d_tw, (void**)&c->d_sa,
+                     (void**)&c->d_sb, (void**)&c->d_est_scratch};
+    for (void** p : ptrs) {
+        if (*p) cudaFree(*p);
+        *p = nullptr;
+    }
+}
+
+extern "C" {
+
+int sdrb_abi_version(void) { return SDRB_ABI_VERSION; }
+
+size_t sdrb_format_bytes(int format) {
+    return format == SDRB_CU8 ? 2 : (format == SDRB_CS16 ? 4 : (format == SDRB_CF32 ? 8 : 0));
+}
+
+const char* sdrb_last_error(const sdrb_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int sdrb_create(int device, sdrb_ctx** out) {
+    sdrb_ctx* ctx = nullptr;
+    if (!out) return fail(nullptr, SDRB_ERR_ARG, "sdrb_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count <= 0)
+        return fail(nullptr, SDRB_ERR_CUDA, "no CUDA device (%s); this library has no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "count = 0");
+    if (device < 0 || device >= count) return fail(nullptr, SDRB_ERR_ARG, "device %d out of range [0,%d)", device, count);
+    CK(cudaSetDevice(device));
+    ctx = new sdrb_ctx();
+    ctx->device = device;
+    cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
+    if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
+        (e = fft16k_prepare()) != cudaSuccess || (e = estimator_prepare()) != cudaSuccess) {
+        fail(nullptr, SDRB_ERR_CUDA, "context setup: %s", cudaGetErrorString(e));
+        delete ctx;
+        return SDRB_ERR_CUDA;
+    }
+    ctx->stream = ctx->own_stream;
+    // constant tables: 16K twiddles and the synthetic source's sine table
+    const std::vector<cpx> t16 = make_f16k_tables();
+    if ((e = cudaMalloc(&ctx->d_tables16k, t16.size() * sizeof(cpx))) != cudaSuccess ||
+        (e = cudaMemcpy(ctx->d_tables16k, t16.data(), t16.size() * sizeof(cpx), cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->d_sine, SYNTH_SINE_N * sizeof(int16_t))) != cudaSuccess ||
+        (e = cudaMemcpy(ctx->d_sine, synth_sine_table(), SYNTH_SINE_N * sizeof(int16_t), cudaMemcpyHostToDevice)) != cudaSuccess) {
+        fail(nullptr, SDRB_ERR_CUDA, "table upload: %s", cudaGetErrorString(e));
+        sdrb_destroy(ctx);
+        return SDRB_ERR_CUDA;
+    }
+    *out = ctx;
+    return SDRB_OK;
+}
+
+int sdrb_destroy(sdrb_ctx* ctx) {
+    if (!ctx) return SDRB_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    free_buffers(ctx);
+    if (ctx->d_tables16k) cudaFree(ctx->d_tables16k);
+    if (ctx->d_sine) cudaFree(ctx->d_sine);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+    delete ctx;
+    return SDRB_OK;
+}
+
+int sdrb_set_cuda_stream(sdrb_ctx* ctx, void* cuda_stream) {
+    if (!ctx) return SDRB_ERR_ARG;
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+    return SDRB_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ configuration
+static bool is_pow2(int n) { return n > 0 && (n & (n - 1)) == 0; }
+
+static int check_config(sdrb_ctx* ctx, const sdrb_config* cfg) {
+    if (!cfg) return fail(ctx, SDRB_ERR_ARG, "config is NULL");
+    if (cfg->samplesPerReading < 1) return fail(ctx, SDRB_ERR_ARG, "samplesPerReading must be >= 1");
+    if (cfg->sampleRate == 0) return fail(ctx, SDRB_ERR_ARG, "sampleRate must be > 0");
+    if (cfg->inputFormat < SDRB_CU8 || cfg->inputFormat > SDRB_CF32)
+        return fail(ctx, SDRB_ERR_ARG, "inputFormat %d is not a sdrb_format", cfg->inputFormat);
+    if (cfg->fftWindow != 0 || cfg->fftRemoveDc != 0 || cfg->ssbTrueSideband != 0 || cfg->ssbChannels > 1)
+        return fail(ctx, SDRB_ERR_UNSUPPORTED,
+                    "extension stages (fftWindow, fftRemoveDc, ssbTrueSideband, ssbChannels > 1) are not built yet");
+    return SDRB_OK;
+}
+
+static int fft_path_for(int n) { return n == F16K_N ? 1 : 0; }
+
+extern "C" int sdrb_plan_config(const sdrb_config* cfg, sdrb_plan* out) {
+    if (!out) return fail(nullptr, SDRB_ERR_ARG, "plan out is NULL");
+    int rc = check_config(nullptr, cfg);
+    if (rc != SDRB_OK) return rc;
+    memset(out, 0, sizeof(*out));
+    EstGeometry g;
+    design_geometry(cfg->sampleRate, cfg->samplesPerReading, cfg->freqFocusRangeKhz, g);
+    out->n = g.n; out->focusLo = g.focusLo; out->focusHi = g.focusHi; out->focusLen = g.focusLen;
+    out->winBins1k = g.winBins1k; out->nWin = g.nWin; out->nBottom = g.nBottom;
+    for (int i = 0; i < 10; i++) { out->winLo[i] = g.winLo[i]; out->winHi[i] = g.winHi[i]; }
+    out->freqPerBin = g.freqPerBin; out->nyquist = g.nyquist;
+    SsbParams P;
+    float taps[256] = {};
+    design_ssb(cfg->sampleRate, cfg->samplesPerReading, cfg->soundMode, cfg->soundMode, cfg->upperSideband, P, taps);
+    out->decim = P.decim; out->nTaps = P.nTaps; out->pcmPerBlock = P.m;
+    out->fftPath = fft_path_for(cfg->samplesPerReading);
+    const BiquadCoef* cs[3] = {&P.rf, &P.hp, &P.bp};
+    float* dst[3] = {out->rf, out->hp, out->bp};
+    for (int i = 0; i < 3; i++) {
+        dst[i][0] = cs[i]->a0; dst[i][1] = cs[i]->a1; dst[i][2] = cs[i]->a2; dst[i][3] = cs[i]->b1; dst[i][4] = cs[i]->b2;
+    }
+    out->agcTarget = P.agcTarget; out->agcFast = P.agcFast; out->agcSlow = P.agcSlow;
+    out->gain = P.gain; out->transientCoeff = P.transientCoeff; out->dcAlpha = P.dcAlpha;
+    for (int i = 0; i < P.nTaps && i < 255; i++) out->firTaps[i] = taps[i];
+    return SDRB_OK;
+}
+
+static int upload_geometry(sdrb_ctx* ctx) {
+    design_geometry(ctx->cfg.sampleRate, ctx->cfg.samplesPerReading, ctx->cfg.freqFocusRangeKhz, ctx->geo);
+    CK(cudaMemcpyAsync(ctx->d_geo, &ctx->geo, sizeof(EstGeometry), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));  // ctx->geo is pageable host memory that may change again
+    const size_t need = estimator_scratch_floats(ctx->geo, ctx->n_streams * ctx->max_blocks);
+    if (ctx->d_est_scratch) { cudaFree(ctx->d_est_scratch); ctx->d_est_scratch = nullptr; }
+    if (need) CK(cudaMalloc(&ctx->d_est_scratch, need * sizeof(float)));
+    return SDRB_OK;
+}
+
+static int upload_ssb(sdrb_ctx* ctx) {
+    const int rf = ctx->rfMode >= 0 ? ctx->rfMode : ctx->cfg.soundMode;
+    design_ssb(ctx->cfg.sampleRate, ctx->cfg.samplesPerReading, rf, ctx->cfg.soundMode, ctx->cfg.upperSideband,
+               ctx->ssb, ctx->taps255);
+    ctx->smax = ssb_smax(ctx->ssb);
+    ssb_homogeneous_map(ctx->ssb.rf, ctx->ssb.n, ctx->M);
+    const std::vector<float> t = slot_major_taps(ctx->taps255, ctx->ssb.nTaps, ctx->ssb.decim, ctx->smax);
+    if (ctx->d_taps) { cudaFree(ctx->d_taps); ctx->d_taps = nullptr; }
+    CK(cudaMalloc(&ctx->d_taps, t.size() * sizeof(float)));
+    CK(cudaMemcpy(ctx->d_taps, t.data(), t.size() * sizeof(float), cudaMemcpyHostToDevice));
+    return SDRB_OK;
+}
+
+static int reset_state(sdrb_ctx* ctx) {
+    std::vector<FftStreamState> fs(ctx->n_streams);
+    for (auto& s : fs) {
+        memset(&s, 0, sizeof(s));
+        s.centerFrequency = ctx->cfg.centerFrequency;
+        s.maxPeakDb = -130.0f;                                  // src/dsp/fft_process.cpp:33-35
+        s.maxPeakHz = static_cast<float>(ctx->cfg.centerFrequency);
+    }
+    CK(cudaMemcpy(ctx->d_fft_state, fs.data(), fs.size() * sizeof(FftStreamState), cudaMemcpyHostToDevice));
+    CK(cudaMemset(ctx->d_ssb_state, 0, 2 * (size_t)ctx->n_streams * sizeof(SsbStreamState)));
+    ctx->rfMode = -1;
+    ctx->last_blocks = 0;
+    ctx->last_stages = 0;
+    return SDRB_OK;
+}
+
+extern "C" {
+
+int sdrb_configure(sdrb_ctx* ctx, const sdrb_config* cfg, int n_streams, int max_blocks) {
+    if (!ctx) return SDRB_ERR_ARG;
+    int rc = check_config(ctx, cfg);
+    if (rc != SDRB_OK) return rc;
+    if (n_streams < 1 || max_blocks < 1) return fail(ctx, SDRB_ERR_ARG, "n_streams and max_blocks must be >= 1");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    free_buffers(ctx);
+    ctx->configured = false;
+    ctx->cfg = *cfg;
+    ctx->n_streams = n_streams;
+    ctx->max_blocks = max_blocks;
+    const int n = cfg->samplesPerReading;
+    const size_t frames = (size_t)n_streams * max_blocks;
+    ctx->fftPath = fft_path_for(n);
+    CK(cudaMalloc(&ctx->d_geo, sizeof(EstGeometry)));
+    CK(cudaMalloc(&ctx->d_fft_state, n_streams * sizeof(FftStreamState)));
+    CK(cudaMalloc(&ctx->d_ssb_state, 2 * (size_t)n_streams * sizeof(SsbStreamState)));
+    CK(cudaMalloc(&ctx->d_local, frames * sizeof(FrameLocal)));
+    CK(cudaMalloc(&ctx->d_results, frames * sizeof(sdrb_frame_result)));
+    CK(cudaMemset(ctx->d_results, 0, frames * sizeof(sdrb_frame_result)));
+    CK(cudaMalloc(&ctx->d_zs, frames * sizeof(float2)));
+    CK(cudaMalloc(&ctx->d_start, frames * sizeof(float2)));
+    if ((rc = upload_geometry(ctx)) != SDRB_OK) return rc;
+    if ((rc = upload_ssb(ctx)) != SDRB_OK) return rc;
+    // power spectrum, audio and PCM are allocated on first use of the stage (sdrb_process)
+    if ((rc = reset_state(ctx)) != SDRB_OK) return rc;
+    ctx->configured = true;
+    return SDRB_OK;
+}
+
+int sdrb_set_center_frequency(sdrb_ctx* ctx, int stream, uint32_t center_hz) {
+    if (!ctx || !ctx->configured) return fail(ctx, SDRB_ERR_STATE, "not configured");
+    if (stream < -1 || stream >= ctx->n_streams) return fail(ctx, SDRB_ERR_ARG, "stream %d out of range", stream);
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    std::vector<FftStreamState> fs(ctx->n_streams);
+    CK(cudaMemcpy(fs.data(), ctx->d_fft_state, fs.size() * sizeof(FftStreamState), cudaMemcpyDeviceToHost));
+    for (int s = 0; s < ctx->n_streams; s++)
+        if (stream < 0 || s == stream) { fs[s].centerFrequency = center_hz; fs[s].centerChanged = 1; }
+    CK(cudaMemcpy(ctx->d_fft_state, fs.data(), fs.size() * sizeof(FftStreamState), cudaMemcpyHostToDevice));
+    if (stream < 0) ctx->cfg.centerFrequency = center_hz;
+    return SDRB_OK;
+}
+
+int sdrb_set_focus_range(sdrb_ctx* ctx, int focus_khz) {
+    if (!ctx || !ctx->configured) return fail(ctx, SDRB_ERR_STATE, "not configured");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->cfg.freqFocusRangeKhz = focus_khz;
+    return upload_geometry(ctx);
+}
+
+int sdrb_set_sound_mode(sdrb_ctx* ctx, int mode) {
+    if (!ctx || !ctx->configured) return fail(ctx, SDRB_ERR_STATE, "not configured");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->cfg.soundMode = mode;
+    return upload_ssb(ctx);
+}
+
+int sdrb_pcm_per_block(const sdrb_ctx* ctx) { return (ctx && ctx->configured) ? ctx->ssb.m : SDRB_ERR_STATE; }
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ the hot path
+static int ensure_fft_buffers(sdrb_ctx* ctx) {
+    const int n = ctx->cfg.samplesPerReading;
+    const size_t frames = (size_t)ctx->n_streams * ctx->max_blocks;
+    if (!ctx->d_power) CK(cudaMalloc(&ctx->d_power, frames * (size_t)n * sizeof(float)));
+    if (ctx->fftPath == 0 && !ctx->d_tw) {
+        std::vector<cpx> tw(n);
+        for (int k = 0; k < n; k++) tw[k] = twiddle(k, n);
+        CK(cudaMalloc(&ctx->d_tw, (size_t)n * sizeof(cpx)));
+        CK(cudaMemcpy(ctx->d_tw, tw.data(), (size_t)n * sizeof(cpx), cudaMemcpyHostToDevice));
+        if (fft_generic_passes(n) > 1) {
+            size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
+            if (chunk < 1) chunk = 1;
+            if (chunk > frames) chunk = frames;
+            CK(cudaMalloc(&ctx->d_sa, chunk * (size_t)n * sizeof(cpx)));
+            if (fft_generic_passes(n) > 2) CK(cudaMalloc(&ctx->d_sb, chunk * (size_t)n * sizeof(cpx)));
+        }
+    }
+    return SDRB_OK;
+}
+
+static int ensure_ssb_buffers(sdrb_ctx* ctx) {
+    const size_t frames = (size_t)ctx->n_streams * ctx->max_blocks;
+    const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 1;
+    if (!ctx->d_a48) CK(cudaMalloc(&ctx->d_a48, frames * m * sizeof(float)));
+    if (!ctx->d_pcm) CK(cudaMalloc(&ctx->d_pcm, frames * m * sizeof(int16_t)));
+    return SDRB_OK;
+}
+
+extern "C" {
+
+int sdrb_process(sdrb_ctx* ctx, const void* iq, int on_device, int n_blocks, unsigned stages) {
+    if (!ctx || !ctx->configured) return fail(ctx, SDRB_ERR_STATE, "sdrb_process before sdrb_configure");
+    if (!iq) return fail(ctx, SDRB_ERR_ARG, "iq is NULL");
+    if (n_blocks < 1 || n_blocks > ctx->max_blocks)
+        return fail(ctx, SDRB_ERR_ARG, "n_blocks %d outside [1, %d]", n_blocks, ctx->max_blocks);
+    if ((stages & ~(SDRB_STAGE_FFT | SDRB_STAGE_SSB)) || stages == 0)
+        return fail(ctx, SDRB_ERR_ARG, "stages must be a combination of SDRB_STAGE_FFT | SDRB_STAGE_SSB");
+    const int n = ctx->cfg.samplesPerReading, fmt = ctx->cfg.inputFormat;
+    const size_t bps = sdrb_format_bytes(fmt);
+    if ((stages & SDRB_STAGE_FFT) && (!is_pow2(n) || n < 2 || n > (1 << 24)))
+        return fail(ctx, SDRB_ERR_UNSUPPORTED, "FFT length %d: only powers of two in [2, 2^24] are built", n);
+    if ((stages & SDRB_STAGE_SSB) && ((size_t)n * bps) % 64 != 0)
+        return fail(ctx, SDRB_ERR_UNSUPPORTED, "SSB block of %d samples: block bytes must be a multiple of 64", n);
+    CK(cudaSetDevice(ctx->device));
+    const int frames = ctx->n_streams * n_blocks;
+    const size_t in_bytes = (size_t)frames * n * bps;
+    cudaStream_t st = ctx->stream;
+    int rc;
+
+    const void* d_iq = iq;
+    if (!on_device) {
+        if (!ctx->d_in) CK(cudaMalloc(&ctx->d_in, (size_t)ctx->n_streams * ctx->max_blocks * n * bps));
+        CK(cudaMemcpyAsync(ctx->d_in, iq, in_bytes, cudaMemcpyHostToDevice, st));
+        d_iq = ctx->d_in;
+    }
+    int launches = 0;
+    ctx->ev_valid = false;
+    if (stages & SDRB_STAGE_FFT) {
+        if ((rc = ensure_fft_buffers(ctx)) != SDRB_OK) return rc;
+        if (ctx->timing) CK(cudaEventRecord(ctx->ev0, st));
+        int fft_launches = 0;
+        if (ctx->fftPath == 1) {
+            CK(launch_fft16k(fmt, d_iq, ctx->d_power, ctx->d_tables16k, frames, ctx->sm_count, st));
+            fft_launches = 1;
+        } else {
+            size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
+            if (chunk < 1) chunk = 1;
+            for (size_t f0 = 0; f0 < (size_t)frames; f0 += chunk) {
+                const int nf = (int)((size_t)frames - f0 < chunk ? (size_t)frames - f0 : chunk);
+                CK(launch_fft_generic(fmt, static_cast<const unsigned char*>(d_iq) + f0 * n * bps,
+                                      ctx->d_power + f0 * n, ctx->d_sa, ctx->d_sb, ctx->d_tw, n, nf, st,
+                                      &fft_launches));
+            }
+        }
+        if (ctx->timing) { CK(cudaEventRecord(ctx->ev1, st)); ctx->ev_valid = true; }
+        ctx->last_fft_launches = fft_launches;
+        launches += fft_launches;
+        CK(launch_estimator(ctx->d_power, ctx->d_geo, ctx->geo, ctx->d_local, ctx->d_est_scratch, frames, st));
+        CK(launch_tracker(ctx->d_local, ctx->d_geo, ctx->d_fft_state, ctx->d_results, ctx->n_streams, n_blocks, st));
+        launches += 2;
+    }
+    if (stages & SDRB_STAGE_SSB) {
+        if (ctx->rfMode < 0) {  // first SSB block latches the RF low-pass design
+            ctx->rfMode = ctx->cfg.soundMode;
+            if ((rc = upload_ssb(ctx)) != SDRB_OK) return rc;
+        }
+        if ((rc = ensure_ssb_buffers(ctx)) != SDRB_OK) return rc;
+        CK(launch_ssb(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->M, ctx->d_zs, ctx->d_start, ctx->d_ssb_state,
+                      ctx->d_a48, ctx->d_pcm, ctx->n_streams, n_blocks, st, &launches));
+    }
+    ctx->launches += (uint64_t)launches;
+    ctx->last_blocks = n_blocks;
+    ctx->last_stages |= stages;
+    if (!on_device) CK(cudaStreamSynchronize(st));  // the host buffer is only borrowed for the call
+    return SDRB_OK;
+}
+
+int sdrb_sync(sdrb_ctx* ctx) {
+    if (!ctx) return SDRB_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SDRB_OK;
+}
+
+int sdrb_get_results(sdrb_ctx* ctx, sdrb_frame_result* host_out, size_t capacity_records) {
+    if (!ctx || !ctx->configured || !(ctx->last_stages & SDRB_STAGE_FFT))
+        return fail(ctx, SDRB_ERR_STATE, "no FFT results: call sdrb_process with SDRB_STAGE_FFT first");
+    const size_t nrec = (size_t)ctx->n_streams * ctx->last_blocks;
+    if (!host_out || capacity_records < nrec) return fail(ctx, SDRB_ERR_ARG, "results buffer holds %zu < %zu records", capacity_records, nrec);
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpyAsync(host_out, ctx->d_results, nrec * sizeof(sdrb_frame_result), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SDRB_OK;
+}
+
+int sdrb_results_device(sdrb_ctx* ctx, const sdrb_frame_result** dev_ptr) {
+    if (!ctx || !ctx->configured || !dev_ptr) return fail(ctx, SDRB_ERR_STATE, "not configured");
+    *dev_ptr = ctx->d_results;
+    return SDRB_OK;
+}
+
+int sdrb_power_device(sdrb_ctx* ctx, const float** dev_ptr) {
+    if (!ctx || !ctx->configured || !dev_ptr) return fail(ctx, SDRB_ERR_STATE, "not configured");
+    if (!ctx->d_power) return fail(ctx, SDRB_ERR_STATE, "no power spectrum yet");
+    *dev_ptr = ctx->d_power;
+    return SDRB_OK;
+}
+
+int sdrb_get_power(sdrb_ctx* ctx, int stream, int block, float* host_out) {
+    if (!ctx || !ctx->configured || !ctx->d_power) return fail(ctx, SDRB_ERR_STATE, "no power spectrum yet");
+    if (stream < 0 || stream >= ctx->n_streams || block < 0 || block >= ctx->last_blocks || !host_out)
+        return fail(ctx, SDRB_ERR_ARG, "stream/block out of range");
+    const size_t n = ctx->cfg.samplesPerReading;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpyAsync(host_out, ctx->d_power + ((size_t)stream * ctx->last_blocks + block) * n, n * sizeof(float),
+                       cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SDRB_OK;
+}
+
+int sdrb_pcm_device(sdrb_ctx* ctx, const int16_t** dev_ptr) {
+    if (!ctx || !ctx->configured || !dev_ptr) return fail(ctx, SDRB_ERR_STATE, "not configured");
+    if (!ctx->d_pcm) return fail(ctx, SDRB_ERR_STATE, "no PCM yet");
+    *dev_ptr = ctx->d_pcm;
+    return SDRB_OK;
+}
+
+int sdrb_get_pcm(sdrb_ctx* ctx, int16_t* host_out, size_t capacity_samples) {
+    if (!ctx || !ctx->configured || !ctx->d_pcm || !(ctx->last_stages & SDRB_STAGE_SSB))
+        return fail(ctx, SDRB_ERR_STATE, "no PCM: call sdrb_process with SDRB_STAGE_SSB first");
+    const size_t ns = (size_t)ctx->n_streams * ctx->last_blocks * ctx->ssb.m;
+    if (capacity_samples < ns || (!host_out && ns)) return fail(ctx, SDRB_ERR_ARG, "PCM buffer holds %zu < %zu samples", capacity_samples, ns);
+    CK(cudaSetDevice(ctx->device));
+    if (ns) CK(cudaMemcpyAsync(host_out, ctx->d_pcm, ns * sizeof(int16_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SDRB_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ state, synth, introspection
+extern "C" {
+
+size_t sdrb_state_bytes(const sdrb_ctx* ctx) {
+    if (!ctx || !ctx->configured) return 0;
+    return sizeof(StateBlobHeader) + (size_t)ctx->n_streams * (sizeof(FftStreamState) + sizeof(SsbStreamState));
+}
+
+int sdrb_save_state(sdrb_ctx* ctx, void* host_blob, size_t bytes) {
+    if (!ctx || !ctx->configured) return fail(ctx, SDRB_ERR_STATE, "not configured");
+    if (!host_blob || bytes < sdrb_state_bytes(ctx)) return fail(ctx, SDRB_ERR_ARG, "state blob too small");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    unsigned char* p = static_cast<unsigned char*>(host_blob);
+    StateBlobHeader h = {kBlobMagic, SDRB_ABI_VERSION, ctx->n_streams, ctx->rfMode};
+    memcpy(p, &h, sizeof h);
+    p += sizeof h;
+    CK(cudaMemcpy(p, ctx->d_fft_state, (size_t)ctx->n_streams * sizeof(FftStreamState), cudaMemcpyDeviceToHost));
+    p += (size_t)ctx->n_streams * sizeof(FftStreamState);
+    CK(cudaMemcpy(p, ctx->d_ssb_state, (size_t)ctx->n_streams * sizeof(SsbStreamState), cudaMemcpyDeviceToHost));
+    return SDRB_OK;
+}
+
+int sdrb_load_state(sdrb_ctx* ctx, const void* host_blob, size_t bytes) {
+    if (!ctx || !ctx->configured) return fail(ctx, SDRB_ERR_STATE, "not configured");
+    if (!host_blob || bytes < sdrb_state_bytes(ctx)) return fail(ctx, SDRB_ERR_ARG, "state blob too small");
+    const unsigned char* p = static_cast<const unsigned char*>(host_blob);
+    StateBlobHeader h;
+    memcpy(&h, p, sizeof h);
+    if (h.magic != kBlobMagic || h.version != SDRB_ABI_VERSION || h.n_streams != ctx->n_streams)
+        return fail(ctx, SDRB_ERR_ARG, "state blob does not match this context (magic/version/stream count)");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    p += sizeof h;
+    CK(cudaMemcpy(ctx->d_fft_state, p, (size_t)ctx->n_streams * sizeof(FftStreamState), cudaMemcpyHostToDevice));
+    p += (size_t)ctx->n_streams * sizeof(FftStreamState);
+    CK(cudaMemcpy(ctx->d_ssb_state, p, (size_t)ctx->n_streams * sizeof(SsbStreamState), cudaMemcpyHostToDevice));
+    ctx->rfMode = h.rfMode;
+    return upload_ssb(ctx);
+}
+
+int sdrb_reset_state(sdrb_ctx* ctx) {
+    if (!ctx || !ctx->configured) return fail(ctx, SDRB_ERR_STATE, "not configured");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    int rc = reset_state(ctx);
+    if (rc != SDRB_OK) return rc;
+    return upload_ssb(ctx);
+}
+
+int sdrb_synth_host(int format, uint32_t sample_rate, int first_stream, int n_streams, int64_t first_sample,
+                    int64_t n_samples, void* host_out) {
+    if (sdrb_format_bytes(format) == 0 || sample_rate == 0 || n_streams < 0 || n_samples < 0 || first_sample < 0 ||
+        !host_out)
+        return fail(nullptr, SDRB_ERR_ARG, "sdrb_synth_host: bad argument");
+    synth_host(format, sample_rate, first_stream, n_streams, first_sample, n_samples, host_out);
+    return SDRB_OK;
+}
+
+int sdrb_synth_device(sdrb_ctx* ctx, int format, uint32_t sample_rate, int first_stream, int n_streams,
+                      int64_t first_sample, int64_t n_samples, void* dev_out) {
+    if (!ctx) return SDRB_ERR_ARG;
+    if (sdrb_format_bytes(format) == 0 || sample_rate == 0 || n_streams < 0 || n_samples < 0 || first_sample < 0 ||
+        !dev_out)
+        return fail(ctx, SDRB_ERR_ARG, "sdrb_synth_device: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    CK(launch_synth(format, sample_rate, first_stream, n_streams, first_sample, n_samples, dev_out, ctx->d_sine,
+                    ctx->stream));
+    ctx->launches += (uint64_t)((n_streams + 32767) / 32768);
+    return SDRB_OK;
+}
+
+uint64_t sdrb_launch_count(const sdrb_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int sdrb_enable_kernel_timing(sdrb_ctx* ctx, int on) {
+    if (!ctx) return SDRB_ERR_ARG;
+    ctx->timing = on != 0;
+    ctx->ev_valid = false;
+    return SDRB_OK;
+}
+
+int sdrb_last_fft_kernel_ms(sdrb_ctx* ctx, float* ms_total) {
+    if (!ctx || !ms_total) return SDRB_ERR_ARG;
+    if (!ctx->ev_valid) return fail(ctx, SDRB_ERR_STATE, "kernel timing is off or no FFT stage ran");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaEventSynchronize(ctx->ev1));
+    CK(cudaEventElapsedTime(ms_total, ctx->ev0, ctx->ev1));
+    return ctx->last_fft_launches;
+}
+
+}  // extern "C"

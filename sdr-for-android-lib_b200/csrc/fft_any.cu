@@ -1,0 +1,170 @@
+// fft_any.cu — generic power-of-two FFT for block lengths without a dedicated kernel.
+//
+// Replaces fftwf_plan_dft_1d/fftwf_execute (src/dsp/fft_process.cpp:77-79) for any
+// N = 2^p, 1 <= p <= 24, as a sequence of Stockham autosort passes of radix 16 (and one
+// pass of radix 8/4/2 for the remainder) over global memory.  The first pass fuses the
+// ingest convert (K1), the last pass fuses |X|^2, the wire-format scale and the fftshift
+// (K3/K4, src/dsp/fft_process.cpp:83-97).  This path moves 16 B per sample per pass, so it
+// is the correctness path; N = 16384 has its own single-pass kernel (fft16k.cu) and the
+// 64K / 1M sizes their four-step kernels (fft_big.cu).
+#include "internal.h"
+
+namespace sdrb {
+
+SDRB_HD void fft8(cpx* v) {
+    // X[k] is left in v[(k & 1) * 4 + (k >> 1)]
+    fft2(v[0], v[4]);
+    fft2(v[1], v[5]);
+    fft2(v[2], v[6]);
+    fft2(v[3], v[7]);
+    v[5] = mul_w8_1(v[5]);
+    v[6] = mul_mi(v[6]);
+    v[7] = mul_w8_3(v[7]);
+    fft4(v[0], v[1], v[2], v[3]);
+    fft4(v[4], v[5], v[6], v[7]);
+}
+
+template <int R>
+struct Radix;
+template <>
+struct Radix<16> {
+    SDRB_HD static void run(cpx* v) { fft16(v); }
+    SDRB_HD static int slot(int k) { return rev16(k); }
+};
+template <>
+struct Radix<8> {
+    SDRB_HD static void run(cpx* v) { fft8(v); }
+    SDRB_HD static int slot(int k) { return (k & 1) * 4 + (k >> 1); }
+};
+template <>
+struct Radix<4> {
+    SDRB_HD static void run(cpx* v) { fft4(v[0], v[1], v[2], v[3]); }
+    SDRB_HD static int slot(int k) { return k; }
+};
+template <>
+struct Radix<2> {
+    SDRB_HD static void run(cpx* v) { fft2(v[0], v[1]); }
+    SDRB_HD static int slot(int k) { return k; }
+};
+
+// One Stockham pass.  Ns = product of the radices of the passes already done.
+// FMT >= 0: input is the raw wire format (first pass); FMT < 0: input is cpx.
+// LAST: write scaled, shifted power instead of cpx.
+template <int R, int FMT, bool LAST>
+__global__ void __launch_bounds__(256)
+k_stockham(const void* __restrict__ in_, void* __restrict__ out_, const cpx* __restrict__ tw, int n, int Ns,
+           float power_scale) {
+    const int nb = n / R;  // butterflies per frame
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= nb) return;
+    const size_t frame = blockIdx.y;
+    cpx v[R];
+    if (FMT >= 0) {
+        typedef typename Ingest<(FMT >= 0 ? FMT : 0)>::raw_t raw_t;
+        const raw_t* in = static_cast<const raw_t*>(in_) + frame * (size_t)n;
+#pragma unroll
+        for (int r = 0; r < R; r++) v[r] = Ingest<(FMT >= 0 ? FMT : 0)>::cvt(in[j + r * nb]);
+    } else {
+        const cpx* in = static_cast<const cpx*>(in_) + frame * (size_t)n;
+#pragma unroll
+        for (int r = 0; r < R; r++) v[r] = in[j + r * nb];
+    }
+    const int k = j & (Ns - 1);
+    if (Ns > 1) {
+        const int tstep = n / (Ns * R);  // W_{Ns R}^(k r) = W_n^(k r tstep)
+#pragma unroll
+        for (int r = 1; r < R; r++) v[r] = cmul(v[r], tw[(size_t)k * r * tstep]);
+    }
+    Radix<R>::run(v);
+    const int j0 = (j - k) * R + k;
+    if (LAST) {
+        float* out = static_cast<float*>(out_) + frame * (size_t)n;
+        const int half = n >> 1;
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            const cpx x = v[Radix<R>::slot(r)];
+            const int bin = j0 + r * Ns;
+            // re*re + im*im, then fftshift: bin k lands at (k + N/2) mod N
+            const float p = __fadd_rn(__fmul_rn(x.x, x.x), __fmul_rn(x.y, x.y));
+            out[(bin + half) & (n - 1)] = p * power_scale;
+        }
+    } else {
+        cpx* out = static_cast<cpx*>(out_) + frame * (size_t)n;
+#pragma unroll
+        for (int r = 0; r < R; r++) out[j0 + r * Ns] = v[Radix<R>::slot(r)];
+    }
+}
+
+template <int R, int FMT>
+static void launch_pass(bool last, const void* in, void* out, const cpx* tw, int n, int Ns, float ps,
+                        int n_frames, cudaStream_t st) {
+    const int nb = n / R;
+    const int threads = nb < 256 ? (nb < 32 ? 32 : nb) : 256;
+    dim3 grid((unsigned)((nb + threads - 1) / threads), (unsigned)n_frames);
+    if (last)
+        k_stockham<R, FMT, true><<<grid, threads, 0, st>>>(in, out, tw, n, Ns, ps);
+    else
+        k_stockham<R, FMT, false><<<grid, threads, 0, st>>>(in, out, tw, n, Ns, ps);
+}
+
+template <int FMT>
+static void launch_pass_r(int R, bool last, const void* in, void* out, const cpx* tw, int n, int Ns, float ps,
+                          int n_frames, cudaStream_t st) {
+    switch (R) {
+        case 16: launch_pass<16, FMT>(last, in, out, tw, n, Ns, ps, n_frames, st); break;
+        case 8: launch_pass<8, FMT>(last, in, out, tw, n, Ns, ps, n_frames, st); break;
+        case 4: launch_pass<4, FMT>(last, in, out, tw, n, Ns, ps, n_frames, st); break;
+        default: launch_pass<2, FMT>(last, in, out, tw, n, Ns, ps, n_frames, st); break;
+    }
+}
+
+int fft_generic_passes(int n) {
+    int p = 0;
+    while ((1 << p) < n) p++;
+    return (p + 3) / 4;
+}
+
+cudaError_t launch_fft_generic(int fmt, const void* iq, float* power, cpx* scratch_a, cpx* scratch_b,
+                               const cpx* twiddles, int n, int n_frames, cudaStream_t st, int* launches) {
+    if (n_frames <= 0) return cudaSuccess;
+    if (n < 2 || (n & (n - 1)) != 0) return cudaErrorInvalidValue;
+    int bits = 0;
+    while ((1 << bits) < n) bits++;
+    float ps = fmt == FMT_CU8 ? Ingest<FMT_CU8>::kPowerScale
+                              : (fmt == FMT_CS16 ? Ingest<FMT_CS16>::kPowerScale : 1.0f);
+    // gridDim.y limit
+    for (int f0 = 0; f0 < n_frames; f0 += 65535) {
+        const int nf = n_frames - f0 < 65535 ? n_frames - f0 : 65535;
+        const size_t in_bytes = fmt == FMT_CU8 ? 2 : (fmt == FMT_CS16 ? 4 : 8);
+        const void* src = static_cast<const unsigned char*>(iq) + (size_t)f0 * n * in_bytes;
+        float* pw = power + (size_t)f0 * n;
+        cpx* sa = scratch_a;  // scratch holds one launch group at a time (stream order serialises reuse)
+        cpx* sb = scratch_b;
+        int left = bits, Ns = 1, pass = 0;
+        const void* cur = src;
+        while (left > 0) {
+            const int rb = left >= 4 ? 4 : left;
+            const int R = 1 << rb;
+            const bool last = (left == rb);
+            void* dst = last ? static_cast<void*>(pw) : static_cast<void*>((pass & 1) ? sb : sa);
+            if (pass == 0) {
+                switch (fmt) {
+                    case FMT_CU8: launch_pass_r<FMT_CU8>(R, last, cur, dst, twiddles, n, Ns, ps, nf, st); break;
+                    case FMT_CS16: launch_pass_r<FMT_CS16>(R, last, cur, dst, twiddles, n, Ns, ps, nf, st); break;
+                    case FMT_CF32: launch_pass_r<FMT_CF32>(R, last, cur, dst, twiddles, n, Ns, ps, nf, st); break;
+                    default: return cudaErrorInvalidValue;
+                }
+            } else {
+                launch_pass_r<-1>(R, last, cur, dst, twiddles, n, Ns, ps, nf, st);
+            }
+            if (launches) (*launches)++;
+            cur = dst;
+            Ns *= R;
+            left -= rb;
+            pass++;
+        }
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace sdrb

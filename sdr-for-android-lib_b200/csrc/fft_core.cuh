@@ -5,6 +5,7 @@
 // __host__ __device__ so that tests/cpp/fft_sim.cpp can run the exact index and
 // butterfly logic of the kernels on the CPU, thread by thread, without a GPU.
 #pragma once
+#include <stdint.h>
 
 #if defined(__CUDACC__)
 #define SDRB_HD __host__ __device__ __forceinline__
@@ -76,5 +77,38 @@ SDRB_HD void fft16(cpx* v) {
     fft4(v[8], v[9], v[10], v[11]);
     fft4(v[12], v[13], v[14], v[15]);
 }
+
+// ---------------------------------------------------------------- ingest formats
+enum : int { FMT_CU8 = 0, FMT_CS16 = 1, FMT_CF32 = 2 };
+
+// One complex sample of the wire format -> float pair (include/sdr_b200.h sdrb_format).
+// CU8 follows convertIQ (src/ssb/ssb_demod_opt.cpp:37-41) except that the exact
+// power-of-two scale 1/128 is deferred: the FFT is linear and scaling by 2^-7 commutes
+// exactly with every float operation, so |X|^2 is multiplied by 2^-14 at the end and
+// the result is bit-identical to scaling the input first.
+template <int FMT>
+struct Ingest;
+template <>
+struct Ingest<FMT_CU8> {
+    typedef uint16_t raw_t;  // two bytes: I, Q
+    static constexpr float kPowerScale = 1.0f / 16384.0f;
+    SDRB_HD static cpx cvt(uint16_t r) {
+        return mk((float)(int)(r & 0xffu) - 127.4f, (float)(int)(r >> 8) - 127.4f);
+    }
+};
+template <>
+struct Ingest<FMT_CS16> {
+    typedef uint32_t raw_t;  // two int16: I, Q   (x * 2^-15, deferred the same way)
+    static constexpr float kPowerScale = 1.0f / 1073741824.0f;
+    SDRB_HD static cpx cvt(uint32_t r) {
+        return mk((float)(int)(int16_t)(r & 0xffffu), (float)(int)(int16_t)(r >> 16));
+    }
+};
+template <>
+struct Ingest<FMT_CF32> {
+    typedef cpx raw_t;
+    static constexpr float kPowerScale = 1.0f;
+    SDRB_HD static cpx cvt(cpx r) { return r; }
+};
 
 }  // namespace sdrb

@@ -5,6 +5,7 @@
 
 #include "../../include/sdr_b200.h"
 #include "fft_core.cuh"
+#include "fft16k.cuh"
 
 namespace sdrb {
 
@@ -22,6 +23,14 @@ struct EstGeometry {
     float freqPerBin;
     float nyquist;
     float sampleRateF;
+    // scalars of :281-285,299 that depend on the geometry only, evaluated on the host with
+    // the reference's float expressions (glibc logf/sqrtf)
+    float sqrt2logN;       // sqrt(2 ln focusLen)
+    float gumbelDen;       // sqrt(6.f) * sqrt2logN
+    float sqrtWin1k;       // sqrt(float(winBins1k))
+    // staging layout of the estimator kernel: segment 0 = focus band, 1..nWin = windows
+    int segOff[12];        // float offsets, segOff[nWin+1] = total
+    int totalBins;
 };
 
 // Frame-local result of the estimator kernel, before the per-stream sequential part.
@@ -90,12 +99,21 @@ cudaError_t launch_fft16k(int fmt, const void* iq, float* power, const cpx* tabl
 cudaError_t fft16k_prepare();  // sets max dynamic shared memory attributes once per process
 // fft_any.cu : generic power-of-two path (N != 16384)
 cudaError_t launch_fft_generic(int fmt, const void* iq, float* power, cpx* scratch_a, cpx* scratch_b,
-                               const cpx* twiddles, int n, int n_frames, cudaStream_t st);
+                               const cpx* twiddles, int n, int n_frames, cudaStream_t st, int* launches);
+int fft_generic_passes(int n);
 // estimator.cu
-cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, FrameLocal* d_local,
-                             int n, int n_frames, cudaStream_t st);
+cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, const EstGeometry& h_geo,
+                             FrameLocal* d_local, float* d_stage_scratch, int n_frames, cudaStream_t st);
+cudaError_t estimator_prepare();
+size_t estimator_scratch_floats(const EstGeometry& g, int n_frames);
 cudaError_t launch_tracker(const FrameLocal* d_local, const EstGeometry* d_geo, FftStreamState* d_state,
                            sdrb_frame_result* d_results, int n_streams, int n_blocks, cudaStream_t st);
+// ssb.cu.  d_state holds 2 * n_streams entries (second half = shadow slots of the audio sections);
+// d_taps is the [decim][ssb_smax] slot-major tap table; M = row-major 2x2 n-step homogeneous map.
+int ssb_smax(const SsbParams& P);
+cudaError_t launch_ssb(int fmt, const void* iq, const SsbParams& P, const float* d_taps, const float* M,
+                       float2* d_zs, float2* d_start, SsbStreamState* d_state, float* d_a48, int16_t* d_pcm,
+                       int n_streams, int n_blocks, cudaStream_t st, int* launches);
 // synth.cu
 cudaError_t launch_synth(int fmt, uint32_t fs, int first_stream, int n_streams, int64_t first_sample,
                          int64_t n_samples, void* d_out, const int16_t* d_sine, cudaStream_t st);

@@ -73,8 +73,8 @@ SDRB_HD void synth_sample(const SynthStream& p, const int16_t* tab, long long i,
     const bool on = key_pos < p.keyOn;
     if (FMT == 0) {
         const uint32_t hD = synth_mix32(hQ + 0x9E3779B9u);
-        int vi = 127 + (((hD & 255u) < 102u) ? 1 : 0) + ((nI * 7) >> 8) + ((6 * synth_cos(tab, ph2) + 16384) >> 15);
-        int vq = 127 + ((((hD >> 8) & 255u) < 102u) ? 1 : 0) + ((nQ * 7) >> 8) + ((6 * synth_sin(tab, ph2) + 16384) >> 15);
+        int vi = 127 + (((hD & 255u) < 102u) ? 1 : 0) + ((nI * 7 + 128) >> 8) + ((6 * synth_cos(tab, ph2) + 16384) >> 15);
+        int vq = 127 + ((((hD >> 8) & 255u) < 102u) ? 1 : 0) + ((nQ * 7 + 128) >> 8) + ((6 * synth_sin(tab, ph2) + 16384) >> 15);
         if (on) {
             vi += (38 * synth_cos(tab, ph1) + 16384) >> 15;
             vq += (38 * synth_sin(tab, ph1) + 16384) >> 15;
