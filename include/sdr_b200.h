@@ -156,6 +156,8 @@ int  sdrb_results_device(sdrb_ctx* ctx, const sdrb_frame_result** dev_ptr);
  * (src/dsp/fft_process.cpp:83-97).  Device layout [n_streams][n_blocks][N]. */
 int  sdrb_power_device(sdrb_ctx* ctx, const float** dev_ptr);
 int  sdrb_get_power(sdrb_ctx* ctx, int stream, int block, float* host_out);
+/* All spectra of the last call, [n_streams][n_blocks][N] floats, into host memory (pinned or pageable). */
+int  sdrb_get_power_all(sdrb_ctx* ctx, float* host_out, size_t capacity_floats);
 /* int16 PCM = the ([S)V payload; layout [n_streams][n_blocks][pcm_per_block]
  * (x ssbChannels when the NCO bank is on: [stream][channel][block][m]). */
 int  sdrb_pcm_device(sdrb_ctx* ctx, const int16_t** dev_ptr);

@@ -7,5 +7,6 @@ raises if the library has not been built.
 """
 from .binding import (  # noqa: F401
     Config, FrameResult, Plan, Context, SdrbError, lib, lib_path, plan_config, synth_host,
-    CU8, CS16, CF32, STAGE_FFT, STAGE_SSB, format_bytes, format_dtype,
+    CU8, CS16, CF32, STAGE_FFT, STAGE_SSB, format_bytes, format_dtype, RESULT_DTYPE,
 )
+from .sharding import shard_streams, gather_records, strongest_peak  # noqa: F401

@@ -74,6 +74,7 @@ EXPORTS = {
     "sdrb_results_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "sdrb_power_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "sdrb_get_power": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "sdrb_get_power_all": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "sdrb_pcm_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "sdrb_get_pcm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "sdrb_state_bytes": (C.c_size_t, [C.c_void_p]),
@@ -196,6 +197,21 @@ class Context:
     def power(self, stream, block):
         out = np.empty(self.cfg.samplesPerReading, dtype=np.float32)
         _check(lib.sdrb_get_power(self._h, stream, block, out.ctypes.data_as(C.c_void_p)), self._h)
+        return out
+
+    def power_all(self, out=None):
+        """All spectra of the last call into `out` (numpy array or pinned torch tensor) or a new array."""
+        n = self.n_streams * self.last_blocks * self.cfg.samplesPerReading
+        if out is None:
+            out = np.empty((self.n_streams, self.last_blocks, self.cfg.samplesPerReading), dtype=np.float32)
+        addr, _ = _ptr(out)
+        _check(lib.sdrb_get_power_all(self._h, C.c_void_p(addr), n), self._h)
+        return out
+
+    def results_into(self, out):
+        """Records of the last call into a preallocated buffer (numpy RESULT_DTYPE array or pinned bytes)."""
+        addr, _ = _ptr(out)
+        _check(lib.sdrb_get_results(self._h, C.c_void_p(addr), self.n_streams * self.last_blocks), self._h)
         return out
 
     def power_device_ptr(self):

@@ -455,6 +455,17 @@ int sdrb_get_power(sdrb_ctx* ctx, int stream, int block, float* host_out) {
     return SDRB_OK;
 }
 
+int sdrb_get_power_all(sdrb_ctx* ctx, float* host_out, size_t capacity_floats) {
+    if (!ctx || !ctx->configured || !ctx->d_power || !(ctx->last_stages & SDRB_STAGE_FFT))
+        return fail(ctx, SDRB_ERR_STATE, "no power spectrum yet");
+    const size_t nf = (size_t)ctx->n_streams * ctx->last_blocks * ctx->cfg.samplesPerReading;
+    if (!host_out || capacity_floats < nf) return fail(ctx, SDRB_ERR_ARG, "power buffer holds %zu < %zu floats", capacity_floats, nf);
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpyAsync(host_out, ctx->d_power, nf * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SDRB_OK;
+}
+
 int sdrb_pcm_device(sdrb_ctx* ctx, const int16_t** dev_ptr) {
     if (!ctx || !ctx->configured || !dev_ptr) return fail(ctx, SDRB_ERR_STATE, "not configured");
     if (!ctx->d_pcm) return fail(ctx, SDRB_ERR_STATE, "no PCM yet");

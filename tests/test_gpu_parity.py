@@ -1,0 +1,259 @@
+"""GPU parity tests: the CUDA path, called through the C-ABI (include/sdr_b200.h), against the oracle
+on identical seeded synthetic IQ.  Tolerances are BASELINE.json's: peak bin / frequencies bit-exact
+away from ties, power 1e-5 relative (on top of the float-FFT error floor, stated below), scalars
+0.01 dB, PCM +-1 LSB."""
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+
+pytestmark = pytest.mark.gpu
+FC = 430_000_000
+
+
+def make_iq(sdrb, fmt, fs, first_stream, n_streams, n_blocks, n, first_block=0):
+    """[S, B, n, 2] wire-format blocks, contiguous in time per stream."""
+    raw = sdrb.synth_host(fmt, fs, first_stream, n_streams, first_block * n, n_blocks * n)
+    return np.ascontiguousarray(raw.reshape(n_streams, n_blocks, n, 2))
+
+
+def power_tolerance(p_ref):
+    # 1e-5 relative power + the float32 FFT error floor (amplitude error ~ eps * sqrt(total energy)),
+    # the same bound tests/cpp/fft_sim.cpp uses against a double-precision DFT.
+    total = float(p_ref.astype(np.float64).sum())
+    return 1e-5 * p_ref + 2.0 * np.sqrt(p_ref) * 3e-7 * np.sqrt(total) + 1e-9 * total / p_ref.size
+
+
+def test_synth_device_matches_host(sdrb, gpu_ctx):
+    import torch
+    for fmt in (sdrb.CU8, sdrb.CS16, sdrb.CF32):
+        S, n, first = 3, 5000, 123_456_789_012
+        host = sdrb.synth_host(fmt, 2_000_000, 7, S, first, n)
+        dev = torch.empty(host.shape, dtype={0: torch.uint8, 1: torch.int16, 2: torch.float32}[fmt], device="cuda")
+        gpu_ctx.synth_device(fmt, 2_000_000, 7, S, first, n, dev.data_ptr())
+        gpu_ctx.sync()
+        assert np.array_equal(dev.cpu().numpy(), host)
+
+
+@pytest.mark.parametrize("fmt", [0, 1, 2])
+@pytest.mark.parametrize("n,fs", [(16384, 2_000_000), (4096, 2_000_000), (65536, 30_720_000), (256, 250_000),
+                                  (32768, 2_500_000), (2, 250_000), (8, 250_000)])
+def test_power_spectrum_parity(sdrb, gpu_ctx, fmt, n, fs):
+    S, B = 3, 2
+    iq = make_iq(sdrb, fmt, fs, 11, S, B, n)
+    gpu_ctx.configure(sdrb.Config(FC, fs, n, 5, inputFormat=fmt), S, B)
+    gpu_ctx.process(iq, B, sdrb.STAGE_FFT)
+    for s in range(S):
+        for b in range(B):
+            ref = ol.oracle_power(ol.to_cf32(iq[s, b], fmt))
+            got = gpu_ctx.power(s, b)
+            assert np.all(np.isfinite(got))
+            assert np.all(np.abs(got - ref) <= power_tolerance(ref)), (s, b, np.abs(got - ref).max())
+            # dB view (10*log10f) within 1e-3 dB for every bin above the float-FFT floor
+            strong = ref > 1e-4 * ref.max()
+            d = np.abs(10 * np.log10(got[strong] + 1e-20) - 10 * np.log10(ref[strong] + 1e-20))
+            assert d.max() < 1e-3
+
+
+def check_results(got, exp, n_frames_checked, where):
+    """got: numpy record, exp: oracle dict.  Scalars within 0.01 dB; indices/frequencies exact."""
+    for k in ("meanSnrDb", "peakAboveNoiseMeanDb", "maxBinSnrDb", "best1kHzSnrDb", "perBinMean", "absPeakDb",
+              "signalPowerDb"):
+        assert abs(float(got[k]) - exp[k]) < 0.01, (where, k, float(got[k]), exp[k])
+    for k in ("meanSnrSigma", "maxBinSnrSigma", "best1kHzSnrSigma"):   # dB / sigma, sigma floors >= 0.5
+        assert abs(float(got[k]) - exp[k]) < 0.02 + 1e-3 * abs(exp[k]), (where, k, float(got[k]), exp[k])
+    assert int(got["peakBin"]) == exp["peakBin"], where
+    assert int(got["valid"]) == exp["valid"], where
+    assert int(got["detectionFlag"]) == exp["detectionFlag"], where
+    assert np.float32(got["best1kHzCenterFreqHz"]) == np.float32(exp["best1kHzCenterFreqHz"]), where
+    assert np.float32(got["trackingFrequencyHz"]) == np.float32(exp["trackingFrequencyHz"]), where
+    assert int(got["trackingFrequency"]) == exp["trackingFrequency"], where
+
+
+def tie_free(power, plan, margin=4e-6):
+    """True when the focus-band maximum is unique beyond dB-float resolution."""
+    f = np.sort(power[plan.focusLo:plan.focusHi + 1])[::-1]
+    return len(f) < 2 or (f[0] - f[1]) > margin * f[0]
+
+
+@pytest.mark.parametrize("fmt,n,fs,focus", [(0, 16384, 2_000_000, 5), (0, 16384, 2_000_000, 200),
+                                            (1, 65536, 30_720_000, 5), (2, 4096, 2_500_000, 5),
+                                            (0, 16384, 2_000_000, 300), (2, 16384, 2_000_000, 0),
+                                            (0, 1024, 250_000, 5)])
+def test_estimator_parity(sdrb, gpu_ctx, fmt, n, fs, focus):
+    """Estimator + tracker against the oracle fed (a) the GPU's own power spectrum — isolates
+    evaluateSignalStrength — and (b) the oracle's own DFT — the whole FFT path."""
+    S, B = 4, 12
+    cfg = sdrb.Config(FC, fs, n, focus, inputFormat=fmt)
+    plan = sdrb.plan_config(cfg)
+    iq = make_iq(sdrb, fmt, fs, 0, S, B, n)
+    gpu_ctx.configure(cfg, S, B)
+    gpu_ctx.process(iq, B, sdrb.STAGE_FFT)
+    res = gpu_ctx.results()
+    checked = 0
+    for s in range(S):
+        same, own = ol.OracleFft(FC, fs, n, focus), ol.OracleFft(FC, fs, n, focus)
+        for b in range(B):
+            p_gpu = gpu_ctx.power(s, b)
+            e1 = same.evaluate(p_gpu)
+            e2 = own.process(ol.to_cf32(iq[s, b], fmt))
+            if plan.focusLen <= 0:
+                assert int(res[s, b]["peakBin"]) == -1 and e1["peakBin"] == -1
+                continue
+            check_results(res[s, b], e1, checked, ("same-power", s, b))
+            if tie_free(p_gpu, plan) and e1["peakBin"] == e2["peakBin"]:
+                for k in ("meanSnrDb", "peakAboveNoiseMeanDb", "maxBinSnrDb", "best1kHzSnrDb", "perBinMean"):
+                    assert abs(float(res[s, b][k]) - e2[k]) < 0.01, ("own-fft", s, b, k)
+                checked += 1
+            assert np.float32(res[s, b]["peakFrequencyHz"]) == np.float32(
+                np.float32(np.float32(e1["peakBin"]) * np.float32(plan.freqPerBin))
+                + np.float32(np.float32(FC) - np.float32(plan.nyquist)))
+    if plan.focusLen > 0:
+        assert checked >= S * B // 2
+
+
+def test_tracking_follows_center_change(sdrb, gpu_ctx):
+    n, fs, S, B = 16384, 2_000_000, 2, 50
+    cfg = sdrb.Config(FC, fs, n, 5, inputFormat=0)
+    iq = make_iq(sdrb, 0, fs, 0, S, 2 * B, n)
+    gpu_ctx.configure(cfg, S, B)
+    orc = [ol.OracleFft(FC, fs, n, 5) for _ in range(S)]
+    tracked = set()
+    for call in range(2):
+        if call == 1:
+            gpu_ctx.set_center_frequency(1, FC + 25_000)
+            orc[1].set_center(FC + 25_000)
+        blk = np.ascontiguousarray(iq[:, call * B:(call + 1) * B])
+        gpu_ctx.process(blk, B, sdrb.STAGE_FFT)
+        res = gpu_ctx.results()
+        for s in range(S):
+            for b in range(B):
+                e = orc[s].evaluate(gpu_ctx.power(s, b))
+                assert int(res[s, b]["trackingFrequency"]) == e["trackingFrequency"], (call, s, b)
+                assert int(res[s, b]["detectionFlag"]) == e["detectionFlag"]
+                tracked.add(e["trackingFrequency"])
+    assert len(tracked) >= 3
+
+
+@pytest.mark.parametrize("fmt,n,fs,mode,upper,B", [(0, 16384, 2_000_000, 1, 1, 9), (0, 16384, 2_000_000, 0, 1, 4),
+                                                   (0, 16384, 2_500_000, 2, 1, 4), (0, 16384, 2_000_000, 1, 0, 3),
+                                                   (1, 65536, 30_720_000, 1, 1, 5), (2, 16384, 2_000_000, 1, 1, 4),
+                                                   (2, 4096, 250_000, 1, 1, 6), (1, 16384, 1_024_000, 1, 1, 3),
+                                                   (0, 128, 2_000_000, 1, 1, 3)])
+def test_ssb_pcm_parity(sdrb, gpu_ctx, fmt, n, fs, mode, upper, B):
+    S = 5
+    cfg = sdrb.Config(FC, fs, n, 5, soundMode=mode, inputFormat=fmt, upperSideband=upper)
+    iq = make_iq(sdrb, fmt, fs, 20, S, B, n)
+    gpu_ctx.configure(cfg, S, B)
+    gpu_ctx.process(iq, B, sdrb.STAGE_SSB)
+    pcm = gpu_ctx.pcm()
+    m = gpu_ctx.pcm_per_block
+    assert pcm.shape == (S, B, m)
+    exact = total = 0
+    for s in range(S):
+        o = ol.OracleSsb()
+        for b in range(B):
+            exp = o.process(ol.to_cf32(iq[s, b], fmt), fs, upper, mode)
+            assert len(exp) == m
+            d = np.abs(pcm[s, b].astype(np.int32) - exp.astype(np.int32))
+            assert d.max(initial=0) <= 1, (s, b, int(d.max()), int(np.argmax(d)))
+            exact += int((d == 0).sum())
+            total += m
+            if not upper:
+                assert not pcm[s, b].any()
+    if total:
+        assert exact >= 0.98 * total
+        if upper and m > 10:
+            assert np.abs(pcm).max() > 50
+
+
+def test_calls_are_continuous_and_batch_independent(sdrb, gpu_ctx):
+    """Blocks split over several calls == one call; stream i of a batch == the same stream alone;
+    state save/load reproduces the continuation."""
+    n, fs, S, B = 16384, 2_000_000, 3, 8
+    cfg = sdrb.Config(FC, fs, n, 5, inputFormat=0)
+    iq = make_iq(sdrb, 0, fs, 40, S, B, n)
+    both = sdrb.STAGE_FFT | sdrb.STAGE_SSB
+    gpu_ctx.configure(cfg, S, B)
+    gpu_ctx.process(iq, B, both)
+    res_all, pcm_all = gpu_ctx.results().copy(), gpu_ctx.pcm().copy()
+    # split 3 + 5 with a checkpoint in between
+    gpu_ctx.configure(cfg, S, B)
+    gpu_ctx.process(np.ascontiguousarray(iq[:, :3]), 3, both)
+    r1, p1 = gpu_ctx.results().copy(), gpu_ctx.pcm().copy()
+    blob = gpu_ctx.save_state()
+    gpu_ctx.process(np.ascontiguousarray(iq[:, 3:]), 5, both)
+    r2, p2 = gpu_ctx.results().copy(), gpu_ctx.pcm().copy()
+    assert np.array_equal(np.concatenate([r1, r2], 1), res_all)
+    assert np.abs(np.concatenate([p1, p2], 1).astype(int) - pcm_all.astype(int)).max() <= 1
+    gpu_ctx.reset_state()
+    gpu_ctx.load_state(blob)
+    gpu_ctx.process(np.ascontiguousarray(iq[:, 3:]), 5, both)
+    assert np.array_equal(gpu_ctx.results(), r2) and np.array_equal(gpu_ctx.pcm(), p2)
+    # stream 1 alone
+    gpu_ctx.configure(cfg, 1, B)
+    gpu_ctx.process(np.ascontiguousarray(iq[1:2]), B, both)
+    assert np.array_equal(gpu_ctx.results()[0], res_all[1])
+    assert np.array_equal(gpu_ctx.pcm()[0], pcm_all[1])
+
+
+def test_device_input_equals_host_input(sdrb, gpu_ctx):
+    import torch
+    n, fs, S, B = 16384, 2_000_000, 2, 2
+    cfg = sdrb.Config(FC, fs, n, 5, inputFormat=1)
+    iq = make_iq(sdrb, 1, fs, 0, S, B, n)
+    gpu_ctx.configure(cfg, S, B)
+    gpu_ctx.process(iq, B)
+    r_h, p_h = gpu_ctx.results().copy(), gpu_ctx.pcm().copy()
+    gpu_ctx.reset_state()
+    d = torch.from_numpy(iq).cuda()
+    gpu_ctx.process(d, B)
+    gpu_ctx.sync()
+    assert np.array_equal(gpu_ctx.results(), r_h) and np.array_equal(gpu_ctx.pcm(), p_h)
+
+
+def test_error_behaviour(sdrb, gpu_ctx):
+    cfg = sdrb.Config(FC, 2_000_000, 12000, 5, inputFormat=2)
+    gpu_ctx.configure(cfg, 1, 1)
+    iq = np.zeros((1, 1, 12000, 2), np.float32)
+    with pytest.raises(sdrb.SdrbError) as e:
+        gpu_ctx.process(iq, 1, sdrb.STAGE_FFT)
+    assert e.value.code == -3 and "power" in str(e.value)
+    with pytest.raises(sdrb.SdrbError):
+        gpu_ctx.process(iq, 2, sdrb.STAGE_SSB)          # more blocks than configured
+    with pytest.raises(sdrb.SdrbError):
+        gpu_ctx.configure(sdrb.Config(FC, 0, 1024, 5), 1, 1)
+    fresh = sdrb.Context(0)
+    with pytest.raises(sdrb.SdrbError) as e:
+        fresh.process(iq, 1)
+    assert e.value.code == -4
+    fresh.close()
+
+
+def test_full_size_properties_c2(sdrb, gpu_ctx):
+    """BASELINE config 2 at full size (1024 u8 streams x 16384): Parseval per frame, peak bin at the
+    keyed tone of the streams that are keyed on, and a checksum that is stable across two runs."""
+    import torch
+    S, n, fs = 1024, 16384, 2_000_000
+    cfg = sdrb.Config(FC, fs, n, 5, inputFormat=0)
+    gpu_ctx.configure(cfg, S, 1)
+    d = torch.empty((S, 1, n, 2), dtype=torch.uint8, device="cuda")
+    gpu_ctx.synth_device(0, fs, 0, S, 0, n, d.data_ptr())
+    gpu_ctx.process(d, 1, sdrb.STAGE_FFT)
+    gpu_ctx.sync()
+    res = gpu_ctx.results()
+    x = (d.to(torch.float64) - 127.4) / 128.0
+    energy = (x * x).sum(dim=(1, 2, 3)).cpu().numpy() * n
+    got = np.array([gpu_ctx.power(s, 0).astype(np.float64).sum() for s in range(0, S, 37)])
+    assert np.allclose(got, energy[::37], rtol=2e-5)
+    plan = sdrb.plan_config(cfg)
+    keyed = [s for s in range(0, S, 4)]          # streams with s % 4 == 0 start keyed on
+    host = sdrb.synth_host(0, fs, 0, 1, 0, 8)    # touch the host generator too
+    assert np.array_equal(host[0], d[0, 0, :8].cpu().numpy())
+    for s in keyed[:64]:
+        assert plan.focusLo <= int(res[s, 0]["peakBin"]) <= plan.focusHi
+        assert float(res[s, 0]["peakAboveNoiseMeanDb"]) > 30.0
+    chk1 = res["peakBin"].astype(np.int64).sum()
+    gpu_ctx.reset_state()
+    gpu_ctx.process(d, 1, sdrb.STAGE_FFT)
+    assert gpu_ctx.results()["peakBin"].astype(np.int64).sum() == chk1
