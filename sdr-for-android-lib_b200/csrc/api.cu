@@ -38,7 +38,6 @@ struct sdrb_ctx {
     EstGeometry geo = {};
     SsbParams ssb = {};
     float taps255[256] = {};
-    float M[4] = {};
     int smax = 1;
     // device buffers
     EstGeometry* d_geo = nullptr;
@@ -48,7 +47,7 @@ struct sdrb_ctx {
     sdrb_frame_result* d_results = nullptr;
     FftStreamState* d_fft_state = nullptr;
     SsbStreamState* d_ssb_state = nullptr;
-    float2 *d_zs = nullptr, *d_start = nullptr;
+    float2* d_start = nullptr;
     float* d_a48 = nullptr;
     int16_t* d_pcm = nullptr;
     float* d_taps = nullptr;
@@ -86,7 +85,7 @@ static int fail(sdrb_ctx* c, int code, const char* fmt, ...) {
 
 static void free_buffers(sdrb_ctx* c) {
     void** ptrs[] = {(void**)&c->d_geo, &c->d_in, (void**)&c->d_power, (void**)&c->d_local, (void**)&c->d_results,
-                     (void**)&c->d_fft_state, (void**)&c->d_ssb_state, (void**)&c->d_zs, (void**)&c->d_start,
+                     (void**)&c->d_fft_state, (void**)&c->d_ssb_state, (void**)&c->d_start,
                      (void**)&c->d_a48, (void**)&c->d_pcm, (void**)&c->d_taps, (void**)&c->d_tw, (void**)&c->d_sa,
                      (void**)&c->d_sb, (void**)&c->d_est_scratch};
     for (void** p : ptrs) {
@@ -223,7 +222,6 @@ static int upload_ssb(sdrb_ctx* ctx) {
     design_ssb(ctx->cfg.sampleRate, ctx->cfg.samplesPerReading, rf, ctx->cfg.soundMode, ctx->cfg.upperSideband,
                ctx->ssb, ctx->taps255);
     ctx->smax = ssb_smax(ctx->ssb);
-    ssb_homogeneous_map(ctx->ssb.rf, ctx->ssb.n, ctx->M);
     const std::vector<float> t = slot_major_taps(ctx->taps255, ctx->ssb.nTaps, ctx->ssb.decim, ctx->smax);
     if (ctx->d_taps) { cudaFree(ctx->d_taps); ctx->d_taps = nullptr; }
     CK(cudaMalloc(&ctx->d_taps, t.size() * sizeof(float)));
@@ -240,7 +238,7 @@ static int reset_state(sdrb_ctx* ctx) {
         s.maxPeakHz = static_cast<float>(ctx->cfg.centerFrequency);
     }
     CK(cudaMemcpy(ctx->d_fft_state, fs.data(), fs.size() * sizeof(FftStreamState), cudaMemcpyHostToDevice));
-    CK(cudaMemset(ctx->d_ssb_state, 0, 2 * (size_t)ctx->n_streams * sizeof(SsbStreamState)));
+    CK(cudaMemset(ctx->d_ssb_state, 0, (size_t)ctx->n_streams * sizeof(SsbStreamState)));
     ctx->rfMode = -1;
     ctx->last_blocks = 0;
     ctx->last_stages = 0;
@@ -266,11 +264,10 @@ int sdrb_configure(sdrb_ctx* ctx, const sdrb_config* cfg, int n_streams, int max
     ctx->fftPath = fft_path_for(n);
     CK(cudaMalloc(&ctx->d_geo, sizeof(EstGeometry)));
     CK(cudaMalloc(&ctx->d_fft_state, n_streams * sizeof(FftStreamState)));
-    CK(cudaMalloc(&ctx->d_ssb_state, 2 * (size_t)n_streams * sizeof(SsbStreamState)));
+    CK(cudaMalloc(&ctx->d_ssb_state, (size_t)n_streams * sizeof(SsbStreamState)));
     CK(cudaMalloc(&ctx->d_local, frames * sizeof(FrameLocal)));
     CK(cudaMalloc(&ctx->d_results, frames * sizeof(sdrb_frame_result)));
     CK(cudaMemset(ctx->d_results, 0, frames * sizeof(sdrb_frame_result)));
-    CK(cudaMalloc(&ctx->d_zs, frames * sizeof(float2)));
     CK(cudaMalloc(&ctx->d_start, frames * sizeof(float2)));
     if ((rc = upload_geometry(ctx)) != SDRB_OK) return rc;
     if ((rc = upload_ssb(ctx)) != SDRB_OK) return rc;
@@ -402,8 +399,8 @@ int sdrb_process(sdrb_ctx* ctx, const void* iq, int on_device, int n_blocks, uns
             if ((rc = upload_ssb(ctx)) != SDRB_OK) return rc;
         }
         if ((rc = ensure_ssb_buffers(ctx)) != SDRB_OK) return rc;
-        CK(launch_ssb(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->M, ctx->d_zs, ctx->d_start, ctx->d_ssb_state,
-                      ctx->d_a48, ctx->d_pcm, ctx->n_streams, n_blocks, st, &launches));
+        CK(launch_ssb(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_start, ctx->d_ssb_state, ctx->d_a48, ctx->d_pcm,
+                      ctx->n_streams, n_blocks, st, &launches));
     }
     ctx->launches += (uint64_t)launches;
     ctx->last_blocks = n_blocks;

@@ -151,23 +151,4 @@ inline std::vector<float> slot_major_taps(const float* h, int nTaps, int decim, 
     return t;
 }
 
-// n-step homogeneous map of the RF section: y[i] = (a1 - b1) y[i-1] + (a2 - b2) y[i-2].
-inline void ssb_homogeneous_map(const BiquadCoef& rf, int n, float M[4]) {
-    const double c1 = (double)rf.a1 - (double)rf.b1, c2 = (double)rf.a2 - (double)rf.b2;
-    double col[2][2];
-    for (int e = 0; e < 2; e++) {
-        double z1 = e == 0 ? 1.0 : 0.0, z2 = e == 0 ? 0.0 : 1.0;
-        for (int i = 0; i < n; i++) {
-            const double y = c1 * z1 + c2 * z2;
-            z2 = z1;
-            z1 = y;
-            if (std::fabs(z1) < 1e-300 && std::fabs(z2) < 1e-300) { z1 = z2 = 0.0; break; }
-        }
-        col[e][0] = z1;
-        col[e][1] = z2;
-    }
-    M[0] = (float)col[0][0]; M[1] = (float)col[1][0];
-    M[2] = (float)col[0][1]; M[3] = (float)col[1][1];
-}
-
 }  // namespace sdrb

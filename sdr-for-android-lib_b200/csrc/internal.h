@@ -108,12 +108,11 @@ cudaError_t estimator_prepare();
 size_t estimator_scratch_floats(const EstGeometry& g, int n_frames);
 cudaError_t launch_tracker(const FrameLocal* d_local, const EstGeometry* d_geo, FftStreamState* d_state,
                            sdrb_frame_result* d_results, int n_streams, int n_blocks, cudaStream_t st);
-// ssb.cu.  d_state holds 2 * n_streams entries (second half = shadow slots of the audio sections);
-// d_taps is the [decim][ssb_smax] slot-major tap table; M = row-major 2x2 n-step homogeneous map.
+// ssb.cu.  d_taps is the [decim][ssb_smax] slot-major tap table.
 int ssb_smax(const SsbParams& P);
-cudaError_t launch_ssb(int fmt, const void* iq, const SsbParams& P, const float* d_taps, const float* M,
-                       float2* d_zs, float2* d_start, SsbStreamState* d_state, float* d_a48, int16_t* d_pcm,
-                       int n_streams, int n_blocks, cudaStream_t st, int* launches);
+cudaError_t launch_ssb(int fmt, const void* iq, const SsbParams& P, const float* d_taps, float2* d_start,
+                       SsbStreamState* d_state, float* d_a48, int16_t* d_pcm, int n_streams, int n_blocks,
+                       cudaStream_t st, int* launches);
 // synth.cu
 cudaError_t launch_synth(int fmt, uint32_t fs, int first_stream, int n_streams, int64_t first_sample,
                          int64_t n_samples, void* d_out, const int16_t* d_sine, cudaStream_t st);

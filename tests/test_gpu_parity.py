@@ -162,7 +162,7 @@ def test_ssb_pcm_parity(sdrb, gpu_ctx, fmt, n, fs, mode, upper, B):
             if not upper:
                 assert not pcm[s, b].any()
     if total:
-        assert exact >= 0.98 * total
+        assert exact >= 0.999 * total, (exact, total)   # the state hand-off is exact: expect bit-identical PCM
         if upper and m > 10:
             assert np.abs(pcm).max() > 50
 
@@ -185,7 +185,7 @@ def test_calls_are_continuous_and_batch_independent(sdrb, gpu_ctx):
     gpu_ctx.process(np.ascontiguousarray(iq[:, 3:]), 5, both)
     r2, p2 = gpu_ctx.results().copy(), gpu_ctx.pcm().copy()
     assert np.array_equal(np.concatenate([r1, r2], 1), res_all)
-    assert np.abs(np.concatenate([p1, p2], 1).astype(int) - pcm_all.astype(int)).max() <= 1
+    assert np.array_equal(np.concatenate([p1, p2], 1), pcm_all)
     gpu_ctx.reset_state()
     gpu_ctx.load_state(blob)
     gpu_ctx.process(np.ascontiguousarray(iq[:, 3:]), 5, both)
