@@ -2,6 +2,7 @@
 // compute entry point needs a CUDA device and fails with SDRB_ERR_CUDA otherwise.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -35,6 +36,7 @@ struct sdrb_ctx {
     int n_streams = 0, max_blocks = 0;
     int rfMode = -1;            // latched by the first SSB call (static rfFilter, ssb_demod_opt.cpp:261-263)
     int fftPath = 0;
+    bool fft16k_v1 = false;
     EstGeometry geo = {};
     SsbParams ssb = {};
     float taps255[256] = {};
@@ -120,14 +122,15 @@ int sdrb_create(int device, sdrb_ctx** out) {
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
-        (e = fft16k_prepare()) != cudaSuccess || (e = estimator_prepare()) != cudaSuccess) {
+        (e = fft16k_prepare()) != cudaSuccess || (e = fft16k2_prepare()) != cudaSuccess || (e = estimator_prepare()) != cudaSuccess) {
         fail(nullptr, SDRB_ERR_CUDA, "context setup: %s", cudaGetErrorString(e));
         delete ctx;
         return SDRB_ERR_CUDA;
     }
     ctx->stream = ctx->own_stream;
     // constant tables: 16K twiddles and the synthetic source's sine table
-    const std::vector<cpx> t16 = make_f16k_tables();
+    ctx->fft16k_v1 = getenv("SDRB_FFT16K_V1") != nullptr;   // A/B switch for the first-generation kernel
+    const std::vector<cpx> t16 = ctx->fft16k_v1 ? make_f16k_tables() : make_f2_tables();
     if ((e = cudaMalloc(&ctx->d_tables16k, t16.size() * sizeof(cpx))) != cudaSuccess ||
         (e = cudaMemcpy(ctx->d_tables16k, t16.data(), t16.size() * sizeof(cpx), cudaMemcpyHostToDevice)) != cudaSuccess ||
         (e = cudaMalloc(&ctx->d_sine, SYNTH_SINE_N * sizeof(int16_t))) != cudaSuccess ||
@@ -374,7 +377,10 @@ int sdrb_process(sdrb_ctx* ctx, const void* iq, int on_device, int n_blocks, uns
         if (ctx->timing) CK(cudaEventRecord(ctx->ev0, st));
         int fft_launches = 0;
         if (ctx->fftPath == 1) {
-            CK(launch_fft16k(fmt, d_iq, ctx->d_power, ctx->d_tables16k, frames, ctx->sm_count, st));
+            if (ctx->fft16k_v1)
+                CK(launch_fft16k(fmt, d_iq, ctx->d_power, ctx->d_tables16k, frames, ctx->sm_count, st));
+            else
+                CK(launch_fft16k2(fmt, d_iq, ctx->d_power, ctx->d_tables16k, frames, ctx->sm_count, st));
             fft_launches = 1;
         } else {
             size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));

@@ -4,6 +4,7 @@
 #include <vector>
 
 #include "fft16k.cuh"
+#include "fft16k2.cuh"
 
 namespace sdrb {
 
@@ -29,6 +30,18 @@ inline std::vector<cpx> make_f16k_tables() {
         for (int s = 0; s < 64; s++) T2[k * 64 + s] = twiddle((long long)s * k, 1024);
     for (int k = 0; k < 16; k++)
         for (int d = 0; d < 4; d++) T3[k * 4 + d] = twiddle((long long)d * k, 64);
+    return t;
+}
+
+// Layout: TP | T2  (F2_TW_ELEMS entries), see fft16k2.cuh
+inline std::vector<cpx> make_f2_tables() {
+    std::vector<cpx> t(F2_TW_ELEMS);
+    cpx* TP = t.data();
+    cpx* T2 = TP + F2_TP;
+    for (int j = 0; j < 5; j++)
+        for (int r = 0; r < 512; r++) TP[j * 512 + r] = twiddle((long long)r << j, F2_N);
+    for (int kb = 0; kb < 32; kb++)
+        for (int c = 0; c < 16; c++) T2[kb * 16 + c] = twiddle((long long)c * kb, 512);
     return t;
 }
 

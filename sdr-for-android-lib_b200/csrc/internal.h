@@ -97,6 +97,10 @@ struct SsbParams {
 cudaError_t launch_fft16k(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
                           int sm_count, cudaStream_t st);
 cudaError_t fft16k_prepare();  // sets max dynamic shared memory attributes once per process
+// fft16k2.cu : second-generation 16K kernel (512 threads x 32 points, TMA-staged input)
+cudaError_t launch_fft16k2(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
+                           int sm_count, cudaStream_t st);
+cudaError_t fft16k2_prepare();
 // fft_any.cu : generic power-of-two path (N != 16384)
 cudaError_t launch_fft_generic(int fmt, const void* iq, float* power, cpx* scratch_a, cpx* scratch_b,
                                const cpx* twiddles, int n, int n_frames, cudaStream_t st, int* launches);

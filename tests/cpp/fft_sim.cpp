@@ -114,5 +114,50 @@ int main() {
                     }
                 }
     printf("bank conflicts: %d\n", conflicts);
-    return (bad || conflicts) ? 1 : 0;
+
+    // ---------------------------------------------------------------- second-generation kernel
+    int bad2 = 0, conflicts2 = 0;
+    {
+        std::vector<cpx> tw2 = make_f2_tables();
+        const cpx* TP = tw2.data();
+        const cpx* T2b = TP + F2_TP;
+        std::vector<cpx> E2(F2_E_ELEMS, mk(0, 0));
+        std::vector<float> out2(N, -1.0f);
+        for (int t = 0; t < F2_THREADS; t++) {
+            cpx v[32];
+            f2_phase1<FMT_CU8>(t, raw.data(), TP, v);
+            f2_phase1_store(t, E2.data(), v);
+        }
+        for (int t = 0; t < F2_THREADS; t++) f2_phase2(t, E2.data(), T2b);
+        for (int t = 0; t < F2_THREADS; t++) f2_phase3(t, E2.data(), out2.data());
+        double maxrel2 = 0;
+        for (int k = 0; k < N; k++) {
+            double p = Xr[k] * Xr[k] + Xi[k] * Xi[k];
+            double g = out2[(k + N / 2) % N];
+            double err = fabs(g - p);
+            double tol = 1e-5 * p + 2.0 * sqrt(p) * 3e-7 * sqrt(total) + 1e-9 * total / N;
+            if (err > tol) { if (bad2 < 10) printf("v2 bin %d ref %.6g got %.6g\n", k, p, g); bad2++; }
+            if (p > 1e-3 * total / N) maxrel2 = fmax(maxrel2, err / p);
+        }
+        printf("fft16k2 sim: bad=%d maxrel=%.3g\n", bad2, maxrel2);
+        // bank audit: 8-byte accesses, each half-warp must cover 16 distinct 8-byte bank pairs
+        auto audit2 = [&](auto addr_of, int iters, const char* name) {
+            for (int w = 0; w < F2_THREADS / 32; w++)
+                for (int j = 0; j < iters; j++)
+                    for (int h = 0; h < 2; h++) {
+                        int seen[16] = {0};
+                        for (int l = 0; l < 16; l++) {
+                            int t = w * 32 + h * 16 + l;
+                            int bank = addr_of(t, j) & 15;
+                            if (seen[bank]++) { conflicts2++; if (conflicts2 < 5) printf("conflict %s w%d j%d\n", name, w, j); }
+                        }
+                    }
+        };
+        audit2([](int t, int k) { return k * F2_PITCH + t; }, 32, "v2 p1 store");
+        audit2([](int t, int b) { return (t >> 4) * F2_PITCH + b * 16 + (t & 15); }, 32, "v2 p2 ld/st");
+        audit2([](int t, int c) { return (t & 31) * F2_PITCH + (t >> 5) * 16 + c; }, 16, "v2 p3 ld h0");
+        audit2([](int t, int c) { return ((t + 512) & 31) * F2_PITCH + ((t + 512) >> 5) * 16 + c; }, 16, "v2 p3 ld h1");
+        printf("v2 bank conflicts: %d\n", conflicts2);
+    }
+    return (bad || conflicts || bad2 || conflicts2) ? 1 : 0;
 }
