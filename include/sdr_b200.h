@@ -147,6 +147,12 @@ int  sdrb_plan_config(const sdrb_config* cfg, sdrb_plan* out);
  * stages: SDRB_STAGE_FFT | SDRB_STAGE_SSB.  Asynchronous on the context's stream. */
 int  sdrb_process(sdrb_ctx* ctx, const void* iq, int on_device, int n_blocks, unsigned stages);
 int  sdrb_sync(sdrb_ctx* ctx);
+/* The same call host-to-host, pipelined: iq_host in, every payload of soapyCallback back out
+ * (records = the scalar callbacks, power = ([F)V, pcm = ([S)V; any output may be NULL and then
+ * stays on the device).  Streams are cut into chunks whose H2D copy, kernels and D2H copies
+ * overlap on three CUDA streams; pass pinned host memory for full overlap.  Synchronous. */
+int  sdrb_process_host(sdrb_ctx* ctx, const void* iq_host, int n_blocks, unsigned stages,
+                       sdrb_frame_result* results_out, float* power_out, int16_t* pcm_out);
 
 /* Results of the last sdrb_process, [n_streams][n_blocks] records (synchronises). */
 int  sdrb_get_results(sdrb_ctx* ctx, sdrb_frame_result* host_out, size_t capacity_records);

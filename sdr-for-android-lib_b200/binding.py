@@ -70,6 +70,7 @@ EXPORTS = {
     "sdrb_plan_config": (C.c_int, [C.POINTER(Config), C.POINTER(Plan)]),
     "sdrb_process": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint]),
     "sdrb_sync": (C.c_int, [C.c_void_p]),
+    "sdrb_process_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p]),
     "sdrb_get_results": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "sdrb_results_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "sdrb_power_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
@@ -184,6 +185,12 @@ class Context:
         if on_device is None:
             on_device = bool(is_cuda)
         _check(lib.sdrb_process(self._h, C.c_void_p(addr), 1 if on_device else 0, n_blocks, stages), self._h)
+        self.last_blocks = n_blocks
+
+    def process_host(self, iq, n_blocks, stages=STAGE_FFT | STAGE_SSB, results=None, power=None, pcm=None):
+        """Pipelined host-to-host call; outputs are preallocated numpy arrays / pinned tensors or None."""
+        ptr = lambda x: C.c_void_p(_ptr(x)[0]) if x is not None else C.c_void_p(0)
+        _check(lib.sdrb_process_host(self._h, ptr(iq), n_blocks, stages, ptr(results), ptr(power), ptr(pcm)), self._h)
         self.last_blocks = n_blocks
 
     def sync(self):

@@ -23,6 +23,7 @@ struct StateBlobHeader {
     uint32_t magic, version;
     int32_t n_streams, rfMode;
 };
+constexpr int kMaxChunks = 8;
 constexpr uint32_t kBlobMagic = 0x53445242u;  // "SDRB"
 }  // namespace
 
@@ -66,6 +67,9 @@ struct sdrb_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool ev_valid = false;
     int last_fft_launches = 0;
+    // host-to-host pipeline (sdrb_process_host)
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t ev_in[8] = {}, ev_done[8] = {};
 };
 
 static int fail(sdrb_ctx* c, int code, const char* fmt, ...) {
@@ -152,6 +156,12 @@ int sdrb_destroy(sdrb_ctx* ctx) {
     if (ctx->d_sine) cudaFree(ctx->d_sine);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->s_in) cudaStreamDestroy(ctx->s_in);
+    if (ctx->s_out) cudaStreamDestroy(ctx->s_out);
+    for (int i = 0; i < kMaxChunks; i++) {
+        if (ctx->ev_in[i]) cudaEventDestroy(ctx->ev_in[i]);
+        if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
+    }
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
     return SDRB_OK;
@@ -345,73 +355,151 @@ static int ensure_ssb_buffers(sdrb_ctx* ctx) {
 
 extern "C" {
 
-int sdrb_process(sdrb_ctx* ctx, const void* iq, int on_device, int n_blocks, unsigned stages) {
+static int validate_process(sdrb_ctx* ctx, const void* iq, int n_blocks, unsigned stages) {
     if (!ctx || !ctx->configured) return fail(ctx, SDRB_ERR_STATE, "sdrb_process before sdrb_configure");
     if (!iq) return fail(ctx, SDRB_ERR_ARG, "iq is NULL");
     if (n_blocks < 1 || n_blocks > ctx->max_blocks)
         return fail(ctx, SDRB_ERR_ARG, "n_blocks %d outside [1, %d]", n_blocks, ctx->max_blocks);
     if ((stages & ~(SDRB_STAGE_FFT | SDRB_STAGE_SSB)) || stages == 0)
         return fail(ctx, SDRB_ERR_ARG, "stages must be a combination of SDRB_STAGE_FFT | SDRB_STAGE_SSB");
-    const int n = ctx->cfg.samplesPerReading, fmt = ctx->cfg.inputFormat;
-    const size_t bps = sdrb_format_bytes(fmt);
+    const int n = ctx->cfg.samplesPerReading;
+    const size_t bps = sdrb_format_bytes(ctx->cfg.inputFormat);
     if ((stages & SDRB_STAGE_FFT) && (!is_pow2(n) || n < 2 || n > (1 << 24)))
         return fail(ctx, SDRB_ERR_UNSUPPORTED, "FFT length %d: only powers of two in [2, 2^24] are built", n);
     if ((stages & SDRB_STAGE_SSB) && ((size_t)n * bps) % 64 != 0)
         return fail(ctx, SDRB_ERR_UNSUPPORTED, "SSB block of %d samples: block bytes must be a multiple of 64", n);
-    CK(cudaSetDevice(ctx->device));
-    const int frames = ctx->n_streams * n_blocks;
-    const size_t in_bytes = (size_t)frames * n * bps;
-    cudaStream_t st = ctx->stream;
     int rc;
-
-    const void* d_iq = iq;
-    if (!on_device) {
-        if (!ctx->d_in) CK(cudaMalloc(&ctx->d_in, (size_t)ctx->n_streams * ctx->max_blocks * n * bps));
-        CK(cudaMemcpyAsync(ctx->d_in, iq, in_bytes, cudaMemcpyHostToDevice, st));
-        d_iq = ctx->d_in;
-    }
-    int launches = 0;
-    ctx->ev_valid = false;
-    if (stages & SDRB_STAGE_FFT) {
-        if ((rc = ensure_fft_buffers(ctx)) != SDRB_OK) return rc;
-        if (ctx->timing) CK(cudaEventRecord(ctx->ev0, st));
-        int fft_launches = 0;
-        if (ctx->fftPath == 1) {
-            if (ctx->fft16k_v1)
-                CK(launch_fft16k(fmt, d_iq, ctx->d_power, ctx->d_tables16k, frames, ctx->sm_count, st));
-            else
-                CK(launch_fft16k2(fmt, d_iq, ctx->d_power, ctx->d_tables16k, frames, ctx->sm_count, st));
-            fft_launches = 1;
-        } else {
-            size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
-            if (chunk < 1) chunk = 1;
-            for (size_t f0 = 0; f0 < (size_t)frames; f0 += chunk) {
-                const int nf = (int)((size_t)frames - f0 < chunk ? (size_t)frames - f0 : chunk);
-                CK(launch_fft_generic(fmt, static_cast<const unsigned char*>(d_iq) + f0 * n * bps,
-                                      ctx->d_power + f0 * n, ctx->d_sa, ctx->d_sb, ctx->d_tw, n, nf, st,
-                                      &fft_launches));
-            }
-        }
-        if (ctx->timing) { CK(cudaEventRecord(ctx->ev1, st)); ctx->ev_valid = true; }
-        ctx->last_fft_launches = fft_launches;
-        launches += fft_launches;
-        CK(launch_estimator(ctx->d_power, ctx->d_geo, ctx->geo, ctx->d_local, ctx->d_est_scratch, frames, st));
-        CK(launch_tracker(ctx->d_local, ctx->d_geo, ctx->d_fft_state, ctx->d_results, ctx->n_streams, n_blocks, st));
-        launches += 2;
-    }
+    CK(cudaSetDevice(ctx->device));
+    if ((stages & SDRB_STAGE_FFT) && (rc = ensure_fft_buffers(ctx)) != SDRB_OK) return rc;
     if (stages & SDRB_STAGE_SSB) {
         if (ctx->rfMode < 0) {  // first SSB block latches the RF low-pass design
             ctx->rfMode = ctx->cfg.soundMode;
             if ((rc = upload_ssb(ctx)) != SDRB_OK) return rc;
         }
         if ((rc = ensure_ssb_buffers(ctx)) != SDRB_OK) return rc;
-        CK(launch_ssb(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_start, ctx->d_ssb_state, ctx->d_a48, ctx->d_pcm,
-                      ctx->n_streams, n_blocks, st, &launches));
+    }
+    return SDRB_OK;
+}
+
+// Every kernel of the path for streams [s0, s0 + ns) of a call of n_blocks readings, on stream st.
+// d_iq points at stream s0's first sample; device outputs are laid out [n_streams][n_blocks][...].
+static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_blocks, unsigned stages,
+                       cudaStream_t st, bool time_fft) {
+    const int n = ctx->cfg.samplesPerReading, fmt = ctx->cfg.inputFormat;
+    const size_t bps = sdrb_format_bytes(fmt);
+    const int frames = ns * n_blocks;
+    const size_t f0s = (size_t)s0 * n_blocks;   // first frame of the range
+    int launches = 0;
+    if (stages & SDRB_STAGE_FFT) {
+        float* power = ctx->d_power + f0s * n;
+        if (time_fft) CK(cudaEventRecord(ctx->ev0, st));
+        int fft_launches = 0;
+        if (ctx->fftPath == 1) {
+            if (ctx->fft16k_v1)
+                CK(launch_fft16k(fmt, d_iq, power, ctx->d_tables16k, frames, ctx->sm_count, st));
+            else
+                CK(launch_fft16k2(fmt, d_iq, power, ctx->d_tables16k, frames, ctx->sm_count, st));
+            fft_launches = 1;
+        } else {
+            size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
+            if (chunk < 1) chunk = 1;
+            for (size_t f0 = 0; f0 < (size_t)frames; f0 += chunk) {
+                const int nf = (int)((size_t)frames - f0 < chunk ? (size_t)frames - f0 : chunk);
+                CK(launch_fft_generic(fmt, static_cast<const unsigned char*>(d_iq) + f0 * n * bps, power + f0 * n,
+                                      ctx->d_sa, ctx->d_sb, ctx->d_tw, n, nf, st, &fft_launches));
+            }
+        }
+        if (time_fft) { CK(cudaEventRecord(ctx->ev1, st)); ctx->ev_valid = true; }
+        ctx->last_fft_launches = fft_launches;
+        launches += fft_launches;
+        float* scratch = ctx->d_est_scratch ? ctx->d_est_scratch + f0s * ctx->geo.totalBins : nullptr;
+        CK(launch_estimator(power, ctx->d_geo, ctx->geo, ctx->d_local + f0s, scratch, frames, st));
+        CK(launch_tracker(ctx->d_local + f0s, ctx->d_geo, ctx->d_fft_state + s0, ctx->d_results + f0s, ns, n_blocks, st));
+        launches += 2;
+    }
+    if (stages & SDRB_STAGE_SSB) {
+        const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 0;
+        CK(launch_ssb(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_start + f0s, ctx->d_ssb_state + s0,
+                      ctx->d_a48 + f0s * m, ctx->d_pcm + f0s * m, ns, n_blocks, st, &launches));
     }
     ctx->launches += (uint64_t)launches;
+    return SDRB_OK;
+}
+
+int sdrb_process(sdrb_ctx* ctx, const void* iq, int on_device, int n_blocks, unsigned stages) {
+    int rc = validate_process(ctx, iq, n_blocks, stages);
+    if (rc != SDRB_OK) return rc;
+    const size_t in_bytes = (size_t)ctx->n_streams * n_blocks * ctx->cfg.samplesPerReading *
+                            sdrb_format_bytes(ctx->cfg.inputFormat);
+    cudaStream_t st = ctx->stream;
+    const void* d_iq = iq;
+    if (!on_device) {
+        if (!ctx->d_in) CK(cudaMalloc(&ctx->d_in, (size_t)ctx->n_streams * ctx->max_blocks *
+                                                   ctx->cfg.samplesPerReading * sdrb_format_bytes(ctx->cfg.inputFormat)));
+        CK(cudaMemcpyAsync(ctx->d_in, iq, in_bytes, cudaMemcpyHostToDevice, st));
+        d_iq = ctx->d_in;
+    }
+    ctx->ev_valid = false;
+    if ((rc = run_streams(ctx, d_iq, 0, ctx->n_streams, n_blocks, stages, st, ctx->timing)) != SDRB_OK) return rc;
     ctx->last_blocks = n_blocks;
     ctx->last_stages |= stages;
     if (!on_device) CK(cudaStreamSynchronize(st));  // the host buffer is only borrowed for the call
+    return SDRB_OK;
+}
+
+// Host-to-host call: what soapyCallback does for every reading (copy in, both processors, all
+// payloads back out: src/sdr-bridge-java-soapy.cpp:441-466, ssb_processor.cpp:103-107), for a
+// whole batch.  Streams are cut into chunks; the H2D copy of chunk c+1, the kernels of chunk c
+// and the D2H copies of chunk c-1 run concurrently on three CUDA streams (full-duplex PCIe).
+// Any of results_out / power_out / pcm_out may be NULL (that payload then stays on the device).
+int sdrb_process_host(sdrb_ctx* ctx, const void* iq_host, int n_blocks, unsigned stages,
+                      sdrb_frame_result* results_out, float* power_out, int16_t* pcm_out) {
+    int rc = validate_process(ctx, iq_host, n_blocks, stages);
+    if (rc != SDRB_OK) return rc;
+    const int n = ctx->cfg.samplesPerReading, S = ctx->n_streams;
+    const size_t bps = sdrb_format_bytes(ctx->cfg.inputFormat);
+    if (!ctx->d_in) CK(cudaMalloc(&ctx->d_in, (size_t)S * ctx->max_blocks * n * bps));
+    if (!ctx->s_in) {
+        CK(cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking));
+        for (int i = 0; i < kMaxChunks; i++) {
+            CK(cudaEventCreateWithFlags(&ctx->ev_in[i], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming));
+        }
+    }
+    const int chunks = S < kMaxChunks ? S : kMaxChunks;
+    const size_t stream_in = (size_t)n_blocks * n * bps;          // bytes of one stream's IQ
+    const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 0;
+    cudaStream_t st = ctx->stream;
+    CK(cudaStreamSynchronize(st));                                  // earlier work on the compute stream
+    ctx->ev_valid = false;
+    for (int c = 0; c < chunks; c++) {
+        const int s0 = (int)((long long)S * c / chunks), s1 = (int)((long long)S * (c + 1) / chunks);
+        const int ns = s1 - s0;
+        if (ns <= 0) continue;
+        const size_t f0 = (size_t)s0 * n_blocks, nf = (size_t)ns * n_blocks;
+        unsigned char* d_chunk = static_cast<unsigned char*>(ctx->d_in) + s0 * stream_in;
+        CK(cudaMemcpyAsync(d_chunk, static_cast<const unsigned char*>(iq_host) + s0 * stream_in, ns * stream_in,
+                           cudaMemcpyHostToDevice, ctx->s_in));
+        CK(cudaEventRecord(ctx->ev_in[c], ctx->s_in));
+        CK(cudaStreamWaitEvent(st, ctx->ev_in[c], 0));
+        if ((rc = run_streams(ctx, d_chunk, s0, ns, n_blocks, stages, st, false)) != SDRB_OK) return rc;
+        CK(cudaEventRecord(ctx->ev_done[c], st));
+        CK(cudaStreamWaitEvent(ctx->s_out, ctx->ev_done[c], 0));
+        if ((stages & SDRB_STAGE_FFT) && results_out)
+            CK(cudaMemcpyAsync(results_out + f0, ctx->d_results + f0, nf * sizeof(sdrb_frame_result),
+                               cudaMemcpyDeviceToHost, ctx->s_out));
+        if ((stages & SDRB_STAGE_FFT) && power_out)
+            CK(cudaMemcpyAsync(power_out + f0 * n, ctx->d_power + f0 * n, nf * n * sizeof(float),
+                               cudaMemcpyDeviceToHost, ctx->s_out));
+        if ((stages & SDRB_STAGE_SSB) && pcm_out && m)
+            CK(cudaMemcpyAsync(pcm_out + f0 * m, ctx->d_pcm + f0 * m, nf * m * sizeof(int16_t),
+                               cudaMemcpyDeviceToHost, ctx->s_out));
+    }
+    ctx->last_blocks = n_blocks;
+    ctx->last_stages |= stages;
+    CK(cudaStreamSynchronize(ctx->s_out));
+    CK(cudaStreamSynchronize(st));
     return SDRB_OK;
 }
 

@@ -1,7 +1,7 @@
 // estimator.cu — evaluateSignalStrength on the GPU (src/dsp/fft_process.cpp:122-378).
 //
 // Two kernels:
-//   k_estimator : one CTA per frame, everything that is frame-local (focus band, reference
+//   k_estimator : one WARP per frame, everything that is frame-local (focus band, reference
 //                 windows, sort, MAD sigmas, pooled per-bin noise, Gumbel / best-1 kHz SNR).
 //   k_tracker   : one thread per stream, the sequential part that carries state from frame to
 //                 frame (frequency tracking :333-361, detection flag :365-378, hold-over of
@@ -15,7 +15,7 @@
 
 namespace sdrb {
 
-constexpr int EST_THREADS = 128;
+constexpr int EST_MAX_WARPS = 4;   // frames per CTA (one warp each)
 constexpr int EST_MAX_SMEM_FLOATS = 48 * 1024;  // 192 KiB of staged bins; above that: global scratch
 
 __device__ __forceinline__ float db10(float p) {
@@ -36,6 +36,7 @@ struct BandStat {
 __device__ void band_scan(const float* p, int len, int W, float maxInit, BandStat& r) {
     float sum = 0.0f, maxP = maxInit;
     int maxIdx = 0;
+#pragma unroll 8
     for (int i = 0; i < len; i++) {
         const float v = p[i];
         sum = __fadd_rn(sum, v);
@@ -47,6 +48,7 @@ __device__ void band_scan(const float* p, int len, int W, float maxInit, BandSta
     for (int i = 0; i < W; i++) run = __fadd_rn(run, p[i]);
     float best = run;
     int bestStart = 0;
+#pragma unroll 4
     for (int s = 1; s + W - 1 < len; s++) {
         run = __fadd_rn(run, __fsub_rn(p[s + W - 1], p[s - 1]));
         if (run > best) { best = run; bestStart = s; }
@@ -79,30 +81,38 @@ __device__ __forceinline__ int pool_addr(const PoolMap& pm, int i) {
     return pm.base[j] + (i - pm.cum[j]);
 }
 
-__global__ void __launch_bounds__(EST_THREADS)
+// Per-warp working set: one warp owns one frame, so the only block-wide barrier is the one that
+// publishes the geometry; everything else is __syncwarp.
+struct EstWarp {
+    BandStat st[11];
+    PoolMap pm;
+    int hist[256];
+    float winMeanDb[10], winBest1kDb[10];
+    float focusDb[2];          // absPeakDb candidate, signalPowerDb
+    FrameLocal out;
+    float perBinMean;
+};
+
+template <bool USE_SMEM>
+__global__ void __launch_bounds__(EST_MAX_WARPS * 32)
 k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo_p, FrameLocal* __restrict__ local,
-            float* __restrict__ gscratch, int use_smem) {
+            float* __restrict__ gscratch, int n_frames) {
     extern __shared__ float stage_smem[];
     __shared__ EstGeometry g;
-    __shared__ BandStat st[11];
-    __shared__ PoolMap pm;
-    __shared__ int hist[256];
-    __shared__ unsigned sh_prefix;
-    __shared__ int sh_k;
-    __shared__ float sh_perBinMean;
-    __shared__ FrameLocal out;
-    __shared__ float winMeanDb[10], winBest1kDb[10];
+    __shared__ EstWarp ws[EST_MAX_WARPS];
 
-    const int tid = threadIdx.x;
-    const size_t frame = blockIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     {
         const int* src = reinterpret_cast<const int*>(geo_p);
         int* dst = reinterpret_cast<int*>(&g);
-        for (int i = tid; i < (int)(sizeof(EstGeometry) / 4); i += EST_THREADS) dst[i] = src[i];
+        for (int i = threadIdx.x; i < (int)(sizeof(EstGeometry) / 4); i += blockDim.x) dst[i] = src[i];
     }
     __syncthreads();
+    const size_t frame = (size_t)blockIdx.x * nwarps + warp;
+    if (frame >= (size_t)n_frames) return;
+    EstWarp& W = ws[warp];
     if (g.focusLen <= 0) {  // :139 early return, the frame leaves every output untouched
-        if (tid == 0) {
+        if (lane == 0) {
             FrameLocal z = {};
             z.peakBin = -1;
             z.best1kStart = -1;
@@ -111,129 +121,151 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
         return;
     }
     const float* P = power + frame * (size_t)g.n;
-    float* stage = use_smem ? stage_smem : gscratch + frame * (size_t)g.totalBins;
+    float* stage = USE_SMEM ? stage_smem + (size_t)warp * g.totalBins : gscratch + frame * (size_t)g.totalBins;
 
     for (int seg = 0; seg <= g.nWin; seg++) {
         const int lo = seg == 0 ? g.focusLo : g.winLo[seg - 1];
         const int len = g.segOff[seg + 1] - g.segOff[seg];
         float* d = stage + g.segOff[seg];
-        for (int i = tid; i < len; i += EST_THREADS) d[i] = P[lo + i];
+        for (int i = lane; i < len; i += 32) d[i] = P[lo + i];
     }
-    __syncthreads();
-    if (tid <= g.nWin) {
-        const int len = g.segOff[tid + 1] - g.segOff[tid];
-        band_scan(stage + g.segOff[tid], len, g.winBins1k, tid == 0 ? -1.0f : 0.0f, st[tid]);
-    }
-    __syncthreads();
-
+    __syncwarp();
     const bool valid = g.nWin >= 2;  // :218
-    if (tid == 0) {
+    if (lane <= g.nWin) {
+        const int len = g.segOff[lane + 1] - g.segOff[lane];
+        BandStat bs;
+        band_scan(stage + g.segOff[lane], len, g.winBins1k, lane == 0 ? -1.0f : 0.0f, bs);
+        W.st[lane] = bs;
+        // the dB figures of this band, one lane per band (:149-155, :203-213)
+        if (lane == 0) {
+            W.focusDb[0] = db10(bs.maxP);
+            W.focusDb[1] = db10(__fdiv_rn(bs.sum, (float)g.focusLen));
+        } else if (valid) {
+            W.winMeanDb[lane - 1] = db10(__fdiv_rn(bs.sum, (float)len));
+            const float b1k = len < g.winBins1k ? __fdiv_rn(bs.sum, (float)len)
+                                                : __fdiv_rn(bs.bestRun, (float)g.winBins1k);
+            W.winBest1kDb[lane - 1] = db10(b1k);
+        }
+    }
+    __syncwarp();
+
+    if (lane == 0) {
         FrameLocal o = {};
         // ---- :142-155 focus band
-        const float dbMax = db10(st[0].maxP);
-        if (dbMax > -130.0f) { o.absPeakDb = dbMax; o.peakBin = g.focusLo + st[0].maxIdx; }
+        const float dbMax = W.focusDb[0];
+        if (dbMax > -130.0f) { o.absPeakDb = dbMax; o.peakBin = g.focusLo + W.st[0].maxIdx; }
         else { o.absPeakDb = -130.0f; o.peakBin = g.focusLo; }
-        o.signalPowerDb = db10(__fdiv_rn(st[0].sum, (float)g.focusLen));
+        o.signalPowerDb = W.focusDb[1];
         o.valid = valid ? 1 : 0;
         o.best1kStart = -1;
-        pm.nSeg = 0;
-        pm.cum[0] = 0;
+        W.pm.nSeg = 0;
+        W.pm.cum[0] = 0;
         if (valid) {
-            // ---- :203-213 per-window dB figures
-            int order[10];
-            for (int w = 0; w < g.nWin; w++) {
-                const int len = g.segOff[w + 2] - g.segOff[w + 1];
-                winMeanDb[w] = db10(__fdiv_rn(st[w + 1].sum, (float)len));
-                const float b1k = len < g.winBins1k ? __fdiv_rn(st[w + 1].sum, (float)len)
-                                                    : __fdiv_rn(st[w + 1].bestRun, (float)g.winBins1k);
-                winBest1kDb[w] = db10(b1k);
-                order[w] = w;
-            }
             // ---- :228-229 std::sort by meanDb (<= 10 elements: insertion sort, stable)
+            int order[10];
+            for (int w = 0; w < g.nWin; w++) order[w] = w;
             for (int i = 1; i < g.nWin; i++) {
                 const int w = order[i];
                 int j = i - 1;
-                while (j >= 0 && winMeanDb[w] < winMeanDb[order[j]]) { order[j + 1] = order[j]; j--; }
+                while (j >= 0 && W.winMeanDb[w] < W.winMeanDb[order[j]]) { order[j + 1] = order[j]; j--; }
                 order[j + 1] = w;
             }
             const int nb = g.nBottom;
             // ---- :235-247 mean-energy SNR
             float x[10];
             float mean = 0.0f;
-            for (int i = 0; i < nb; i++) { x[i] = winMeanDb[order[i]]; mean = __fadd_rn(mean, x[i]); }
+            for (int i = 0; i < nb; i++) { x[i] = W.winMeanDb[order[i]]; mean = __fadd_rn(mean, x[i]); }
             mean = __fdiv_rn(mean, (float)nb);
             const float sigma = fmaxf(__fmul_rn(1.4816f, small_mad(x, nb, mean)), 0.5f);
             o.meanSnrDb = __fsub_rn(o.signalPowerDb, mean);
             o.meanSnrSigma = __fdiv_rn(o.meanSnrDb, sigma);
             // ---- :292-300 best-1 kHz reference statistics (sigma1k needs sigmaBin, finished below)
             float mean1k = 0.0f;
-            for (int i = 0; i < nb; i++) { x[i] = winBest1kDb[order[i]]; mean1k = __fadd_rn(mean1k, x[i]); }
+            for (int i = 0; i < nb; i++) { x[i] = W.winBest1kDb[order[i]]; mean1k = __fadd_rn(mean1k, x[i]); }
             mean1k = __fdiv_rn(mean1k, (float)nb);
             o.best1kHzSnrDb = mean1k;                                      // parked until the final step
             o.best1kHzSnrSigma = __fmul_rn(1.4816f, small_mad(x, nb, mean1k));
             // pooled-bin map (:252-257)
-            pm.nSeg = nb < 4 ? nb : 4;
-            for (int j = 0; j < pm.nSeg; j++) {
+            W.pm.nSeg = nb < 4 ? nb : 4;
+            for (int j = 0; j < W.pm.nSeg; j++) {
                 const int w = order[j];
-                pm.base[j] = g.segOff[w + 1];
-                pm.cum[j + 1] = pm.cum[j] + (g.segOff[w + 2] - g.segOff[w + 1]);
+                W.pm.base[j] = g.segOff[w + 1];
+                W.pm.cum[j + 1] = W.pm.cum[j] + (g.segOff[w + 2] - g.segOff[w + 1]);
             }
         }
-        out = o;
+        W.out = o;
     }
-    __syncthreads();
+    __syncwarp();
 
     if (valid) {
+        const PoolMap pm = W.pm;
         const int pooledN = pm.cum[pm.nSeg];
         // per-bin dB of the quiet windows, in place (:255-256)
-        for (int i = tid; i < pooledN; i += EST_THREADS) {
+        for (int i = lane; i < pooledN; i += 32) {
             const int a = pool_addr(pm, i);
             stage[a] = db10(stage[a]);
         }
-        __syncthreads();
-        if (tid == 0) {  // :261-262 sequential mean
+        __syncwarp();
+        if (lane == 0) {  // :261-262 sequential mean
             float s = 0.0f;
             for (int j = 0; j < pm.nSeg; j++) {
                 const float* d = stage + pm.base[j];
                 const int len = pm.cum[j + 1] - pm.cum[j];
+#pragma unroll 8
                 for (int i = 0; i < len; i++) s = __fadd_rn(s, d[i]);
             }
-            sh_perBinMean = __fdiv_rn(s, (float)pooledN);
+            W.perBinMean = __fdiv_rn(s, (float)pooledN);
         }
-        __syncthreads();
-        const float perBinMean = sh_perBinMean;
-        for (int i = tid; i < pooledN; i += EST_THREADS) {  // :265-266
+        __syncwarp();
+        const float perBinMean = W.perBinMean;
+        for (int i = lane; i < pooledN; i += 32) {  // :265-266
             const int a = pool_addr(pm, i);
             stage[a] = fabsf(__fsub_rn(stage[a], perBinMean));
         }
-        __syncthreads();
-        // :267-268 median of the gaps: radix select over the mapped array
+        __syncwarp();
+        // :267-268 median of the gaps: 4-pass radix select on the bit pattern; each lane owns 8 of
+        // the 256 histogram bins and the crossing bin is found with a warp scan
         unsigned prefix = 0, mask = 0;
         int k = pooledN / 2;
         for (int shift = 24; shift >= 0; shift -= 8) {
-            for (int i = tid; i < 256; i += EST_THREADS) hist[i] = 0;
-            __syncthreads();
-            for (int i = tid; i < pooledN; i += EST_THREADS) {
+            for (int i = lane; i < 256; i += 32) W.hist[i] = 0;
+            __syncwarp();
+            for (int i = lane; i < pooledN; i += 32) {
                 const unsigned b = __float_as_uint(stage[pool_addr(pm, i)]);
-                if ((b & mask) == prefix) atomicAdd(&hist[(b >> shift) & 255u], 1);
+                if ((b & mask) == prefix) atomicAdd(&W.hist[(b >> shift) & 255u], 1);
             }
-            __syncthreads();
-            if (tid == 0) {
-                int acc = 0, d = 0;
-                for (; d < 255; d++) {
-                    if (acc + hist[d] > k) break;
-                    acc += hist[d];
+            __syncwarp();
+            int mine = 0;
+#pragma unroll
+            for (int j = 0; j < 8; j++) mine += W.hist[8 * lane + j];
+            int incl = mine;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += v;
+            }
+            const unsigned cross = __ballot_sync(0xffffffffu, incl > k);
+            const int L = cross ? __ffs(cross) - 1 : 31;
+            int digit = 0, acc = 0;
+            if (lane == L) {
+                acc = incl - mine;
+                digit = 8 * L;
+                for (int j = 0; j < 7; j++) {
+                    const int h = W.hist[8 * L + j];
+                    if (acc + h > k) break;
+                    acc += h;
+                    digit++;
                 }
-                sh_prefix = prefix | ((unsigned)d << shift);
-                sh_k = k - acc;
             }
-            __syncthreads();
-            prefix = sh_prefix;
-            k = sh_k;
+            digit = __shfl_sync(0xffffffffu, digit, L);
+            acc = __shfl_sync(0xffffffffu, acc, L);
+            prefix |= (unsigned)digit << shift;
+            k -= acc;
             mask |= 255u << shift;
+            __syncwarp();
         }
-        if (tid == 0) {
-            FrameLocal o = out;
+        if (lane == 0) {
+            FrameLocal o = W.out;
             const float sigmaBin = fmaxf(__fmul_rn(1.4816f, __uint_as_float(prefix)), 1.0f);
             o.perBinMean = perBinMean;
             o.peakAboveNoiseMeanDb = __fsub_rn(o.absPeakDb, perBinMean);                     // :274
@@ -246,22 +278,22 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
             const float mean1k = o.best1kHzSnrDb;
             const float sigmaFloor1k = __fdiv_rn(sigmaBin, g.sqrtWin1k);
             const float sigma1k = fmaxf(fmaxf(o.best1kHzSnrSigma, sigmaFloor1k), 0.5f);
-            const float fb = g.focusLen < g.winBins1k ? __fdiv_rn(st[0].sum, (float)g.focusLen)
-                                                      : __fdiv_rn(st[0].bestRun, (float)g.winBins1k);
+            const float fb = g.focusLen < g.winBins1k ? __fdiv_rn(W.st[0].sum, (float)g.focusLen)
+                                                      : __fdiv_rn(W.st[0].bestRun, (float)g.winBins1k);
             if (fb > 0.0f) {
                 o.best1kHzSnrDb = __fsub_rn(db10(fb), mean1k);
                 o.best1kHzSnrSigma = __fdiv_rn(o.best1kHzSnrDb, sigma1k);
-                o.best1kStart = g.focusLo + st[0].bestStart;
+                o.best1kStart = g.focusLo + W.st[0].bestStart;
             } else {
                 o.best1kHzSnrDb = 0.0f;
                 o.best1kHzSnrSigma = 0.0f;
                 o.best1kStart = -1;
             }
-            out = o;
+            W.out = o;
         }
     }
-    __syncthreads();
-    if (tid == 0) local[frame] = out;
+    __syncwarp();
+    if (lane == 0) local[frame] = W.out;
 }
 
 // Frame clock (SURVEY.md 8a note T): t = (frame + 1) * n / fs in ns, integer arithmetic.
@@ -356,7 +388,7 @@ k_tracker(const FrameLocal* __restrict__ local, const EstGeometry* __restrict__ 
 }
 
 cudaError_t estimator_prepare() {
-    return cudaFuncSetAttribute(k_estimator, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    return cudaFuncSetAttribute(k_estimator<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 EST_MAX_SMEM_FLOATS * (int)sizeof(float));
 }
 
@@ -367,10 +399,18 @@ size_t estimator_scratch_floats(const EstGeometry& g, int n_frames) {
 cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, const EstGeometry& h_geo,
                              FrameLocal* d_local, float* d_stage_scratch, int n_frames, cudaStream_t st) {
     if (n_frames <= 0) return cudaSuccess;
-    const int use_smem = h_geo.totalBins <= EST_MAX_SMEM_FLOATS ? 1 : 0;
+    const int bins = h_geo.totalBins > 0 ? h_geo.totalBins : 1;
+    const int use_smem = bins <= EST_MAX_SMEM_FLOATS ? 1 : 0;
     if (!use_smem && !d_stage_scratch) return cudaErrorInvalidValue;
-    const size_t smem = use_smem ? (size_t)(h_geo.totalBins > 0 ? h_geo.totalBins : 1) * sizeof(float) : 0;
-    k_estimator<<<n_frames, EST_THREADS, smem, st>>>(power, d_geo, d_local, d_stage_scratch, use_smem);
+    // frames (warps) per CTA: as many as fit in ~48 KiB of staging, 1..EST_MAX_WARPS
+    int warps = use_smem ? (12 * 1024) / bins : EST_MAX_WARPS;
+    warps = warps < 1 ? 1 : (warps > EST_MAX_WARPS ? EST_MAX_WARPS : warps);
+    const size_t smem = use_smem ? (size_t)bins * warps * sizeof(float) : 0;
+    const int grid = (n_frames + warps - 1) / warps;
+    if (use_smem)
+        k_estimator<true><<<grid, warps * 32, smem, st>>>(power, d_geo, d_local, d_stage_scratch, n_frames);
+    else
+        k_estimator<false><<<grid, warps * 32, 0, st>>>(power, d_geo, d_local, d_stage_scratch, n_frames);
     return cudaGetLastError();
 }
 

@@ -212,6 +212,26 @@ def test_device_input_equals_host_input(sdrb, gpu_ctx):
     assert np.array_equal(gpu_ctx.results(), r_h) and np.array_equal(gpu_ctx.pcm(), p_h)
 
 
+def test_pipelined_host_call_equals_plain_call(sdrb, gpu_ctx):
+    """sdrb_process_host (chunked H2D / kernels / D2H overlap) returns exactly what sdrb_process does."""
+    n, fs, S, B = 16384, 2_000_000, 11, 3
+    cfg = sdrb.Config(FC, fs, n, 5, inputFormat=0)
+    iq = make_iq(sdrb, 0, fs, 60, S, B, n)
+    gpu_ctx.configure(cfg, S, B)
+    gpu_ctx.process(iq, B)
+    res, pcm = gpu_ctx.results().copy(), gpu_ctx.pcm().copy()
+    pw = gpu_ctx.power_all().copy()
+    gpu_ctx.reset_state()
+    r2 = np.zeros((S, B), dtype=sdrb.RESULT_DTYPE)
+    p2 = np.zeros((S, B, n), dtype=np.float32)
+    c2 = np.zeros((S, B, gpu_ctx.pcm_per_block), dtype=np.int16)
+    gpu_ctx.process_host(iq, B, results=r2, power=p2, pcm=c2)
+    assert np.array_equal(r2, res) and np.array_equal(p2, pw) and np.array_equal(c2, pcm)
+    gpu_ctx.reset_state()
+    gpu_ctx.process_host(iq, B, sdrb.STAGE_FFT, results=r2)      # outputs are optional
+    assert np.array_equal(r2, res)
+
+
 def test_error_behaviour(sdrb, gpu_ctx):
     cfg = sdrb.Config(FC, 2_000_000, 12000, 5, inputFormat=2)
     gpu_ctx.configure(cfg, 1, 1)
