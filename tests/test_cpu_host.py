@@ -134,3 +134,22 @@ def test_synth_source_properties(sdrb):
     spec = np.abs(np.fft.fftshift(np.fft.fft(k[:, 0] + 1j * k[:, 1]))) ** 2
     p = sdrb.plan_config(sdrb.Config())
     assert p.focusLo <= int(np.argmax(spec)) <= p.focusHi
+
+
+def test_dropin_front_end_exports_reference_interface():
+    """libsdr_b200_dropin.so defines the reference's C++ entry points (src/dsp/fft_process.h:29-35,
+    src/ssb/ssb_demod_opt.h:64-65, src/ssb/ssb_processor.h:22-31) and binds only the C-ABI."""
+    import subprocess
+    lib = os.path.join(ROOT, "sdr-for-android-lib_b200", "libsdr_b200_dropin.so")
+    assert os.path.exists(lib), "run __graft_entry__.build()"
+    syms = subprocess.run(["nm", "-D", "-C", lib], capture_output=True, text=True, check=True).stdout
+    defined = [l for l in syms.splitlines() if " T " in l or " W " in l]
+    for want in ("FFTProcessor::FFTProcessor()", "FFTProcessor::configure(FftProcessorConfig const&)",
+                 "FFTProcessor::process(std::complex<float> const*, unsigned int)",
+                 "processSSB_opt(std::vector<std::complex<float>", "lastBlockContainsPulse()",
+                 "SSBProcessor::startProcessing(", "SSBProcessor::stopProcessing()",
+                 "SSBProcessor::enqueueData(std::vector<std::complex<float>"):
+        assert any(want in l for l in defined), want
+    undefined = [l.split()[-1] for l in syms.splitlines() if " U " in l]
+    assert any(u.startswith("sdrb_process_host") for u in undefined)
+    assert not any(u.startswith("cuda") or u.startswith("cu") and u[2:3].isupper() for u in undefined)
