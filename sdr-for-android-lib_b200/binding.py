@@ -237,8 +237,11 @@ class Context:
         return p.value
 
     def pcm(self):
+        """[streams, blocks, m]; with the NCO channel bank on: [streams, channels, blocks, m]."""
         m = self.pcm_per_block
-        out = np.zeros((self.n_streams, self.last_blocks, m), dtype=np.int16)
+        ch = int(self.cfg.ssbChannels)
+        shape = (self.n_streams, ch, self.last_blocks, m) if ch > 1 else (self.n_streams, self.last_blocks, m)
+        out = np.zeros(shape, dtype=np.int16)
         _check(lib.sdrb_get_pcm(self._h, out.ctypes.data_as(C.c_void_p), out.size), self._h)
         return out
 

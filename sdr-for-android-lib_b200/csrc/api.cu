@@ -10,6 +10,7 @@
 #include "fft_tables.h"
 #include "host_design.h"
 #include "internal.h"
+#include "nco.cuh"
 #include "synth.cuh"
 
 using namespace sdrb;
@@ -22,6 +23,7 @@ constexpr size_t kGenericScratchBytes = 256u << 20;  // per ping-pong buffer of 
 struct StateBlobHeader {
     uint32_t magic, version;
     int32_t n_streams, rfMode;
+    uint64_t ssb_samples;     // NCO phase origin of the extended SSB chain
 };
 constexpr int kMaxChunks = 8;
 constexpr uint32_t kBlobMagic = 0x53445242u;  // "SDRB"
@@ -42,6 +44,12 @@ struct sdrb_ctx {
     SsbParams ssb = {};
     float taps255[256] = {};
     int smax = 1;
+    // extension stages (identity = reference behaviour)
+    int channels = 1;           // SSB channels per stream (NCO bank)
+    bool ssb_ext = false;       // any of: NCO offset, channel bank, true sideband
+    uint32_t inc2 = 0;          // Weaver second-mix increment
+    unsigned long long ssb_samples = 0;  // samples per stream since reset (NCO phase origin)
+    int front = 0;              // bit 0 window, bit 1 block-mean removal
     // device buffers
     EstGeometry* d_geo = nullptr;
     void* d_in = nullptr;
@@ -50,7 +58,7 @@ struct sdrb_ctx {
     sdrb_frame_result* d_results = nullptr;
     FftStreamState* d_fft_state = nullptr;
     SsbStreamState* d_ssb_state = nullptr;
-    float2* d_start = nullptr;
+    void* d_start = nullptr;    // float2 per frame (reference-exact path) or float4 per (frame, channel)
     float* d_a48 = nullptr;
     int16_t* d_pcm = nullptr;
     float* d_taps = nullptr;
@@ -59,6 +67,9 @@ struct sdrb_ctx {
     cpx *d_sa = nullptr, *d_sb = nullptr;
     float* d_est_scratch = nullptr;
     int16_t* d_sine = nullptr;
+    uint32_t* d_inc1 = nullptr;
+    float* d_win = nullptr;
+    cpx* d_front = nullptr;
     // last call
     int last_blocks = 0;
     unsigned last_stages = 0;
@@ -91,9 +102,10 @@ static int fail(sdrb_ctx* c, int code, const char* fmt, ...) {
 
 static void free_buffers(sdrb_ctx* c) {
     void** ptrs[] = {(void**)&c->d_geo, &c->d_in, (void**)&c->d_power, (void**)&c->d_local, (void**)&c->d_results,
-                     (void**)&c->d_fft_state, (void**)&c->d_ssb_state, (void**)&c->d_start,
+                     (void**)&c->d_fft_state, (void**)&c->d_ssb_state, &c->d_start,
                      (void**)&c->d_a48, (void**)&c->d_pcm, (void**)&c->d_taps, (void**)&c->d_tw, (void**)&c->d_sa,
-                     (void**)&c->d_sb, (void**)&c->d_est_scratch};
+                     (void**)&c->d_sb, (void**)&c->d_est_scratch, (void**)&c->d_inc1, (void**)&c->d_win,
+                     (void**)&c->d_front};
     for (void** p : ptrs) {
         if (*p) cudaFree(*p);
         *p = nullptr;
@@ -133,8 +145,7 @@ int sdrb_create(int device, sdrb_ctx** out) {
     }
     ctx->stream = ctx->own_stream;
     // constant tables: 16K twiddles and the synthetic source's sine table
-    ctx->fft16k_v1 = getenv("SDRB_FFT16K_V1") != nullptr;   // A/B switch for the first-generation kernel
-    const std::vector<cpx> t16 = ctx->fft16k_v1 ? make_f16k_tables() : make_f2_tables();
+    const std::vector<cpx> t16 = make_f2_tables();
     if ((e = cudaMalloc(&ctx->d_tables16k, t16.size() * sizeof(cpx))) != cudaSuccess ||
         (e = cudaMemcpy(ctx->d_tables16k, t16.data(), t16.size() * sizeof(cpx), cudaMemcpyHostToDevice)) != cudaSuccess ||
         (e = cudaMalloc(&ctx->d_sine, SYNTH_SINE_N * sizeof(int16_t))) != cudaSuccess ||
@@ -185,9 +196,10 @@ static int check_config(sdrb_ctx* ctx, const sdrb_config* cfg) {
     if (cfg->sampleRate == 0) return fail(ctx, SDRB_ERR_ARG, "sampleRate must be > 0");
     if (cfg->inputFormat < SDRB_CU8 || cfg->inputFormat > SDRB_CF32)
         return fail(ctx, SDRB_ERR_ARG, "inputFormat %d is not a sdrb_format", cfg->inputFormat);
-    if (cfg->fftWindow != 0 || cfg->fftRemoveDc != 0 || cfg->ssbTrueSideband != 0 || cfg->ssbChannels > 1)
-        return fail(ctx, SDRB_ERR_UNSUPPORTED,
-                    "extension stages (fftWindow, fftRemoveDc, ssbTrueSideband, ssbChannels > 1) are not built yet");
+    if (cfg->fftWindow < 0 || cfg->fftWindow > 1) return fail(ctx, SDRB_ERR_ARG, "fftWindow must be 0 (rectangular) or 1 (Hann)");
+    if (cfg->ssbChannels < 0 || cfg->ssbChannels > 4096) return fail(ctx, SDRB_ERR_ARG, "ssbChannels must be in [0, 4096]");
+    if (!(cfg->ssbChannelOffsetHz == cfg->ssbChannelOffsetHz) || !(cfg->ssbChannelSpacingHz == cfg->ssbChannelSpacingHz))
+        return fail(ctx, SDRB_ERR_ARG, "ssbChannelOffsetHz / ssbChannelSpacingHz must be numbers");
     return SDRB_OK;
 }
 
@@ -206,7 +218,8 @@ extern "C" int sdrb_plan_config(const sdrb_config* cfg, sdrb_plan* out) {
     out->freqPerBin = g.freqPerBin; out->nyquist = g.nyquist;
     SsbParams P;
     float taps[256] = {};
-    design_ssb(cfg->sampleRate, cfg->samplesPerReading, cfg->soundMode, cfg->soundMode, cfg->upperSideband, P, taps);
+    design_ssb(cfg->sampleRate, cfg->samplesPerReading, cfg->soundMode, cfg->soundMode, cfg->upperSideband,
+               cfg->ssbTrueSideband != 0, P, taps);
     out->decim = P.decim; out->nTaps = P.nTaps; out->pcmPerBlock = P.m;
     out->fftPath = fft_path_for(cfg->samplesPerReading);
     const BiquadCoef* cs[3] = {&P.rf, &P.hp, &P.bp};
@@ -232,8 +245,22 @@ static int upload_geometry(sdrb_ctx* ctx) {
 
 static int upload_ssb(sdrb_ctx* ctx) {
     const int rf = ctx->rfMode >= 0 ? ctx->rfMode : ctx->cfg.soundMode;
-    design_ssb(ctx->cfg.sampleRate, ctx->cfg.samplesPerReading, rf, ctx->cfg.soundMode, ctx->cfg.upperSideband,
+    const bool tsb = ctx->cfg.ssbTrueSideband != 0;
+    design_ssb(ctx->cfg.sampleRate, ctx->cfg.samplesPerReading, rf, ctx->cfg.soundMode, ctx->cfg.upperSideband, tsb,
                ctx->ssb, ctx->taps255);
+    // NCO increments of the channel bank (extension; oracle/sdr_oracle_ext.c): channel c is tuned to
+    // offset + c * spacing; with true sideband the first mix goes to the sideband centre (+/- B/2)
+    // and the second mix brings it back, B = the low-pass bandwidth latched with the first block.
+    const double halfBand = tsb ? (double)ssb_mode(rf).lowpassBd * 0.5 : 0.0;
+    const double sgn = ctx->cfg.upperSideband ? 1.0 : -1.0;
+    std::vector<uint32_t> inc(ctx->channels);
+    for (int c = 0; c < ctx->channels; c++)
+        inc[c] = nco_inc((double)ctx->cfg.ssbChannelOffsetHz + (double)c * (double)ctx->cfg.ssbChannelSpacingHz +
+                             sgn * halfBand, ctx->cfg.sampleRate);
+    ctx->inc2 = tsb ? nco_inc(halfBand, ctx->cfg.sampleRate) : 0u;
+    if (ctx->d_inc1) { cudaFree(ctx->d_inc1); ctx->d_inc1 = nullptr; }
+    CK(cudaMalloc(&ctx->d_inc1, inc.size() * sizeof(uint32_t)));
+    CK(cudaMemcpy(ctx->d_inc1, inc.data(), inc.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     ctx->smax = ssb_smax(ctx->ssb);
     const std::vector<float> t = slot_major_taps(ctx->taps255, ctx->ssb.nTaps, ctx->ssb.decim, ctx->smax);
     if (ctx->d_taps) { cudaFree(ctx->d_taps); ctx->d_taps = nullptr; }
@@ -251,8 +278,9 @@ static int reset_state(sdrb_ctx* ctx) {
         s.maxPeakHz = static_cast<float>(ctx->cfg.centerFrequency);
     }
     CK(cudaMemcpy(ctx->d_fft_state, fs.data(), fs.size() * sizeof(FftStreamState), cudaMemcpyHostToDevice));
-    CK(cudaMemset(ctx->d_ssb_state, 0, (size_t)ctx->n_streams * sizeof(SsbStreamState)));
+    CK(cudaMemset(ctx->d_ssb_state, 0, (size_t)ctx->n_streams * ctx->channels * sizeof(SsbStreamState)));
     ctx->rfMode = -1;
+    ctx->ssb_samples = 0;
     ctx->last_blocks = 0;
     ctx->last_stages = 0;
     return SDRB_OK;
@@ -275,13 +303,23 @@ int sdrb_configure(sdrb_ctx* ctx, const sdrb_config* cfg, int n_streams, int max
     const int n = cfg->samplesPerReading;
     const size_t frames = (size_t)n_streams * max_blocks;
     ctx->fftPath = fft_path_for(n);
+    ctx->channels = cfg->ssbChannels > 1 ? cfg->ssbChannels : 1;
+    ctx->ssb_ext = ctx->channels > 1 || cfg->ssbTrueSideband != 0 || cfg->ssbChannelOffsetHz != 0.0f;
+    ctx->front = (cfg->fftWindow ? 1 : 0) | (cfg->fftRemoveDc ? 2 : 0);
+    if (ctx->front & 1) {   // symmetric Hann in double, rounded once (oracle/sdr_oracle_ext.c:sdr_oracle_window)
+        std::vector<float> w(n);
+        for (int i = 0; i < n; i++)
+            w[i] = n > 1 ? (float)(0.5 - 0.5 * std::cos(2.0 * 3.14159265358979323846 * (double)i / (double)(n - 1))) : 1.0f;
+        CK(cudaMalloc(&ctx->d_win, (size_t)n * sizeof(float)));
+        CK(cudaMemcpy(ctx->d_win, w.data(), (size_t)n * sizeof(float), cudaMemcpyHostToDevice));
+    }
     CK(cudaMalloc(&ctx->d_geo, sizeof(EstGeometry)));
     CK(cudaMalloc(&ctx->d_fft_state, n_streams * sizeof(FftStreamState)));
-    CK(cudaMalloc(&ctx->d_ssb_state, (size_t)n_streams * sizeof(SsbStreamState)));
+    CK(cudaMalloc(&ctx->d_ssb_state, (size_t)n_streams * ctx->channels * sizeof(SsbStreamState)));
     CK(cudaMalloc(&ctx->d_local, frames * sizeof(FrameLocal)));
     CK(cudaMalloc(&ctx->d_results, frames * sizeof(sdrb_frame_result)));
     CK(cudaMemset(ctx->d_results, 0, frames * sizeof(sdrb_frame_result)));
-    CK(cudaMalloc(&ctx->d_start, frames * sizeof(float2)));
+    CK(cudaMalloc(&ctx->d_start, frames * ctx->channels * sizeof(float4)));
     if ((rc = upload_geometry(ctx)) != SDRB_OK) return rc;
     if ((rc = upload_ssb(ctx)) != SDRB_OK) return rc;
     // power spectrum, audio and PCM are allocated on first use of the stage (sdrb_process)
@@ -329,6 +367,12 @@ static int ensure_fft_buffers(sdrb_ctx* ctx) {
     const int n = ctx->cfg.samplesPerReading;
     const size_t frames = (size_t)ctx->n_streams * ctx->max_blocks;
     if (!ctx->d_power) CK(cudaMalloc(&ctx->d_power, frames * (size_t)n * sizeof(float)));
+    if (ctx->fftPath == 0 && ctx->front && !ctx->d_front) {
+        size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
+        if (chunk < 1) chunk = 1;
+        if (chunk > frames) chunk = frames;
+        CK(cudaMalloc(&ctx->d_front, chunk * (size_t)n * sizeof(cpx)));
+    }
     if (ctx->fftPath == 0 && !ctx->d_tw) {
         std::vector<cpx> tw(n);
         for (int k = 0; k < n; k++) tw[k] = twiddle(k, n);
@@ -346,7 +390,7 @@ static int ensure_fft_buffers(sdrb_ctx* ctx) {
 }
 
 static int ensure_ssb_buffers(sdrb_ctx* ctx) {
-    const size_t frames = (size_t)ctx->n_streams * ctx->max_blocks;
+    const size_t frames = (size_t)ctx->n_streams * ctx->max_blocks * ctx->channels;
     const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 1;
     if (!ctx->d_a48) CK(cudaMalloc(&ctx->d_a48, frames * m * sizeof(float)));
     if (!ctx->d_pcm) CK(cudaMalloc(&ctx->d_pcm, frames * m * sizeof(int16_t)));
@@ -395,18 +439,24 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
         if (time_fft) CK(cudaEventRecord(ctx->ev0, st));
         int fft_launches = 0;
         if (ctx->fftPath == 1) {
-            if (ctx->fft16k_v1)
-                CK(launch_fft16k(fmt, d_iq, power, ctx->d_tables16k, frames, ctx->sm_count, st));
-            else
-                CK(launch_fft16k2(fmt, d_iq, power, ctx->d_tables16k, frames, ctx->sm_count, st));
+            // window / block-mean removal (extension) are fused into phase 1 of the 16K kernel
+            CK(launch_fft16k2(fmt, d_iq, power, ctx->d_tables16k, frames, ctx->sm_count, st, ctx->front, ctx->d_win));
             fft_launches = 1;
         } else {
             size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
             if (chunk < 1) chunk = 1;
             for (size_t f0 = 0; f0 < (size_t)frames; f0 += chunk) {
                 const int nf = (int)((size_t)frames - f0 < chunk ? (size_t)frames - f0 : chunk);
-                CK(launch_fft_generic(fmt, static_cast<const unsigned char*>(d_iq) + f0 * n * bps, power + f0 * n,
-                                      ctx->d_sa, ctx->d_sb, ctx->d_tw, n, nf, st, &fft_launches));
+                const void* src = static_cast<const unsigned char*>(d_iq) + f0 * n * bps;
+                int src_fmt = fmt;
+                if (ctx->front) {   // extension front end as a pre-pass: raw IQ -> (x - mean) * w in cf32
+                    CK(launch_fft_front(fmt, src, ctx->d_front, ctx->d_win, n, nf, ctx->front, st));
+                    fft_launches++;
+                    src = ctx->d_front;
+                    src_fmt = FMT_CF32;
+                }
+                CK(launch_fft_generic(src_fmt, src, power + f0 * n, ctx->d_sa, ctx->d_sb, ctx->d_tw, n, nf, st,
+                                      &fft_launches));
             }
         }
         if (time_fft) { CK(cudaEventRecord(ctx->ev1, st)); ctx->ev_valid = true; }
@@ -419,8 +469,17 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
     }
     if (stages & SDRB_STAGE_SSB) {
         const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 0;
-        CK(launch_ssb(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_start + f0s, ctx->d_ssb_state + s0,
-                      ctx->d_a48 + f0s * m, ctx->d_pcm + f0s * m, ns, n_blocks, st, &launches));
+        if (!ctx->ssb_ext) {
+            CK(launch_ssb(fmt, d_iq, ctx->ssb, ctx->d_taps, static_cast<float2*>(ctx->d_start) + f0s,
+                          ctx->d_ssb_state + s0, ctx->d_a48 + f0s * m, ctx->d_pcm + f0s * m, ns, n_blocks, st,
+                          &launches));
+        } else {
+            const size_t C = (size_t)ctx->channels;
+            CK(launch_ssb_ext(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_inc1, ctx->inc2, ctx->cfg.ssbTrueSideband != 0,
+                              static_cast<float4*>(ctx->d_start) + f0s * C, ctx->d_ssb_state + (size_t)s0 * C,
+                              ctx->d_a48 + f0s * C * m, ctx->d_pcm + f0s * C * m, ns, ctx->channels, n_blocks,
+                              ctx->ssb_samples, st, &launches));
+        }
     }
     ctx->launches += (uint64_t)launches;
     return SDRB_OK;
@@ -443,6 +502,7 @@ int sdrb_process(sdrb_ctx* ctx, const void* iq, int on_device, int n_blocks, uns
     if ((rc = run_streams(ctx, d_iq, 0, ctx->n_streams, n_blocks, stages, st, ctx->timing)) != SDRB_OK) return rc;
     ctx->last_blocks = n_blocks;
     ctx->last_stages |= stages;
+    if (stages & SDRB_STAGE_SSB) ctx->ssb_samples += (unsigned long long)n_blocks * ctx->cfg.samplesPerReading;
     if (!on_device) CK(cudaStreamSynchronize(st));  // the host buffer is only borrowed for the call
     return SDRB_OK;
 }
@@ -493,11 +553,12 @@ int sdrb_process_host(sdrb_ctx* ctx, const void* iq_host, int n_blocks, unsigned
             CK(cudaMemcpyAsync(power_out + f0 * n, ctx->d_power + f0 * n, nf * n * sizeof(float),
                                cudaMemcpyDeviceToHost, ctx->s_out));
         if ((stages & SDRB_STAGE_SSB) && pcm_out && m)
-            CK(cudaMemcpyAsync(pcm_out + f0 * m, ctx->d_pcm + f0 * m, nf * m * sizeof(int16_t),
-                               cudaMemcpyDeviceToHost, ctx->s_out));
+            CK(cudaMemcpyAsync(pcm_out + f0 * m * ctx->channels, ctx->d_pcm + f0 * m * ctx->channels,
+                               nf * m * ctx->channels * sizeof(int16_t), cudaMemcpyDeviceToHost, ctx->s_out));
     }
     ctx->last_blocks = n_blocks;
     ctx->last_stages |= stages;
+    if (stages & SDRB_STAGE_SSB) ctx->ssb_samples += (unsigned long long)n_blocks * n;
     CK(cudaStreamSynchronize(ctx->s_out));
     CK(cudaStreamSynchronize(st));
     return SDRB_OK;
@@ -567,7 +628,7 @@ int sdrb_pcm_device(sdrb_ctx* ctx, const int16_t** dev_ptr) {
 int sdrb_get_pcm(sdrb_ctx* ctx, int16_t* host_out, size_t capacity_samples) {
     if (!ctx || !ctx->configured || !ctx->d_pcm || !(ctx->last_stages & SDRB_STAGE_SSB))
         return fail(ctx, SDRB_ERR_STATE, "no PCM: call sdrb_process with SDRB_STAGE_SSB first");
-    const size_t ns = (size_t)ctx->n_streams * ctx->last_blocks * ctx->ssb.m;
+    const size_t ns = (size_t)ctx->n_streams * ctx->channels * ctx->last_blocks * ctx->ssb.m;
     if (capacity_samples < ns || (!host_out && ns)) return fail(ctx, SDRB_ERR_ARG, "PCM buffer holds %zu < %zu samples", capacity_samples, ns);
     CK(cudaSetDevice(ctx->device));
     if (ns) CK(cudaMemcpyAsync(host_out, ctx->d_pcm, ns * sizeof(int16_t), cudaMemcpyDeviceToHost, ctx->stream));
@@ -582,7 +643,8 @@ extern "C" {
 
 size_t sdrb_state_bytes(const sdrb_ctx* ctx) {
     if (!ctx || !ctx->configured) return 0;
-    return sizeof(StateBlobHeader) + (size_t)ctx->n_streams * (sizeof(FftStreamState) + sizeof(SsbStreamState));
+    return sizeof(StateBlobHeader) +
+           (size_t)ctx->n_streams * (sizeof(FftStreamState) + (size_t)ctx->channels * sizeof(SsbStreamState));
 }
 
 int sdrb_save_state(sdrb_ctx* ctx, void* host_blob, size_t bytes) {
@@ -591,12 +653,13 @@ int sdrb_save_state(sdrb_ctx* ctx, void* host_blob, size_t bytes) {
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(ctx->stream));
     unsigned char* p = static_cast<unsigned char*>(host_blob);
-    StateBlobHeader h = {kBlobMagic, SDRB_ABI_VERSION, ctx->n_streams, ctx->rfMode};
+    StateBlobHeader h = {kBlobMagic, SDRB_ABI_VERSION, ctx->n_streams, ctx->rfMode, ctx->ssb_samples};
     memcpy(p, &h, sizeof h);
     p += sizeof h;
     CK(cudaMemcpy(p, ctx->d_fft_state, (size_t)ctx->n_streams * sizeof(FftStreamState), cudaMemcpyDeviceToHost));
     p += (size_t)ctx->n_streams * sizeof(FftStreamState);
-    CK(cudaMemcpy(p, ctx->d_ssb_state, (size_t)ctx->n_streams * sizeof(SsbStreamState), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(p, ctx->d_ssb_state, (size_t)ctx->n_streams * ctx->channels * sizeof(SsbStreamState),
+                  cudaMemcpyDeviceToHost));
     return SDRB_OK;
 }
 
@@ -613,8 +676,10 @@ int sdrb_load_state(sdrb_ctx* ctx, const void* host_blob, size_t bytes) {
     p += sizeof h;
     CK(cudaMemcpy(ctx->d_fft_state, p, (size_t)ctx->n_streams * sizeof(FftStreamState), cudaMemcpyHostToDevice));
     p += (size_t)ctx->n_streams * sizeof(FftStreamState);
-    CK(cudaMemcpy(ctx->d_ssb_state, p, (size_t)ctx->n_streams * sizeof(SsbStreamState), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->d_ssb_state, p, (size_t)ctx->n_streams * ctx->channels * sizeof(SsbStreamState),
+                  cudaMemcpyHostToDevice));
     ctx->rfMode = h.rfMode;
+    ctx->ssb_samples = h.ssb_samples;
     return upload_ssb(ctx);
 }
 

@@ -49,10 +49,44 @@ struct F2Smem {
     static constexpr int kBytes = (F2_E_ELEMS + F2_TW_ELEMS) * 8 + kStageBytes + 16;
 };
 
-template <int FMT>
+// Extension front end fused into phase 1 (no reference code: FFTProcessor::process feeds the raw
+// block to FFTW, src/dsp/fft_process.cpp:62-79).  FRONT bit 1: subtract the block mean (tree sum
+// over the CTA); bit 0: multiply by the window table w[n].  Definition: oracle/sdr_oracle_ext.c.
+template <int FRONT>
+__device__ __forceinline__ void f2_front(int t, cpx* v, const float* __restrict__ win, cpx* red) {
+    if (FRONT & 2) {
+        cpx s = mk(0.f, 0.f);
+#pragma unroll
+        for (int a = 0; a < 32; a++) s = cadd(s, v[a]);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            s.x += __shfl_xor_sync(0xffffffffu, s.x, d);
+            s.y += __shfl_xor_sync(0xffffffffu, s.y, d);
+        }
+        if ((t & 31) == 0) red[t >> 5] = s;
+        __syncthreads();
+        cpx m = mk(0.f, 0.f);
+#pragma unroll
+        for (int w = 0; w < F2_THREADS / 32; w++) m = cadd(m, red[w]);
+        m.x *= 1.0f / F2_N;
+        m.y *= 1.0f / F2_N;
+#pragma unroll
+        for (int a = 0; a < 32; a++) v[a] = csub(v[a], m);
+    }
+    if (FRONT & 1) {
+#pragma unroll
+        for (int a = 0; a < 32; a++) {
+            const float w = __ldg(win + 512 * a + t);
+            v[a].x *= w;
+            v[a].y *= w;
+        }
+    }
+}
+
+template <int FMT, int FRONT>
 __global__ void __launch_bounds__(F2_THREADS, 1)
 k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict__ out,
-          const cpx* __restrict__ tables, int n_frames) {
+          const cpx* __restrict__ tables, const float* __restrict__ win, int n_frames) {
     typedef typename Ingest2<FMT>::raw_t raw_t;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     cpx* E = reinterpret_cast<cpx*>(smem_raw);
@@ -62,6 +96,7 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
     unsigned long long* bar = reinterpret_cast<unsigned long long*>(reinterpret_cast<unsigned char*>(stage) +
                                                                     F2Smem<FMT>::kStageBytes);
     constexpr bool kStaged = F2Smem<FMT>::kStaged;
+    __shared__ cpx red[F2_THREADS / 32];
     const int t = threadIdx.x;
 
     for (int i = t; i < F2_TW_ELEMS; i += F2_THREADS) TP[i] = tables[i];
@@ -81,10 +116,12 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
         if (kStaged) {
             mbar_wait(bar, parity);
             parity ^= 1u;
-            f2_phase1<FMT>(t, stage, TP, v);
+            f2_phase1_load<FMT>(t, stage, v);
         } else {
-            f2_phase1<FMT>(t, in + (size_t)f * F2_N, TP, v);
+            f2_phase1_load<FMT>(t, in + (size_t)f * F2_N, v);
         }
+        if (FRONT) f2_front<FRONT>(t, v, win, red);
+        f2_phase1_compute(t, TP, v);
         __syncthreads();  // E is free (previous phase 3 done) and the stage has been consumed
         if (kStaged && t == 0 && f + (int)gridDim.x < n_frames) {
             mbar_expect_tx(bar, F2Smem<FMT>::kStageBytes);
@@ -98,34 +135,51 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
     }
 }
 
-cudaError_t fft16k2_prepare() {
+template <int FMT, int FRONT>
+static cudaError_t prep_one() {
+    return cudaFuncSetAttribute(k_fft16k2<FMT, FRONT>, cudaFuncAttributeMaxDynamicSharedMemorySize, F2Smem<FMT>::kBytes);
+}
+template <int FMT>
+static cudaError_t prep_fmt() {
     cudaError_t e;
-    e = cudaFuncSetAttribute(k_fft16k2<FMT_CU8>, cudaFuncAttributeMaxDynamicSharedMemorySize, F2Smem<FMT_CU8>::kBytes);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_fft16k2<FMT_CS16>, cudaFuncAttributeMaxDynamicSharedMemorySize, F2Smem<FMT_CS16>::kBytes);
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(k_fft16k2<FMT_CF32>, cudaFuncAttributeMaxDynamicSharedMemorySize, F2Smem<FMT_CF32>::kBytes);
+    if ((e = prep_one<FMT, 0>()) != cudaSuccess) return e;
+    if ((e = prep_one<FMT, 1>()) != cudaSuccess) return e;
+    if ((e = prep_one<FMT, 2>()) != cudaSuccess) return e;
+    return prep_one<FMT, 3>();
 }
 
+cudaError_t fft16k2_prepare() {
+    cudaError_t e;
+    if ((e = prep_fmt<FMT_CU8>()) != cudaSuccess) return e;
+    if ((e = prep_fmt<FMT_CS16>()) != cudaSuccess) return e;
+    return prep_fmt<FMT_CF32>();
+}
+
+template <int FMT>
+static void launch_fmt(int front, const void* iq, float* power, const cpx* tables, const float* win, int n_frames,
+                       int grid, cudaStream_t st) {
+    typedef typename Ingest2<FMT>::raw_t raw_t;
+    const raw_t* in = static_cast<const raw_t*>(iq);
+    const size_t smem = F2Smem<FMT>::kBytes;
+    switch (front & 3) {
+        case 0: k_fft16k2<FMT, 0><<<grid, F2_THREADS, smem, st>>>(in, power, tables, win, n_frames); break;
+        case 1: k_fft16k2<FMT, 1><<<grid, F2_THREADS, smem, st>>>(in, power, tables, win, n_frames); break;
+        case 2: k_fft16k2<FMT, 2><<<grid, F2_THREADS, smem, st>>>(in, power, tables, win, n_frames); break;
+        default: k_fft16k2<FMT, 3><<<grid, F2_THREADS, smem, st>>>(in, power, tables, win, n_frames); break;
+    }
+}
+
+// front: bit 0 = window (win must hold F2_N floats), bit 1 = subtract the block mean
 cudaError_t launch_fft16k2(int fmt, const void* iq, float* power, const cpx* tables, int n_frames, int sm_count,
-                           cudaStream_t st) {
+                           cudaStream_t st, int front, const float* win) {
     if (n_frames <= 0) return cudaSuccess;
+    if ((front & 1) && !win) return cudaErrorInvalidValue;
     const int grid = n_frames < sm_count ? n_frames : sm_count;
     switch (fmt) {
-        case FMT_CU8:
-            k_fft16k2<FMT_CU8><<<grid, F2_THREADS, F2Smem<FMT_CU8>::kBytes, st>>>(
-                static_cast<const uint16_t*>(iq), power, tables, n_frames);
-            break;
-        case FMT_CS16:
-            k_fft16k2<FMT_CS16><<<grid, F2_THREADS, F2Smem<FMT_CS16>::kBytes, st>>>(
-                static_cast<const uint32_t*>(iq), power, tables, n_frames);
-            break;
-        case FMT_CF32:
-            k_fft16k2<FMT_CF32><<<grid, F2_THREADS, F2Smem<FMT_CF32>::kBytes, st>>>(
-                static_cast<const cpx*>(iq), power, tables, n_frames);
-            break;
-        default:
-            return cudaErrorInvalidValue;
+        case FMT_CU8: launch_fmt<FMT_CU8>(front, iq, power, tables, win, n_frames, grid, st); break;
+        case FMT_CS16: launch_fmt<FMT_CS16>(front, iq, power, tables, win, n_frames, grid, st); break;
+        case FMT_CF32: launch_fmt<FMT_CF32>(front, iq, power, tables, win, n_frames, grid, st); break;
+        default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
 }

@@ -111,11 +111,13 @@ struct Ingest2<FMT_CF32> {
 
 SDRB_HD int f2_slot(int plane, int row, int c) { return plane * F2_PITCH + row * 16 + c; }
 
-// ---- phase 1 (compute part): load, DFT32 over a, twiddle.  v[slot32(ka)] holds the result.
+// ---- phase 1: load + convert, then DFT32 over a and twiddle.  v[slot32(ka)] holds the result.
 template <int FMT>
-SDRB_HD void f2_phase1(int t, const typename Ingest2<FMT>::raw_t* in, const cpx* TP, cpx* v) {
+SDRB_HD void f2_phase1_load(int t, const typename Ingest2<FMT>::raw_t* in, cpx* v) {
 #pragma unroll
     for (int a = 0; a < 32; a++) v[a] = Ingest2<FMT>::cvt(in[512 * a + t]);
+}
+SDRB_HD void f2_phase1_compute(int t, const cpx* TP, cpx* v) {
     fft32(v);
     // W_N^(t ka) from W_N^(t 2^j): w[k] = w[k with lowest set bit cleared] * P[ctz k]
     cpx P[5];
@@ -129,6 +131,11 @@ SDRB_HD void f2_phase1(int t, const typename Ingest2<FMT>::raw_t* in, const cpx*
         w[k] = (k == low) ? P[j] : cmul(w[k - low], P[j]);
         v[slot32(k)] = cmul(v[slot32(k)], w[k]);
     }
+}
+template <int FMT>
+SDRB_HD void f2_phase1(int t, const typename Ingest2<FMT>::raw_t* in, const cpx* TP, cpx* v) {
+    f2_phase1_load<FMT>(t, in, v);
+    f2_phase1_compute(t, TP, v);
 }
 SDRB_HD void f2_phase1_store(int t, cpx* E, const cpx* v) {
 #pragma unroll

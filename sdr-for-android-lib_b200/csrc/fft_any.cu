@@ -7,6 +7,7 @@
 // (K3/K4, src/dsp/fft_process.cpp:83-97).  This path moves 16 B per sample per pass, so it
 // is the correctness path; N = 16384 has its own single-pass kernel (fft16k.cu) and the
 // 64K / 1M sizes their four-step kernels (fft_big.cu).
+#include "fft16k2.cuh"
 #include "internal.h"
 
 namespace sdrb {
@@ -116,6 +117,53 @@ static void launch_pass_r(int R, bool last, const void* in, void* out, const cpx
         case 4: launch_pass<4, FMT>(last, in, out, tw, n, Ns, ps, n_frames, st); break;
         default: launch_pass<2, FMT>(last, in, out, tw, n, Ns, ps, n_frames, st); break;
     }
+}
+
+// Extension front end for the multi-pass paths (no reference code; definition in
+// oracle/sdr_oracle_ext.c:sdr_oracle_fft_front): out[i] = (x[i] - mean) * w[i] as cf32, one CTA per
+// frame.  front bit 0 = window, bit 1 = subtract the block mean.  The 16K kernel fuses this instead.
+template <int FMT>
+__global__ void __launch_bounds__(256)
+k_fft_front(const typename Ingest2<FMT>::raw_t* __restrict__ in, cpx* __restrict__ out, const float* __restrict__ win,
+            int n, int front) {
+    __shared__ cpx red[8];
+    const size_t frame = blockIdx.x;
+    const typename Ingest2<FMT>::raw_t* src = in + frame * (size_t)n;
+    cpx* dst = out + frame * (size_t)n;
+    cpx m = mk(0.f, 0.f);
+    if (front & 2) {
+        cpx s = mk(0.f, 0.f);
+        for (int i = threadIdx.x; i < n; i += 256) s = cadd(s, Ingest2<FMT>::cvt(src[i]));
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            s.x += __shfl_xor_sync(0xffffffffu, s.x, d);
+            s.y += __shfl_xor_sync(0xffffffffu, s.y, d);
+        }
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+        __syncthreads();
+#pragma unroll
+        for (int w = 0; w < 8; w++) m = cadd(m, red[w]);
+        m.x = m.x / (float)n;
+        m.y = m.y / (float)n;
+    }
+    for (int i = threadIdx.x; i < n; i += 256) {
+        cpx v = csub(Ingest2<FMT>::cvt(src[i]), m);
+        if (front & 1) { const float w = win[i]; v.x *= w; v.y *= w; }
+        dst[i] = v;
+    }
+}
+
+cudaError_t launch_fft_front(int fmt, const void* iq, cpx* out, const float* win, int n, int n_frames, int front,
+                             cudaStream_t st) {
+    if (n_frames <= 0) return cudaSuccess;
+    if ((front & 1) && !win) return cudaErrorInvalidValue;
+    switch (fmt) {
+        case FMT_CU8: k_fft_front<FMT_CU8><<<n_frames, 256, 0, st>>>(static_cast<const uint16_t*>(iq), out, win, n, front); break;
+        case FMT_CS16: k_fft_front<FMT_CS16><<<n_frames, 256, 0, st>>>(static_cast<const uint32_t*>(iq), out, win, n, front); break;
+        case FMT_CF32: k_fft_front<FMT_CF32><<<n_frames, 256, 0, st>>>(static_cast<const cpx*>(iq), out, win, n, front); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
 }
 
 int fft_generic_passes(int n) {

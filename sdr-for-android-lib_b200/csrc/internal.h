@@ -99,12 +99,15 @@ cudaError_t launch_fft16k(int fmt, const void* iq, float* power, const cpx* tabl
 cudaError_t fft16k_prepare();  // sets max dynamic shared memory attributes once per process
 // fft16k2.cu : second-generation 16K kernel (512 threads x 32 points, TMA-staged input)
 cudaError_t launch_fft16k2(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
-                           int sm_count, cudaStream_t st);
+                           int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);
 cudaError_t fft16k2_prepare();
 // fft_any.cu : generic power-of-two path (N != 16384)
 cudaError_t launch_fft_generic(int fmt, const void* iq, float* power, cpx* scratch_a, cpx* scratch_b,
                                const cpx* twiddles, int n, int n_frames, cudaStream_t st, int* launches);
 int fft_generic_passes(int n);
+// extension front end (window / block-mean removal) for the multi-pass paths: raw IQ -> cf32
+cudaError_t launch_fft_front(int fmt, const void* iq, cpx* out, const float* win, int n, int n_frames, int front,
+                             cudaStream_t st);
 // estimator.cu
 cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, const EstGeometry& h_geo,
                              FrameLocal* d_local, float* d_stage_scratch, int n_frames, cudaStream_t st);
@@ -117,6 +120,13 @@ int ssb_smax(const SsbParams& P);
 cudaError_t launch_ssb(int fmt, const void* iq, const SsbParams& P, const float* d_taps, float2* d_start,
                        SsbStreamState* d_state, float* d_a48, int16_t* d_pcm, int n_streams, int n_blocks,
                        cudaStream_t st, int* launches);
+cudaError_t launch_ssb_audio(const float* d_a48, const SsbParams& P, SsbStreamState* d_state, int16_t* d_pcm,
+                             int n_streams, int n_blocks, cudaStream_t st);
+// ssb_ext.cu : NCO channel bank + Weaver sideband selection (extension stages)
+cudaError_t launch_ssb_ext(int fmt, const void* iq, const SsbParams& P, const float* d_taps, const uint32_t* d_inc1,
+                           uint32_t inc2, int true_sideband, float4* d_start, SsbStreamState* d_state, float* d_a48,
+                           int16_t* d_pcm, int n_streams, int channels, int n_blocks, unsigned long long base_samples,
+                           cudaStream_t st, int* launches);
 // synth.cu
 cudaError_t launch_synth(int fmt, uint32_t fs, int first_stream, int n_streams, int64_t first_sample,
                          int64_t n_samples, void* d_out, const int16_t* d_sine, cudaStream_t st);

@@ -51,10 +51,14 @@ class SsbState(C.Structure):
                 ("lowpassBd", C.c_float), ("lowpassQ", C.c_float), ("transientCoeff", C.c_float)]
 
 
+class SsbxState(C.Structure):
+    _fields_ = [("base", SsbState), ("rfq", Biquad), ("samples", C.c_uint64), ("halfBand", C.c_double)]
+
+
 def build_oracle():
     """(Re)build the C restatement; cheap, so done on demand."""
-    src = os.path.join(ORACLE_DIR, "sdr_oracle.c")
-    if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(src):
+    srcs = [os.path.join(ORACLE_DIR, f) for f in ("sdr_oracle.c", "sdr_oracle_ext.c", "sdr_oracle.h")]
+    if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", ORACLE_DIR, "liboracle"], stdout=subprocess.DEVNULL)
     return ORACLE_SO
 
@@ -95,6 +99,16 @@ def oracle():
         o.sdr_oracle_biquad_process.argtypes = [C.POINTER(Biquad), f32p, C.c_int]
         o.sdr_oracle_transient_boost.argtypes = [f32p, C.c_int, C.c_float]
         o.sdr_oracle_float_to_pcm.argtypes = [f32p, C.c_int, C.c_float, i16p]
+        # extension stages (oracle/sdr_oracle_ext.c): definitions without reference code
+        o.sdr_oracle_window.argtypes = [C.c_int, C.c_int, f32p]
+        o.sdr_oracle_fft_front.argtypes = [f32p, C.c_int, C.c_int, C.c_int, f32p]
+        o.sdr_oracle_nco.argtypes = [C.c_uint32, f32p, f32p]
+        o.sdr_oracle_nco_inc.restype = C.c_uint32
+        o.sdr_oracle_nco_inc.argtypes = [C.c_double, C.c_uint32]
+        o.sdr_oracle_ssbx_init.argtypes = [C.POINTER(SsbxState)]
+        o.sdr_oracle_process_ssbx.restype = C.c_int
+        o.sdr_oracle_process_ssbx.argtypes = [C.POINTER(SsbxState), f32p, C.c_int, C.c_uint32, C.c_int, C.c_int,
+                                              C.c_int, C.c_double, i16p, C.c_int]
         _oracle = o
     return _oracle
 
@@ -248,3 +262,28 @@ class RefFft:
         out = np.empty(self.n, dtype=np.float32)
         ref().sdr_ref_fft_power(self.h, _fp(out), self.n)
         return out
+
+
+def oracle_fft_front(iq_f32, window_kind, remove_dc):
+    """Extension front end of the FFT path: (x - block mean) * window (oracle/sdr_oracle_ext.c)."""
+    iq = np.ascontiguousarray(iq_f32, dtype=np.float32)
+    out = np.empty_like(iq)
+    oracle().sdr_oracle_fft_front(_fp(iq), iq.shape[0], window_kind, remove_dc, _fp(out))
+    return out
+
+
+class OracleSsbx:
+    """One channel of the extended SSB chain (NCO mix + optional Weaver sideband selection)."""
+
+    def __init__(self, offset_hz=0.0, true_sideband=0):
+        self.st = SsbxState()
+        self.offset, self.tsb = float(offset_hz), int(true_sideband)
+        oracle().sdr_oracle_ssbx_init(C.byref(self.st))
+
+    def process(self, iq_f32, fs, upper=1, mode=1):
+        iq = np.ascontiguousarray(iq_f32, dtype=np.float32)
+        n = iq.shape[0]
+        out = np.zeros(n + 8, dtype=np.int16)
+        m = oracle().sdr_oracle_process_ssbx(C.byref(self.st), _fp(iq), n, fs, upper, mode, self.tsb, self.offset,
+                                             out.ctypes.data_as(i16p), n + 8)
+        return out[:m].copy()

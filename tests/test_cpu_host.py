@@ -111,9 +111,14 @@ def test_config_errors(sdrb):
         with pytest.raises(sdrb.SdrbError) as e:
             sdrb.plan_config(bad)
         assert e.value.code == -1
-    with pytest.raises(sdrb.SdrbError) as e:
-        sdrb.plan_config(sdrb.Config(fftWindow=1))
-    assert e.value.code == -3
+    for bad in (sdrb.Config(fftWindow=2), sdrb.Config(ssbChannels=-1), sdrb.Config(ssbChannels=5000),
+                sdrb.Config(ssbChannelOffsetHz=float("nan"))):
+        with pytest.raises(sdrb.SdrbError) as e:
+            sdrb.plan_config(bad)
+        assert e.value.code == -1
+    # extension stages plan like the reference chain; the true-sideband low-pass is designed at B/2
+    a, b = sdrb.plan_config(sdrb.Config()), sdrb.plan_config(sdrb.Config(ssbTrueSideband=1, fftWindow=1))
+    assert a.pcmPerBlock == b.pcmPerBlock and a.rf[0] > b.rf[0] > 0
 
 
 def test_synth_source_properties(sdrb):
