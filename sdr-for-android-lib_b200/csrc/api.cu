@@ -19,6 +19,7 @@ namespace {
 thread_local std::string g_create_error;
 
 constexpr size_t kGenericScratchBytes = 256u << 20;  // per ping-pong buffer of the generic FFT
+constexpr size_t kFourStepL2Bytes = 96u << 20;       // four-step intermediate kept within the 126 MB L2
 
 struct StateBlobHeader {
     uint32_t magic, version;
@@ -65,6 +66,9 @@ struct sdrb_ctx {
     cpx* d_tables16k = nullptr;
     cpx* d_tw = nullptr;
     cpx *d_sa = nullptr, *d_sb = nullptr;
+    cpx* d_fb_tables = nullptr;   // four-step twiddle tables
+    cpx* d_fbA = nullptr;         // four-step intermediate A' (fb_group frames)
+    int fb_group = 0;
     float* d_est_scratch = nullptr;
     int16_t* d_sine = nullptr;
     uint32_t* d_inc1 = nullptr;
@@ -105,7 +109,7 @@ static void free_buffers(sdrb_ctx* c) {
                      (void**)&c->d_fft_state, (void**)&c->d_ssb_state, &c->d_start,
                      (void**)&c->d_a48, (void**)&c->d_pcm, (void**)&c->d_taps, (void**)&c->d_tw, (void**)&c->d_sa,
                      (void**)&c->d_sb, (void**)&c->d_est_scratch, (void**)&c->d_inc1, (void**)&c->d_win,
-                     (void**)&c->d_front};
+                     (void**)&c->d_front, (void**)&c->d_fb_tables, (void**)&c->d_fbA};
     for (void** p : ptrs) {
         if (*p) cudaFree(*p);
         *p = nullptr;
@@ -138,7 +142,7 @@ int sdrb_create(int device, sdrb_ctx** out) {
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
-        (e = fft16k_prepare()) != cudaSuccess || (e = fft16k2_prepare()) != cudaSuccess || (e = estimator_prepare()) != cudaSuccess) {
+        (e = fft16k_prepare()) != cudaSuccess || (e = fft16k2_prepare()) != cudaSuccess || (e = fft_big_prepare()) != cudaSuccess || (e = estimator_prepare()) != cudaSuccess) {
         fail(nullptr, SDRB_ERR_CUDA, "context setup: %s", cudaGetErrorString(e));
         delete ctx;
         return SDRB_ERR_CUDA;
@@ -203,7 +207,7 @@ static int check_config(sdrb_ctx* ctx, const sdrb_config* cfg) {
     return SDRB_OK;
 }
 
-static int fft_path_for(int n) { return n == F16K_N ? 1 : 0; }
+static int fft_path_for(int n) { return n == F16K_N ? 1 : (fft_big_supports(n) ? 2 : 0); }
 
 extern "C" int sdrb_plan_config(const sdrb_config* cfg, sdrb_plan* out) {
     if (!out) return fail(nullptr, SDRB_ERR_ARG, "plan out is NULL");
@@ -367,6 +371,17 @@ static int ensure_fft_buffers(sdrb_ctx* ctx) {
     const int n = ctx->cfg.samplesPerReading;
     const size_t frames = (size_t)ctx->n_streams * ctx->max_blocks;
     if (!ctx->d_power) CK(cudaMalloc(&ctx->d_power, frames * (size_t)n * sizeof(float)));
+    if (ctx->fftPath == 2 && !ctx->d_fbA) {
+        const std::vector<cpx> tb = n == 65536 ? make_fb_tables<16>() : make_fb_tables<32>();
+        CK(cudaMalloc(&ctx->d_fb_tables, tb.size() * sizeof(cpx)));
+        CK(cudaMemcpy(ctx->d_fb_tables, tb.data(), tb.size() * sizeof(cpx), cudaMemcpyHostToDevice));
+        size_t group = kFourStepL2Bytes / ((size_t)n * sizeof(cpx));
+        if (group < 1) group = 1;
+        if (group > frames) group = frames;
+        ctx->fb_group = (int)group;
+        CK(cudaMalloc(&ctx->d_fbA, group * (size_t)n * sizeof(cpx)));
+        if (ctx->front) CK(cudaMalloc(&ctx->d_front, group * (size_t)n * sizeof(cpx)));
+    }
     if (ctx->fftPath == 0 && ctx->front && !ctx->d_front) {
         size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
         if (chunk < 1) chunk = 1;
@@ -442,6 +457,21 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
             // window / block-mean removal (extension) are fused into phase 1 of the 16K kernel
             CK(launch_fft16k2(fmt, d_iq, power, ctx->d_tables16k, frames, ctx->sm_count, st, ctx->front, ctx->d_win));
             fft_launches = 1;
+        } else if (ctx->fftPath == 2) {
+            // four-step: frames in groups whose intermediate stays L2-resident between the two kernels
+            for (int f0 = 0; f0 < frames; f0 += ctx->fb_group) {
+                const int nf = frames - f0 < ctx->fb_group ? frames - f0 : ctx->fb_group;
+                const void* src = static_cast<const unsigned char*>(d_iq) + (size_t)f0 * n * bps;
+                int src_fmt = fmt;
+                if (ctx->front) {
+                    CK(launch_fft_front(fmt, src, ctx->d_front, ctx->d_win, n, nf, ctx->front, st));
+                    fft_launches++;
+                    src = ctx->d_front;
+                    src_fmt = FMT_CF32;
+                }
+                CK(launch_fft_big(src_fmt, src, power + (size_t)f0 * n, ctx->d_fbA, ctx->d_fb_tables, n, nf, st));
+                fft_launches += 2;
+            }
         } else {
             size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
             if (chunk < 1) chunk = 1;

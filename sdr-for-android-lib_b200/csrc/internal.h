@@ -108,6 +108,12 @@ int fft_generic_passes(int n);
 // extension front end (window / block-mean removal) for the multi-pass paths: raw IQ -> cf32
 cudaError_t launch_fft_front(int fmt, const void* iq, cpx* out, const float* win, int n, int n_frames, int front,
                              cudaStream_t st);
+// fft_big.cu : multi-CTA four-step FFT (N = 65536, 1048576), bulk-TMA staged row tiles
+cudaError_t fft_big_prepare();
+bool fft_big_supports(int n);
+int fft_big_table_elems(int n);
+cudaError_t launch_fft_big(int fmt, const void* iq, float* power, cpx* A, const cpx* tables, int n, int n_frames,
+                           cudaStream_t st);
 // estimator.cu
 cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, const EstGeometry& h_geo,
                              FrameLocal* d_local, float* d_stage_scratch, int n_frames, cudaStream_t st);

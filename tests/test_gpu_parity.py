@@ -277,3 +277,22 @@ def test_full_size_properties_c2(sdrb, gpu_ctx):
     gpu_ctx.reset_state()
     gpu_ctx.process(d, 1, sdrb.STAGE_FFT)
     assert gpu_ctx.results()["peakBin"].astype(np.int64).sum() == chk1
+
+
+@pytest.mark.parametrize("fmt", [2, 0])
+def test_power_spectrum_parity_1m(sdrb, gpu_ctx, fmt):
+    """BASELINE config C5: 1 048 576-point transform (multi-CTA four-step path), estimator included."""
+    n, fs, S, B = 1 << 20, 10_000_000, 2, 2
+    iq = make_iq(sdrb, fmt, fs, 3, S, B, n)
+    cfg = sdrb.Config(FC, fs, n, 5, inputFormat=fmt)
+    assert sdrb.plan_config(cfg).fftPath == 2
+    gpu_ctx.configure(cfg, S, B)
+    gpu_ctx.process(iq, B, sdrb.STAGE_FFT)
+    res = gpu_ctx.results()
+    for s in range(S):
+        orc = ol.OracleFft(FC, fs, n, 5)
+        for b in range(B):
+            ref = ol.oracle_power(ol.to_cf32(iq[s, b], fmt))
+            got = gpu_ctx.power(s, b)
+            assert np.all(np.abs(got - ref) <= power_tolerance(ref)), (s, b, float(np.abs(got - ref).max()))
+            check_results(res[s, b], orc.evaluate(got), 0, ("1M", s, b))
