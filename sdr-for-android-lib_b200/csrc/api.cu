@@ -40,7 +40,7 @@ struct sdrb_ctx {
     int n_streams = 0, max_blocks = 0;
     int rfMode = -1;            // latched by the first SSB call (static rfFilter, ssb_demod_opt.cpp:261-263)
     int fftPath = 0;
-    bool fft16k_v1 = false;
+    int fft16k_gen = 2;         // 2 = scalar-FP32 kernel (default), 3 = packed-FP32 kernel (SDRB_FFT16K=3); same speed, see DESIGN.md 5.1
     EstGeometry geo = {};
     SsbParams ssb = {};
     float taps255[256] = {};
@@ -63,7 +63,8 @@ struct sdrb_ctx {
     float* d_a48 = nullptr;
     int16_t* d_pcm = nullptr;
     float* d_taps = nullptr;
-    cpx* d_tables16k = nullptr;
+    cpx* d_tables16k = nullptr;            // v2 tables
+    unsigned char* d_tables16k3 = nullptr;  // v3 tables
     cpx* d_tw = nullptr;
     cpx *d_sa = nullptr, *d_sb = nullptr;
     cpx* d_fb_tables = nullptr;   // four-step twiddle tables
@@ -142,16 +143,21 @@ int sdrb_create(int device, sdrb_ctx** out) {
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
-        (e = fft16k_prepare()) != cudaSuccess || (e = fft16k2_prepare()) != cudaSuccess || (e = fft_big_prepare()) != cudaSuccess || (e = estimator_prepare()) != cudaSuccess) {
+        (e = fft16k2_prepare()) != cudaSuccess || (e = fft16k3_prepare()) != cudaSuccess || (e = fft_big_prepare()) != cudaSuccess || (e = estimator_prepare()) != cudaSuccess) {
         fail(nullptr, SDRB_ERR_CUDA, "context setup: %s", cudaGetErrorString(e));
         delete ctx;
         return SDRB_ERR_CUDA;
     }
     ctx->stream = ctx->own_stream;
     // constant tables: 16K twiddles and the synthetic source's sine table
+    const char* gen = getenv("SDRB_FFT16K");
+    ctx->fft16k_gen = (gen && gen[0] == '3') ? 3 : 2;
     const std::vector<cpx> t16 = make_f2_tables();
+    const std::vector<unsigned char> t3 = make_f3_tables();
     if ((e = cudaMalloc(&ctx->d_tables16k, t16.size() * sizeof(cpx))) != cudaSuccess ||
         (e = cudaMemcpy(ctx->d_tables16k, t16.data(), t16.size() * sizeof(cpx), cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->d_tables16k3, t3.size())) != cudaSuccess ||
+        (e = cudaMemcpy(ctx->d_tables16k3, t3.data(), t3.size(), cudaMemcpyHostToDevice)) != cudaSuccess ||
         (e = cudaMalloc(&ctx->d_sine, SYNTH_SINE_N * sizeof(int16_t))) != cudaSuccess ||
         (e = cudaMemcpy(ctx->d_sine, synth_sine_table(), SYNTH_SINE_N * sizeof(int16_t), cudaMemcpyHostToDevice)) != cudaSuccess) {
         fail(nullptr, SDRB_ERR_CUDA, "table upload: %s", cudaGetErrorString(e));
@@ -168,6 +174,7 @@ int sdrb_destroy(sdrb_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     free_buffers(ctx);
     if (ctx->d_tables16k) cudaFree(ctx->d_tables16k);
+    if (ctx->d_tables16k3) cudaFree(ctx->d_tables16k3);
     if (ctx->d_sine) cudaFree(ctx->d_sine);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -207,7 +214,7 @@ static int check_config(sdrb_ctx* ctx, const sdrb_config* cfg) {
     return SDRB_OK;
 }
 
-static int fft_path_for(int n) { return n == F16K_N ? 1 : (fft_big_supports(n) ? 2 : 0); }
+static int fft_path_for(int n) { return n == F3_N ? 1 : (fft_big_supports(n) ? 2 : 0); }
 
 extern "C" int sdrb_plan_config(const sdrb_config* cfg, sdrb_plan* out) {
     if (!out) return fail(nullptr, SDRB_ERR_ARG, "plan out is NULL");
@@ -455,7 +462,10 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
         int fft_launches = 0;
         if (ctx->fftPath == 1) {
             // window / block-mean removal (extension) are fused into phase 1 of the 16K kernel
-            CK(launch_fft16k2(fmt, d_iq, power, ctx->d_tables16k, frames, ctx->sm_count, st, ctx->front, ctx->d_win));
+            if (ctx->fft16k_gen == 2)
+                CK(launch_fft16k2(fmt, d_iq, power, ctx->d_tables16k, frames, ctx->sm_count, st, ctx->front, ctx->d_win));
+            else
+                CK(launch_fft16k3(fmt, d_iq, power, ctx->d_tables16k3, frames, ctx->sm_count, st, ctx->front, ctx->d_win));
             fft_launches = 1;
         } else if (ctx->fftPath == 2) {
             // four-step: frames in groups whose intermediate stays L2-resident between the two kernels

@@ -3,8 +3,8 @@
 #include <cmath>
 #include <vector>
 
-#include "fft16k.cuh"
 #include "fft16k2.cuh"
+#include "fft16k3.cuh"
 #include "fft_big.cuh"
 
 namespace sdrb {
@@ -14,24 +14,6 @@ inline cpx twiddle(long long num, long long den) {
     num %= den;
     const double a = -2.0 * 3.14159265358979323846264338327950288 * (double)num / (double)den;
     return mk((float)std::cos(a), (float)std::sin(a));
-}
-
-// Layout: TA | TB | T2 | T3  (F16K_TW_ELEMS entries), see fft16k.cuh
-inline std::vector<cpx> make_f16k_tables() {
-    std::vector<cpx> t(F16K_TW_ELEMS);
-    cpx* TA = t.data();
-    cpx* TB = TA + F16K_TA;
-    cpx* T2 = TB + F16K_TB;
-    cpx* T3 = T2 + F16K_T2;
-    for (int w = 0; w < 32; w++)
-        for (int k = 0; k < 16; k++) TA[w * 16 + k] = twiddle(32LL * w * k, F16K_N);
-    for (int k = 0; k < 16; k++)
-        for (int l = 0; l < 32; l++) TB[k * 32 + l] = twiddle((long long)l * k, F16K_N);
-    for (int k = 0; k < 16; k++)
-        for (int s = 0; s < 64; s++) T2[k * 64 + s] = twiddle((long long)s * k, 1024);
-    for (int k = 0; k < 16; k++)
-        for (int d = 0; d < 4; d++) T3[k * 4 + d] = twiddle((long long)d * k, 64);
-    return t;
 }
 
 // Layout: TP | T2  (F2_TW_ELEMS entries), see fft16k2.cuh
@@ -44,6 +26,22 @@ inline std::vector<cpx> make_f2_tables() {
     for (int kb = 0; kb < 32; kb++)
         for (int c = 0; c < 16; c++) T2[kb * 16 + c] = twiddle((long long)c * kb, 512);
     return t;
+}
+
+// Layout (bytes): TP as cpx[5][512] | T2 as pw4[16][16], see fft16k3.cuh
+inline std::vector<unsigned char> make_f3_tables() {
+    std::vector<unsigned char> raw(F3_TABLE_BYTES);
+    cpx* TP = reinterpret_cast<cpx*>(raw.data());
+    pw4* T2 = reinterpret_cast<pw4*>(raw.data() + F3_TP * 8);
+    for (int j = 0; j < 5; j++)
+        for (int r = 0; r < 512; r++) TP[j * 512 + r] = twiddle((long long)r << j, F3_N);
+    for (int k = 0; k < 16; k++)
+        for (int c = 0; c < 16; c++) {
+            const cpx lo = twiddle((long long)c * k, 512), hi = twiddle((long long)c * (k + 16), 512);
+            T2[k * 16 + c].re = mkp(lo.x, hi.x);
+            T2[k * 16 + c].im = mkp(lo.y, hi.y);
+        }
+    return raw;
 }
 
 // Layout: TL | TLO | THI | TB  (FbGeom<R>::kTables entries), see fft_big.cuh

@@ -5,7 +5,6 @@
 
 #include "../../include/sdr_b200.h"
 #include "fft_core.cuh"
-#include "fft16k.cuh"
 
 namespace sdrb {
 
@@ -93,14 +92,14 @@ struct SsbParams {
 };
 
 // ---------------------------------------------------------------- launchers
-// fft16k.cu
-cudaError_t launch_fft16k(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
-                          int sm_count, cudaStream_t st);
-cudaError_t fft16k_prepare();  // sets max dynamic shared memory attributes once per process
 // fft16k2.cu : second-generation 16K kernel (512 threads x 32 points, TMA-staged input)
 cudaError_t launch_fft16k2(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
                            int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);
 cudaError_t fft16k2_prepare();
+// fft16k3.cu : third-generation 16K kernel (packed FP32 pairs, same decomposition and staging)
+cudaError_t launch_fft16k3(int fmt, const void* iq, float* power, const unsigned char* tables, int n_frames,
+                           int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);
+cudaError_t fft16k3_prepare();
 // fft_any.cu : generic power-of-two path (N != 16384)
 cudaError_t launch_fft_generic(int fmt, const void* iq, float* power, cpx* scratch_a, cpx* scratch_b,
                                const cpx* twiddles, int n, int n_frames, cudaStream_t st, int* launches);
