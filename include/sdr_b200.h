@@ -192,6 +192,8 @@ uint64_t sdrb_launch_count(const sdrb_ctx* ctx);
 /* Device time in ms of the dominant (FFT) kernel launches of the last sdrb_process, measured
  * with CUDA events on the launching stream; returns count of launches timed. */
 int  sdrb_last_fft_kernel_ms(sdrb_ctx* ctx, float* ms_total);
+/* Readings covered by the launch(es) timed above (the 16K path times its first chunk only). */
+int  sdrb_last_fft_kernel_frames(const sdrb_ctx* ctx);
 int  sdrb_enable_kernel_timing(sdrb_ctx* ctx, int on);
 
 #ifdef __cplusplus

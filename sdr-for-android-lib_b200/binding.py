@@ -89,6 +89,7 @@ EXPORTS = {
     "sdrb_launch_count": (C.c_uint64, [C.c_void_p]),
     "sdrb_last_fft_kernel_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "sdrb_enable_kernel_timing": (C.c_int, [C.c_void_p, C.c_int]),
+    "sdrb_last_fft_kernel_frames": (C.c_int, [C.c_void_p]),
 }
 
 if not os.path.exists(lib_path):
@@ -267,6 +268,10 @@ class Context:
 
     def enable_kernel_timing(self, on=True):
         _check(lib.sdrb_enable_kernel_timing(self._h, 1 if on else 0), self._h)
+
+    @property
+    def last_fft_kernel_frames(self):
+        return int(lib.sdrb_last_fft_kernel_frames(self._h))
 
     def last_fft_kernel_ms(self):
         ms = C.c_float()

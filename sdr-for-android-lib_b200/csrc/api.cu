@@ -83,6 +83,8 @@ struct sdrb_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool ev_valid = false;
     int last_fft_launches = 0;
+    int last_fft_frames = 0;    // frames covered by the timed FFT launch(es)
+    int est_chunk = 0;          // frames per FFT->estimator chunk on the 16K path (0 = whole call)
     // host-to-host pipeline (sdrb_process_host)
     cudaStream_t s_in = nullptr, s_out = nullptr;
     cudaEvent_t ev_in[8] = {}, ev_done[8] = {};
@@ -150,6 +152,8 @@ int sdrb_create(int device, sdrb_ctx** out) {
     }
     ctx->stream = ctx->own_stream;
     // constant tables: 16K twiddles and the synthetic source's sine table
+    const char* chunk_env = getenv("SDRB_EST_CHUNK");
+    ctx->est_chunk = chunk_env ? atoi(chunk_env) : 0;   // measured: chunking for L2 residency loses (0.67 vs 0.45 ms per step)
     const char* gen = getenv("SDRB_FFT16K");
     ctx->fft16k_gen = (gen && gen[0] == '3') ? 3 : 2;
     const std::vector<cpx> t16 = make_f2_tables();
@@ -458,15 +462,31 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
     int launches = 0;
     if (stages & SDRB_STAGE_FFT) {
         float* power = ctx->d_power + f0s * n;
-        if (time_fft) CK(cudaEventRecord(ctx->ev0, st));
+        if (time_fft && ctx->fftPath != 1) CK(cudaEventRecord(ctx->ev0, st));
         int fft_launches = 0;
+        bool estimator_done = false;
         if (ctx->fftPath == 1) {
-            // window / block-mean removal (extension) are fused into phase 1 of the 16K kernel
-            if (ctx->fft16k_gen == 2)
-                CK(launch_fft16k2(fmt, d_iq, power, ctx->d_tables16k, frames, ctx->sm_count, st, ctx->front, ctx->d_win));
-            else
-                CK(launch_fft16k3(fmt, d_iq, power, ctx->d_tables16k3, frames, ctx->sm_count, st, ctx->front, ctx->d_win));
-            fft_launches = 1;
+            // window / block-mean removal (extension) are fused into phase 1 of the 16K kernel.
+            // Frames go through FFT -> estimator in chunks whose spectra (64 KiB each) are still in
+            // the 126 MB L2 when the estimator reads its bands back.
+            const int chunk = ctx->est_chunk > 0 ? ctx->est_chunk : frames;
+            for (int f0 = 0; f0 < frames; f0 += chunk) {
+                const int nf = frames - f0 < chunk ? frames - f0 : chunk;
+                const void* src = static_cast<const unsigned char*>(d_iq) + (size_t)f0 * n * bps;
+                if (time_fft && f0 == 0) CK(cudaEventRecord(ctx->ev0, st));
+                if (ctx->fft16k_gen == 2)
+                    CK(launch_fft16k2(fmt, src, power + (size_t)f0 * n, ctx->d_tables16k, nf, ctx->sm_count, st, ctx->front, ctx->d_win));
+                else
+                    CK(launch_fft16k3(fmt, src, power + (size_t)f0 * n, ctx->d_tables16k3, nf, ctx->sm_count, st, ctx->front, ctx->d_win));
+                if (time_fft && f0 == 0) { CK(cudaEventRecord(ctx->ev1, st)); ctx->ev_valid = true; ctx->last_fft_frames = nf; }
+                fft_launches++;
+                if (chunk < frames) {
+                    CK(launch_estimator(power + (size_t)f0 * n, ctx->d_geo, ctx->geo, ctx->d_local + f0s + f0,
+                                        ctx->d_est_scratch, f0s + f0, ctx->n_streams * ctx->max_blocks, nf, st));
+                    launches += ctx->geo.focusLen > 0 ? 2 : 1;
+                }
+            }
+            estimator_done = chunk < frames;
         } else if (ctx->fftPath == 2) {
             // four-step: frames in groups whose intermediate stays L2-resident between the two kernels
             for (int f0 = 0; f0 < frames; f0 += ctx->fb_group) {
@@ -499,13 +519,16 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
                                       &fft_launches));
             }
         }
-        if (time_fft) { CK(cudaEventRecord(ctx->ev1, st)); ctx->ev_valid = true; }
-        ctx->last_fft_launches = fft_launches;
+        if (time_fft && ctx->fftPath != 1) { CK(cudaEventRecord(ctx->ev1, st)); ctx->ev_valid = true; ctx->last_fft_frames = frames; }
+        ctx->last_fft_launches = ctx->fftPath == 1 ? 1 : fft_launches;
         launches += fft_launches;
-        float* scratch = ctx->d_est_scratch ? ctx->d_est_scratch + f0s * ctx->geo.totalBins : nullptr;
-        CK(launch_estimator(power, ctx->d_geo, ctx->geo, ctx->d_local + f0s, scratch, frames, st));
+        if (!estimator_done) {
+            CK(launch_estimator(power, ctx->d_geo, ctx->geo, ctx->d_local + f0s, ctx->d_est_scratch, f0s,
+                                ctx->n_streams * ctx->max_blocks, frames, st));
+            launches += ctx->geo.focusLen > 0 ? 2 : 1;
+        }
         CK(launch_tracker(ctx->d_local + f0s, ctx->d_geo, ctx->d_fft_state + s0, ctx->d_results + f0s, ns, n_blocks, st));
-        launches += 2;
+        launches += 1;
     }
     if (stages & SDRB_STAGE_SSB) {
         const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 0;
@@ -762,6 +785,8 @@ int sdrb_enable_kernel_timing(sdrb_ctx* ctx, int on) {
     ctx->ev_valid = false;
     return SDRB_OK;
 }
+
+int sdrb_last_fft_kernel_frames(const sdrb_ctx* ctx) { return ctx ? ctx->last_fft_frames : 0; }
 
 int sdrb_last_fft_kernel_ms(sdrb_ctx* ctx, float* ms_total) {
     if (!ctx || !ms_total) return SDRB_ERR_ARG;

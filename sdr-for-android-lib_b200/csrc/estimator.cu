@@ -1,26 +1,35 @@
 // estimator.cu — evaluateSignalStrength on the GPU (src/dsp/fft_process.cpp:122-378).
 //
-// Two kernels:
-//   k_estimator : one WARP per frame, everything that is frame-local (focus band, reference
-//                 windows, sort, MAD sigmas, pooled per-bin noise, Gumbel / best-1 kHz SNR).
+// Three kernels:
+//   k_band_scan : one THREAD per (frame, band); band 0 = focus band, 1..nWin = reference windows.
+//                 The float sums the reference does sequentially (signalPowerSum :148, window sums
+//                 :199, the sliding run-sum of best1kHzMean :163-180 / :310-318) are done
+//                 sequentially here too, un-fused, so that the arg-max bin, the best-1 kHz start
+//                 bin and every band sum round exactly like the reference.  32 bands per warp.
+//   k_estimator : one WARP per frame: dB figures of the bands (double log10 rounded once; glibc's
+//                 log10f is not reproducible on the GPU, difference <= 1 ulp), stable rank sort of
+//                 the windows by mean dB (:228-229), bottom-40 % statistics (:235-247, :292-300),
+//                 pooled per-bin noise (:252-269: dB of every bin of the quiet windows, mean,
+//                 median absolute deviation by a 4-pass radix select), Gumbel / best-1 kHz SNR.
 //   k_tracker   : one thread per stream, the sequential part that carries state from frame to
 //                 frame (frequency tracking :333-361, detection flag :365-378, hold-over of
 //                 outputs on skipped / invalid frames) and writes the sdrb_frame_result records.
-//
-// Float sums that the reference does sequentially (signalPowerSum :148, window sums :199,
-// the sliding run-sum :175, perBinMean :261) are done sequentially here too, one lane per
-// band, with un-fused adds, so that they round exactly like the reference; only log10 differs
-// (double-precision log10 rounded once vs glibc log10f).
+// The pooled per-bin mean (:261-262) is a tree sum here (the reference adds sequentially); it
+// only feeds tolerance-checked scalars (0.01 dB), not an index or a sort decision.
 #include "internal.h"
 
 namespace sdrb {
 
-constexpr int EST_MAX_WARPS = 4;   // frames per CTA (one warp each)
-constexpr int EST_MAX_SMEM_FLOATS = 48 * 1024;  // 192 KiB of staged bins; above that: global scratch
+constexpr int EST_WARPS = 4;                 // frames per CTA in k_estimator (one warp each)
+constexpr int EST_SMEM_POOL_FLOATS = 2048;   // pooled bins staged in shared memory per warp; above: global scratch
+constexpr int EST_MAX_BANDS = 11;
 
 __device__ __forceinline__ float db10(float p) {
     // 10.0f * log10f(p / refPower + 1e-20f), refPower = 1  (src/dsp/fft_process.cpp:149)
     return __fmul_rn(10.0f, (float)log10((double)__fadd_rn(p, 1e-20f)));
+}
+__device__ __forceinline__ float db10_fast(float p) {   // per-bin noise statistics only
+    return __fmul_rn(10.0f, log10f(__fadd_rn(p, 1e-20f)));
 }
 
 struct BandStat {
@@ -31,10 +40,50 @@ struct BandStat {
     int bestStart;   // offset of the first window that reaches bestRun
 };
 
-// Sequential pass over one band held at p[0..len).  Mirrors :146-155 (sum + arg-max),
-// :198-202 (sum + max) and best1kHzMean :163-180 / :310-318 (run-sum, strict >).
-__device__ void band_scan(const float* p, int len, int W, float maxInit, BandStat& r) {
-    float sum = 0.0f, maxP = maxInit;
+// ---------------------------------------------------------------- k_band_scan
+// Mirrors :146-155 (sum + arg-max), :198-202 (sum + max) and best1kHzMean :163-180 / :310-318
+// (run-sum with +new -old updates, strict >).
+// STAGED: the CTA first copies the bands of its `fpc` frames into shared memory with coalesced
+// loads (the spectra were just written by the FFT kernel and are mostly in HBM: one thread per
+// band walking global memory is latency-bound), then every thread scans its band from there.
+template <bool STAGED>
+__global__ void __launch_bounds__(128)
+k_band_scan(const float* __restrict__ power, const EstGeometry* __restrict__ geo_p, BandStat* __restrict__ stats,
+            int fpc, int n_frames) {
+    extern __shared__ float band_smem[];
+    __shared__ EstGeometry g;
+    {
+        const int* src = reinterpret_cast<const int*>(geo_p);
+        int* dst = reinterpret_cast<int*>(&g);
+        for (int i = threadIdx.x; i < (int)(sizeof(EstGeometry) / 4); i += blockDim.x) dst[i] = src[i];
+    }
+    __syncthreads();
+    if (g.focusLen <= 0) return;
+    const int nSeg = g.nWin + 1;
+    const int frame0 = blockIdx.x * fpc;
+    const int nf = min(fpc, n_frames - frame0);
+    if (STAGED) {
+        for (int f = 0; f < nf; f++) {
+            const float* __restrict__ P = power + (size_t)(frame0 + f) * g.n;
+            float* dst = band_smem + (size_t)f * g.totalBins;
+            for (int seg = 0; seg < nSeg; seg++) {
+                const int lo = seg == 0 ? g.focusLo : g.winLo[seg - 1];
+                const int len = g.segOff[seg + 1] - g.segOff[seg];
+                for (int i = threadIdx.x; i < len; i += blockDim.x) dst[g.segOff[seg] + i] = __ldg(P + lo + i);
+            }
+        }
+        __syncthreads();
+    }
+    const int id = threadIdx.x;
+    if (id >= nf * nSeg) return;
+    const int fl = id / nSeg, seg = id % nSeg;
+    const int frame = frame0 + fl;
+    const int lo = seg == 0 ? g.focusLo : g.winLo[seg - 1];
+    const int len = g.segOff[seg + 1] - g.segOff[seg];
+    const int W = g.winBins1k;
+    const float* __restrict__ p = STAGED ? band_smem + (size_t)fl * g.totalBins + g.segOff[seg]
+                                         : power + (size_t)frame * g.n + lo;
+    float sum = 0.0f, maxP = seg == 0 ? -1.0f : 0.0f;
     int maxIdx = 0;
 #pragma unroll 8
     for (int i = 0; i < len; i++) {
@@ -42,75 +91,53 @@ __device__ void band_scan(const float* p, int len, int W, float maxInit, BandSta
         sum = __fadd_rn(sum, v);
         if (v > maxP) { maxP = v; maxIdx = i; }
     }
+    BandStat r;
     r.sum = sum; r.maxP = maxP; r.maxIdx = maxIdx;
-    if (len < W) { r.bestRun = sum; r.bestStart = 0; return; }
-    float run = 0.0f;
-    for (int i = 0; i < W; i++) run = __fadd_rn(run, p[i]);
-    float best = run;
-    int bestStart = 0;
-#pragma unroll 4
-    for (int s = 1; s + W - 1 < len; s++) {
-        run = __fadd_rn(run, __fsub_rn(p[s + W - 1], p[s - 1]));
-        if (run > best) { best = run; bestStart = s; }
+    if (len < W) {
+        r.bestRun = sum; r.bestStart = 0;
+    } else {
+        float run = 0.0f;
+        for (int i = 0; i < W; i++) run = __fadd_rn(run, p[i]);
+        float best = run;
+        int bestStart = 0;
+#pragma unroll 8
+        for (int s = 1; s + W - 1 < len; s++) {
+            run = __fadd_rn(run, __fsub_rn(p[s + W - 1], p[s - 1]));
+            if (run > best) { best = run; bestStart = s; }
+        }
+        r.bestRun = best; r.bestStart = bestStart;
     }
-    r.bestRun = best; r.bestStart = bestStart;
+    stats[(size_t)frame * EST_MAX_BANDS + seg] = r;
 }
 
-// Median-of-gaps helper for <= 10 values (:238-242, :296-300): sorted |x - mean| [nb/2].
-__device__ float small_mad(const float* x, int nb, float mean) {
-    float g[10];
-    for (int i = 0; i < nb; i++) g[i] = fabsf(__fsub_rn(x[i], mean));
-    for (int i = 1; i < nb; i++) {
-        const float t = g[i];
-        int j = i - 1;
-        while (j >= 0 && g[j] > t) { g[j + 1] = g[j]; j--; }
-        g[j + 1] = t;
-    }
-    return g[nb / 2];
+// ---------------------------------------------------------------- k_estimator
+// Median-of-gaps for <= 4 values (:238-242, :296-300): sorted |x - mean| [nb / 2].
+__device__ __forceinline__ void cswap(float& a, float& b) { const float lo = fminf(a, b), hi = fmaxf(a, b); a = lo; b = hi; }
+__device__ __forceinline__ float mad4(const float* x, int nb, float mean) {
+    float g[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) g[i] = i < nb ? fabsf(__fsub_rn(x[i], mean)) : 3.0e38f;
+    cswap(g[0], g[1]); cswap(g[2], g[3]); cswap(g[0], g[2]); cswap(g[1], g[3]); cswap(g[1], g[2]);
+    const int m = nb / 2;
+    return m == 0 ? g[0] : (m == 1 ? g[1] : g[2]);
 }
-
-struct PoolMap {
-    int nSeg;
-    int base[4];   // stage offset of each pooled segment (sorted-window order)
-    int cum[5];    // cumulative lengths, cum[nSeg] = pooledN
-};
-
-__device__ __forceinline__ int pool_addr(const PoolMap& pm, int i) {
-    int j = 0;
-    while (j + 1 < pm.nSeg && i >= pm.cum[j + 1]) j++;
-    return pm.base[j] + (i - pm.cum[j]);
-}
-
-// Per-warp working set: one warp owns one frame, so the only block-wide barrier is the one that
-// publishes the geometry; everything else is __syncwarp.
-struct EstWarp {
-    BandStat st[11];
-    PoolMap pm;
-    int hist[256];
-    float winMeanDb[10], winBest1kDb[10];
-    float focusDb[2];          // absPeakDb candidate, signalPowerDb
-    FrameLocal out;
-    float perBinMean;
-};
 
 template <bool USE_SMEM>
-__global__ void __launch_bounds__(EST_MAX_WARPS * 32)
-k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo_p, FrameLocal* __restrict__ local,
-            float* __restrict__ gscratch, int n_frames) {
+__global__ void __launch_bounds__(EST_WARPS * 32)
+k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo_p, const BandStat* __restrict__ stats,
+            FrameLocal* __restrict__ local, float* __restrict__ gscratch, int pooled_cap, int n_frames) {
     extern __shared__ float stage_smem[];
     __shared__ EstGeometry g;
-    __shared__ EstWarp ws[EST_MAX_WARPS];
-
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    __shared__ int hist_all[EST_WARPS][256];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     {
         const int* src = reinterpret_cast<const int*>(geo_p);
         int* dst = reinterpret_cast<int*>(&g);
         for (int i = threadIdx.x; i < (int)(sizeof(EstGeometry) / 4); i += blockDim.x) dst[i] = src[i];
     }
     __syncthreads();
-    const size_t frame = (size_t)blockIdx.x * nwarps + warp;
-    if (frame >= (size_t)n_frames) return;
-    EstWarp& W = ws[warp];
+    const int frame = blockIdx.x * EST_WARPS + warp;
+    if (frame >= n_frames) return;
     if (g.focusLen <= 0) {  // :139 early return, the frame leaves every output untouched
         if (lane == 0) {
             FrameLocal z = {};
@@ -120,180 +147,157 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
         }
         return;
     }
-    const float* P = power + frame * (size_t)g.n;
-    float* stage = USE_SMEM ? stage_smem + (size_t)warp * g.totalBins : gscratch + frame * (size_t)g.totalBins;
-
-    for (int seg = 0; seg <= g.nWin; seg++) {
-        const int lo = seg == 0 ? g.focusLo : g.winLo[seg - 1];
-        const int len = g.segOff[seg + 1] - g.segOff[seg];
-        float* d = stage + g.segOff[seg];
-        for (int i = lane; i < len; i += 32) d[i] = P[lo + i];
-    }
-    __syncwarp();
-    const bool valid = g.nWin >= 2;  // :218
-    if (lane <= g.nWin) {
-        const int len = g.segOff[lane + 1] - g.segOff[lane];
-        BandStat bs;
-        band_scan(stage + g.segOff[lane], len, g.winBins1k, lane == 0 ? -1.0f : 0.0f, bs);
-        W.st[lane] = bs;
-        // the dB figures of this band, one lane per band (:149-155, :203-213)
-        if (lane == 0) {
-            W.focusDb[0] = db10(bs.maxP);
-            W.focusDb[1] = db10(__fdiv_rn(bs.sum, (float)g.focusLen));
-        } else if (valid) {
-            W.winMeanDb[lane - 1] = db10(__fdiv_rn(bs.sum, (float)len));
-            const float b1k = len < g.winBins1k ? __fdiv_rn(bs.sum, (float)len)
-                                                : __fdiv_rn(bs.bestRun, (float)g.winBins1k);
-            W.winBest1kDb[lane - 1] = db10(b1k);
-        }
-    }
-    __syncwarp();
-
+    const unsigned FULL = 0xffffffffu;
+    const int nWin = g.nWin, W = g.winBins1k;
+    const bool valid = nWin >= 2;  // :218
+    const bool isWin = lane >= 1 && lane <= nWin;
+    BandStat bs = {};
+    if (lane <= nWin) bs = stats[(size_t)frame * EST_MAX_BANDS + lane];
+    const int len = lane <= nWin ? g.segOff[lane + 1] - g.segOff[lane] : 1;
+    // dB figures of the bands, one lane per band (:149-155, :203-213)
+    float dbA = 0.0f, dbB = 0.0f;   // focus: (absPeakDb candidate, signalPowerDb); window: (meanDb, best1kDb)
     if (lane == 0) {
-        FrameLocal o = {};
-        // ---- :142-155 focus band
-        const float dbMax = W.focusDb[0];
-        if (dbMax > -130.0f) { o.absPeakDb = dbMax; o.peakBin = g.focusLo + W.st[0].maxIdx; }
+        dbA = db10(bs.maxP);
+        dbB = db10(__fdiv_rn(bs.sum, (float)g.focusLen));
+    } else if (isWin && valid) {
+        dbA = db10(__fdiv_rn(bs.sum, (float)len));
+        dbB = db10(len < W ? __fdiv_rn(bs.sum, (float)len) : __fdiv_rn(bs.bestRun, (float)W));
+    }
+    FrameLocal o = {};
+    {   // ---- :142-155 focus band
+        const float dbMax = __shfl_sync(FULL, dbA, 0);
+        const int maxIdx = __shfl_sync(FULL, bs.maxIdx, 0);
+        if (dbMax > -130.0f) { o.absPeakDb = dbMax; o.peakBin = g.focusLo + maxIdx; }
         else { o.absPeakDb = -130.0f; o.peakBin = g.focusLo; }
-        o.signalPowerDb = W.focusDb[1];
+        o.signalPowerDb = __shfl_sync(FULL, dbB, 0);
         o.valid = valid ? 1 : 0;
         o.best1kStart = -1;
-        W.pm.nSeg = 0;
-        W.pm.cum[0] = 0;
-        if (valid) {
-            // ---- :228-229 std::sort by meanDb (<= 10 elements: insertion sort, stable)
-            int order[10];
-            for (int w = 0; w < g.nWin; w++) order[w] = w;
-            for (int i = 1; i < g.nWin; i++) {
-                const int w = order[i];
-                int j = i - 1;
-                while (j >= 0 && W.winMeanDb[w] < W.winMeanDb[order[j]]) { order[j + 1] = order[j]; j--; }
-                order[j + 1] = w;
-            }
-            const int nb = g.nBottom;
-            // ---- :235-247 mean-energy SNR
-            float x[10];
-            float mean = 0.0f;
-            for (int i = 0; i < nb; i++) { x[i] = W.winMeanDb[order[i]]; mean = __fadd_rn(mean, x[i]); }
-            mean = __fdiv_rn(mean, (float)nb);
-            const float sigma = fmaxf(__fmul_rn(1.4816f, small_mad(x, nb, mean)), 0.5f);
-            o.meanSnrDb = __fsub_rn(o.signalPowerDb, mean);
-            o.meanSnrSigma = __fdiv_rn(o.meanSnrDb, sigma);
-            // ---- :292-300 best-1 kHz reference statistics (sigma1k needs sigmaBin, finished below)
-            float mean1k = 0.0f;
-            for (int i = 0; i < nb; i++) { x[i] = W.winBest1kDb[order[i]]; mean1k = __fadd_rn(mean1k, x[i]); }
-            mean1k = __fdiv_rn(mean1k, (float)nb);
-            o.best1kHzSnrDb = mean1k;                                      // parked until the final step
-            o.best1kHzSnrSigma = __fmul_rn(1.4816f, small_mad(x, nb, mean1k));
-            // pooled-bin map (:252-257)
-            W.pm.nSeg = nb < 4 ? nb : 4;
-            for (int j = 0; j < W.pm.nSeg; j++) {
-                const int w = order[j];
-                W.pm.base[j] = g.segOff[w + 1];
-                W.pm.cum[j + 1] = W.pm.cum[j] + (g.segOff[w + 2] - g.segOff[w + 1]);
-            }
-        }
-        W.out = o;
     }
+    const float focusSum = __shfl_sync(FULL, bs.sum, 0), focusBestRun = __shfl_sync(FULL, bs.bestRun, 0);
+    const int focusBestStart = __shfl_sync(FULL, bs.bestStart, 0);
+    if (!valid) {
+        if (lane == 0) local[frame] = o;
+        return;
+    }
+    // ---- :228-229 sort by meanDb, as a stable rank (one window per lane)
+    int rank = 0;
+    for (int v = 1; v <= nWin; v++) {
+        const float other = __shfl_sync(FULL, dbA, v);
+        if (isWin && (other < dbA || (other == dbA && v < lane))) rank++;
+    }
+    const int nb = g.nBottom;   // <= 4
+    float x[4], x1k[4];
+    int plo[4], cum[5];
+    cum[0] = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        x[i] = x1k[i] = 0.0f;
+        plo[i] = 0;
+        cum[i + 1] = cum[i];
+        if (i < nb) {
+            const int src = __ffs(__ballot_sync(FULL, isWin && rank == i)) - 1;   // window src - 1, sorted position i
+            x[i] = __shfl_sync(FULL, dbA, src);
+            x1k[i] = __shfl_sync(FULL, dbB, src);
+            plo[i] = g.winLo[src - 1];
+            cum[i + 1] = cum[i] + (g.segOff[src + 1] - g.segOff[src]);
+        }
+    }
+    // ---- :235-247 mean-energy SNR (sequential sums over <= 4 values, uniform across lanes)
+    float mean = 0.0f, mean1k = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+        if (i < nb) { mean = __fadd_rn(mean, x[i]); mean1k = __fadd_rn(mean1k, x1k[i]); }
+    mean = __fdiv_rn(mean, (float)nb);
+    mean1k = __fdiv_rn(mean1k, (float)nb);
+    const float sigma = fmaxf(__fmul_rn(1.4816f, mad4(x, nb, mean)), 0.5f);
+    o.meanSnrDb = __fsub_rn(o.signalPowerDb, mean);
+    o.meanSnrSigma = __fdiv_rn(o.meanSnrDb, sigma);
+    const float mad1k = __fmul_rn(1.4816f, mad4(x1k, nb, mean1k));   // :296-300, floor applied below
+    // ---- :252-262 pooled per-bin dB of the quiet windows and their mean
+    const int pooledN = cum[nb < 4 ? nb : 4];
+    float* stage = USE_SMEM ? stage_smem + (size_t)warp * pooled_cap : gscratch + (size_t)frame * pooled_cap;
+    const float* P = power + (size_t)frame * g.n;
+    float part = 0.0f;
+    for (int i = lane; i < pooledN; i += 32) {
+        const int j = (i >= cum[1]) + (i >= cum[2]) + (i >= cum[3]);
+        const int bin = (j == 0 ? plo[0] : (j == 1 ? plo[1] : (j == 2 ? plo[2] : plo[3]))) +
+                        (i - (j == 0 ? 0 : (j == 1 ? cum[1] : (j == 2 ? cum[2] : cum[3]))));
+        const float d = db10_fast(__ldg(P + bin));
+        stage[i] = d;
+        part += d;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(FULL, part, d);
+    const float perBinMean = __fdiv_rn(part, (float)pooledN);
+    for (int i = lane; i < pooledN; i += 32) stage[i] = fabsf(__fsub_rn(stage[i], perBinMean));   // :265-266
     __syncwarp();
-
-    if (valid) {
-        const PoolMap pm = W.pm;
-        const int pooledN = pm.cum[pm.nSeg];
-        // per-bin dB of the quiet windows, in place (:255-256)
+    // ---- :267-268 median of the gaps: 4-pass radix select on the bit pattern; each lane owns 8 of
+    // the 256 histogram bins and the crossing bin is found with a warp scan
+    int* hist = hist_all[warp];
+    unsigned prefix = 0, mask = 0;
+    int k = pooledN / 2;
+    for (int shift = 24; shift >= 0; shift -= 8) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) hist[lane + 32 * j] = 0;
+        __syncwarp();
         for (int i = lane; i < pooledN; i += 32) {
-            const int a = pool_addr(pm, i);
-            stage[a] = db10(stage[a]);
+            const unsigned bits = __float_as_uint(stage[i]);
+            if ((bits & mask) == prefix) atomicAdd(&hist[(bits >> shift) & 255u], 1);
         }
         __syncwarp();
-        if (lane == 0) {  // :261-262 sequential mean
-            float s = 0.0f;
-            for (int j = 0; j < pm.nSeg; j++) {
-                const float* d = stage + pm.base[j];
-                const int len = pm.cum[j + 1] - pm.cum[j];
-#pragma unroll 8
-                for (int i = 0; i < len; i++) s = __fadd_rn(s, d[i]);
-            }
-            W.perBinMean = __fdiv_rn(s, (float)pooledN);
-        }
-        __syncwarp();
-        const float perBinMean = W.perBinMean;
-        for (int i = lane; i < pooledN; i += 32) {  // :265-266
-            const int a = pool_addr(pm, i);
-            stage[a] = fabsf(__fsub_rn(stage[a], perBinMean));
-        }
-        __syncwarp();
-        // :267-268 median of the gaps: 4-pass radix select on the bit pattern; each lane owns 8 of
-        // the 256 histogram bins and the crossing bin is found with a warp scan
-        unsigned prefix = 0, mask = 0;
-        int k = pooledN / 2;
-        for (int shift = 24; shift >= 0; shift -= 8) {
-            for (int i = lane; i < 256; i += 32) W.hist[i] = 0;
-            __syncwarp();
-            for (int i = lane; i < pooledN; i += 32) {
-                const unsigned b = __float_as_uint(stage[pool_addr(pm, i)]);
-                if ((b & mask) == prefix) atomicAdd(&W.hist[(b >> shift) & 255u], 1);
-            }
-            __syncwarp();
-            int mine = 0;
+        int mine = 0;
 #pragma unroll
-            for (int j = 0; j < 8; j++) mine += W.hist[8 * lane + j];
-            int incl = mine;
+        for (int j = 0; j < 8; j++) mine += hist[8 * lane + j];
+        int incl = mine;
 #pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const int v = __shfl_up_sync(0xffffffffu, incl, d);
-                if (lane >= d) incl += v;
-            }
-            const unsigned cross = __ballot_sync(0xffffffffu, incl > k);
-            const int L = cross ? __ffs(cross) - 1 : 31;
-            int digit = 0, acc = 0;
-            if (lane == L) {
-                acc = incl - mine;
-                digit = 8 * L;
-                for (int j = 0; j < 7; j++) {
-                    const int h = W.hist[8 * L + j];
-                    if (acc + h > k) break;
-                    acc += h;
-                    digit++;
-                }
-            }
-            digit = __shfl_sync(0xffffffffu, digit, L);
-            acc = __shfl_sync(0xffffffffu, acc, L);
-            prefix |= (unsigned)digit << shift;
-            k -= acc;
-            mask |= 255u << shift;
-            __syncwarp();
+        for (int d = 1; d < 32; d <<= 1) {
+            const int v = __shfl_up_sync(FULL, incl, d);
+            if (lane >= d) incl += v;
         }
-        if (lane == 0) {
-            FrameLocal o = W.out;
-            const float sigmaBin = fmaxf(__fmul_rn(1.4816f, __uint_as_float(prefix)), 1.0f);
-            o.perBinMean = perBinMean;
-            o.peakAboveNoiseMeanDb = __fsub_rn(o.absPeakDb, perBinMean);                     // :274
-            // :281-288 Gumbel-corrected max-bin SNR
-            const float gumbelLoc = __fadd_rn(perBinMean, __fmul_rn(sigmaBin, g.sqrt2logN));
-            const float gumbelSig = fmaxf(__fdiv_rn(__fmul_rn(sigmaBin, 3.14159f), g.gumbelDen), 0.5f);
-            o.maxBinSnrDb = __fsub_rn(o.absPeakDb, gumbelLoc);
-            o.maxBinSnrSigma = __fdiv_rn(o.maxBinSnrDb, gumbelSig);
-            // :299-327 best-1 kHz SNR
-            const float mean1k = o.best1kHzSnrDb;
-            const float sigmaFloor1k = __fdiv_rn(sigmaBin, g.sqrtWin1k);
-            const float sigma1k = fmaxf(fmaxf(o.best1kHzSnrSigma, sigmaFloor1k), 0.5f);
-            const float fb = g.focusLen < g.winBins1k ? __fdiv_rn(W.st[0].sum, (float)g.focusLen)
-                                                      : __fdiv_rn(W.st[0].bestRun, (float)g.winBins1k);
-            if (fb > 0.0f) {
-                o.best1kHzSnrDb = __fsub_rn(db10(fb), mean1k);
-                o.best1kHzSnrSigma = __fdiv_rn(o.best1kHzSnrDb, sigma1k);
-                o.best1kStart = g.focusLo + W.st[0].bestStart;
-            } else {
-                o.best1kHzSnrDb = 0.0f;
-                o.best1kHzSnrSigma = 0.0f;
-                o.best1kStart = -1;
+        const unsigned cross = __ballot_sync(FULL, incl > k);
+        const int L = cross ? __ffs(cross) - 1 : 31;
+        int digit = 0, acc = 0;
+        if (lane == L) {
+            acc = incl - mine;
+            digit = 8 * L;
+            for (int j = 0; j < 7; j++) {
+                const int h = hist[8 * L + j];
+                if (acc + h > k) break;
+                acc += h;
+                digit++;
             }
-            W.out = o;
         }
+        digit = __shfl_sync(FULL, digit, L);
+        acc = __shfl_sync(FULL, acc, L);
+        prefix |= (unsigned)digit << shift;
+        k -= acc;
+        mask |= 255u << shift;
+        __syncwarp();
     }
-    __syncwarp();
-    if (lane == 0) local[frame] = W.out;
+    if (lane == 0) {
+        const float sigmaBin = fmaxf(__fmul_rn(1.4816f, __uint_as_float(prefix)), 1.0f);
+        o.perBinMean = perBinMean;
+        o.peakAboveNoiseMeanDb = __fsub_rn(o.absPeakDb, perBinMean);                     // :274
+        // :281-288 Gumbel-corrected max-bin SNR
+        const float gumbelLoc = __fadd_rn(perBinMean, __fmul_rn(sigmaBin, g.sqrt2logN));
+        const float gumbelSig = fmaxf(__fdiv_rn(__fmul_rn(sigmaBin, 3.14159f), g.gumbelDen), 0.5f);
+        o.maxBinSnrDb = __fsub_rn(o.absPeakDb, gumbelLoc);
+        o.maxBinSnrSigma = __fdiv_rn(o.maxBinSnrDb, gumbelSig);
+        // :299-327 best-1 kHz SNR
+        const float sigmaFloor1k = __fdiv_rn(sigmaBin, g.sqrtWin1k);
+        const float sigma1k = fmaxf(fmaxf(mad1k, sigmaFloor1k), 0.5f);
+        const float fb = g.focusLen < W ? __fdiv_rn(focusSum, (float)g.focusLen) : __fdiv_rn(focusBestRun, (float)W);
+        if (fb > 0.0f) {
+            o.best1kHzSnrDb = __fsub_rn(db10(fb), mean1k);
+            o.best1kHzSnrSigma = __fdiv_rn(o.best1kHzSnrDb, sigma1k);
+            o.best1kStart = g.focusLo + focusBestStart;
+        } else {
+            o.best1kHzSnrDb = 0.0f;
+            o.best1kHzSnrSigma = 0.0f;
+            o.best1kStart = -1;
+        }
+        local[frame] = o;
+    }
 }
 
 // Frame clock (SURVEY.md 8a note T): t = (frame + 1) * n / fs in ns, integer arithmetic.
@@ -387,30 +391,63 @@ k_tracker(const FrameLocal* __restrict__ local, const EstGeometry* __restrict__ 
     state[s] = st;
 }
 
+static int pooled_cap_of(const EstGeometry& g) {
+    // the nBottom (<= 4) longest reference windows bound the pooled bin count
+    int lens[10];
+    for (int w = 0; w < g.nWin; w++) lens[w] = g.segOff[w + 2] - g.segOff[w + 1];
+    for (int i = 0; i < g.nWin; i++)
+        for (int j = i + 1; j < g.nWin; j++)
+            if (lens[j] > lens[i]) { const int t = lens[i]; lens[i] = lens[j]; lens[j] = t; }
+    int cap = 0;
+    for (int i = 0; i < g.nBottom && i < g.nWin && i < 4; i++) cap += lens[i];
+    return cap > 0 ? cap : 1;
+}
+
 cudaError_t estimator_prepare() {
+    cudaError_t e = cudaFuncSetAttribute(k_band_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(k_estimator<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                EST_MAX_SMEM_FLOATS * (int)sizeof(float));
+                                EST_WARPS * EST_SMEM_POOL_FLOATS * (int)sizeof(float));
 }
 
+// Scratch (floats): band statistics for every frame, then the pooled-bin staging area when it does
+// not fit in shared memory.
+static size_t band_floats(int n_frames) { return (size_t)n_frames * EST_MAX_BANDS * (sizeof(BandStat) / sizeof(float)); }
 size_t estimator_scratch_floats(const EstGeometry& g, int n_frames) {
-    return g.totalBins > EST_MAX_SMEM_FLOATS ? (size_t)g.totalBins * (size_t)n_frames : 0;
+    const int cap = pooled_cap_of(g);
+    return band_floats(n_frames) + (cap > EST_SMEM_POOL_FLOATS ? (size_t)cap * (size_t)n_frames : 0);
 }
 
+// scratch = base of the context's scratch (sized for cap_frames); frame0 = index of this call's
+// first frame inside the context (power / d_local are already offset by the caller).
 cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, const EstGeometry& h_geo,
-                             FrameLocal* d_local, float* d_stage_scratch, int n_frames, cudaStream_t st) {
+                             FrameLocal* d_local, float* scratch, size_t frame0, int cap_frames, int n_frames,
+                             cudaStream_t st) {
     if (n_frames <= 0) return cudaSuccess;
-    const int bins = h_geo.totalBins > 0 ? h_geo.totalBins : 1;
-    const int use_smem = bins <= EST_MAX_SMEM_FLOATS ? 1 : 0;
-    if (!use_smem && !d_stage_scratch) return cudaErrorInvalidValue;
-    // frames (warps) per CTA: as many as fit in ~48 KiB of staging, 1..EST_MAX_WARPS
-    int warps = use_smem ? (12 * 1024) / bins : EST_MAX_WARPS;
-    warps = warps < 1 ? 1 : (warps > EST_MAX_WARPS ? EST_MAX_WARPS : warps);
-    const size_t smem = use_smem ? (size_t)bins * warps * sizeof(float) : 0;
-    const int grid = (n_frames + warps - 1) / warps;
-    if (use_smem)
-        k_estimator<true><<<grid, warps * 32, smem, st>>>(power, d_geo, d_local, d_stage_scratch, n_frames);
-    else
-        k_estimator<false><<<grid, warps * 32, 0, st>>>(power, d_geo, d_local, d_stage_scratch, n_frames);
+    if (!scratch) return cudaErrorInvalidValue;
+    BandStat* stats = reinterpret_cast<BandStat*>(scratch) + frame0 * EST_MAX_BANDS;
+    const int nSeg = h_geo.nWin + 1;
+    if (h_geo.focusLen > 0) {
+        // frames per CTA: one thread per band (<= 128 threads), staged bands within 64 KiB
+        int fpc = 128 / nSeg;
+        const int by_smem = (64 * 1024) / (h_geo.totalBins * (int)sizeof(float));
+        if (by_smem >= 1 && false) {   // measured on B200: staging is slower (129 us vs 37 us), kept for reference
+            if (fpc > by_smem) fpc = by_smem;
+            const size_t smem = (size_t)fpc * h_geo.totalBins * sizeof(float);
+            k_band_scan<true><<<(n_frames + fpc - 1) / fpc, 128, smem, st>>>(power, d_geo, stats, fpc, n_frames);
+        } else {
+            k_band_scan<false><<<(n_frames + fpc - 1) / fpc, 128, 0, st>>>(power, d_geo, stats, fpc, n_frames);
+        }
+    }
+    const int cap = pooled_cap_of(h_geo);
+    const int grid = (n_frames + EST_WARPS - 1) / EST_WARPS;
+    if (cap <= EST_SMEM_POOL_FLOATS) {
+        k_estimator<true><<<grid, EST_WARPS * 32, (size_t)EST_WARPS * cap * sizeof(float), st>>>(
+            power, d_geo, stats, d_local, nullptr, cap, n_frames);
+    } else {
+        float* gs = scratch + band_floats(cap_frames) + frame0 * (size_t)cap;
+        k_estimator<false><<<grid, EST_WARPS * 32, 0, st>>>(power, d_geo, stats, d_local, gs, cap, n_frames);
+    }
     return cudaGetLastError();
 }
 

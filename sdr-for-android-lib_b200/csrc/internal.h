@@ -115,7 +115,8 @@ cudaError_t launch_fft_big(int fmt, const void* iq, float* power, cpx* A, const 
                            cudaStream_t st);
 // estimator.cu
 cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, const EstGeometry& h_geo,
-                             FrameLocal* d_local, float* d_stage_scratch, int n_frames, cudaStream_t st);
+                             FrameLocal* d_local, float* scratch, size_t frame0, int cap_frames, int n_frames,
+                             cudaStream_t st);
 cudaError_t estimator_prepare();
 size_t estimator_scratch_floats(const EstGeometry& g, int n_frames);
 cudaError_t launch_tracker(const FrameLocal* d_local, const EstGeometry* d_geo, FftStreamState* d_state,
