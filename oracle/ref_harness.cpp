@@ -198,3 +198,42 @@ double sdr_ref_run_frames(void* h, const float* iq, int n, int frames_in_buf, in
 }
 
 } /* extern "C" */
+
+/* ------------------------------ pulse detectors ------------------------------ */
+#include "dsp/spectral_pulse_detector.h"
+#include "ssb/audio_pulse_detector.h"
+#include <vector>
+
+extern "C" {
+
+/* SpectralPulseDetector as the bridge uses it: default-constructed global, then configure() with
+ * fsEnergy = sampleRate / samplesPerReading (src/sdr-bridge-java-soapy.cpp:105,1131-1137). */
+void* sdr_ref_spd_create(float fs_energy) {
+    SpectralPulseDetector* d = new SpectralPulseDetector();
+    SpectralPulseDetector::Config c;
+    c.fsEnergy = fs_energy;
+    d->configure(c);
+    return d;
+}
+void sdr_ref_spd_destroy(void* h) { delete static_cast<SpectralPulseDetector*>(h); }
+/* out: liveEtat, level, locked, lastSnr, tTarget, estimatedFreqHz */
+void sdr_ref_spd_process(void* h, float snr_sigma, float freq_hz, float* out) {
+    SpectralPulseDetector* d = static_cast<SpectralPulseDetector*>(h);
+    const int level = static_cast<int>(d->process(snr_sigma, freq_hz));
+    out[0] = (float)d->liveEtat(); out[1] = (float)level; out[2] = d->isLocked() ? 1.f : 0.f;
+    out[3] = d->lastPulseStrength(); out[4] = d->lockedPeriodS(); out[5] = d->estimatedFreqHz();
+}
+
+/* AudioPulseDetector with its default Config (src/ssb/ssb_processor.h member pulseDetector_). */
+void* sdr_ref_apd_create(void) { return new AudioPulseDetector(); }
+void sdr_ref_apd_destroy(void* h) { delete static_cast<AudioPulseDetector*>(h); }
+/* out: liveEtat, level, locked, lastSnr, tTarget */
+void sdr_ref_apd_process(void* h, const int16_t* pcm, int n, float* out) {
+    AudioPulseDetector* d = static_cast<AudioPulseDetector*>(h);
+    std::vector<int16_t> v(pcm, pcm + n);
+    const int level = static_cast<int>(d->process(v));
+    out[0] = (float)d->liveEtat(); out[1] = (float)level; out[2] = d->isLocked() ? 1.f : 0.f;
+    out[3] = d->lastPulseStrength(); out[4] = d->lockedPeriodS();
+}
+
+}  /* extern "C" */

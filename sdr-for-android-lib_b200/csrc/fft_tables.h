@@ -5,6 +5,7 @@
 
 #include "fft16k2.cuh"
 #include "fft16k3.cuh"
+#include "fft16k4.cuh"
 #include "fft_big.cuh"
 
 namespace sdrb {
@@ -42,6 +43,17 @@ inline std::vector<unsigned char> make_f3_tables() {
             T2[k * 16 + c].im = mkp(lo.y, hi.y);
         }
     return raw;
+}
+
+// Layout: TQ as cpx[6][256] | T3 as cpx[16][16], see fft16k4.cuh
+inline std::vector<cpx> make_f4_tables() {
+    std::vector<cpx> t(F4_TQ + F4_T3);
+    for (int j = 0; j < 5; j++)
+        for (int r = 0; r < 256; r++) t[j * 256 + r] = twiddle((long long)r << j, F4_H);
+    for (int r = 0; r < 256; r++) t[5 * 256 + r] = twiddle(r, F4_N);
+    for (int kb = 0; kb < 16; kb++)
+        for (int c = 0; c < 16; c++) t[F4_TQ + kb * 16 + c] = twiddle((long long)c * kb, 256);
+    return t;
 }
 
 // Layout: TL | TLO | THI | TB  (FbGeom<R>::kTables entries), see fft_big.cuh

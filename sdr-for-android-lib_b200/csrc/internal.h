@@ -100,6 +100,10 @@ cudaError_t fft16k2_prepare();
 cudaError_t launch_fft16k3(int fmt, const void* iq, float* power, const unsigned char* tables, int n_frames,
                            int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);
 cudaError_t fft16k3_prepare();
+// fft16k4.cu : fourth-generation 16K kernel (two 8192-point jobs per transform, 2 CTAs per SM)
+cudaError_t launch_fft16k4(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
+                           int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);
+cudaError_t fft16k4_prepare(const cpx* host_tables);
 // fft_any.cu : generic power-of-two path (N != 16384)
 cudaError_t launch_fft_generic(int fmt, const void* iq, float* power, cpx* scratch_a, cpx* scratch_b,
                                const cpx* twiddles, int n, int n_frames, cudaStream_t st, int* launches);
