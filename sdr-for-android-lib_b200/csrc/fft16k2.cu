@@ -11,6 +11,11 @@
 
 namespace sdrb {
 
+__constant__ cpx c_f2_t2[F2_T2];   // W_512^(c kb), [kb][c]
+struct F2DevTw {
+    __device__ __forceinline__ cpx operator()(int kb, int c) const { return c_f2_t2[kb * 16 + c]; }
+};
+
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(void* bar, unsigned count) {
@@ -46,7 +51,7 @@ template <int FMT>
 struct F2Smem {
     static constexpr bool kStaged = FMT != FMT_CF32;
     static constexpr int kStageBytes = kStaged ? F2_N * (int)sizeof(typename Ingest2<FMT>::raw_t) : 0;
-    static constexpr int kBytes = (F2_E_ELEMS + F2_TW_ELEMS) * 8 + kStageBytes + 16;
+    static constexpr int kBytes = (F2_E_ELEMS + F2_TP) * 8 + kStageBytes + 16;
 };
 
 // Extension front end fused into phase 1 (no reference code: FFTProcessor::process feeds the raw
@@ -91,15 +96,14 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
     extern __shared__ __align__(128) unsigned char smem_raw[];
     cpx* E = reinterpret_cast<cpx*>(smem_raw);
     cpx* TP = E + F2_E_ELEMS;
-    cpx* T2 = TP + F2_TP;
-    raw_t* stage = reinterpret_cast<raw_t*>(T2 + F2_T2);
+    raw_t* stage = reinterpret_cast<raw_t*>(TP + F2_TP);
     unsigned long long* bar = reinterpret_cast<unsigned long long*>(reinterpret_cast<unsigned char*>(stage) +
                                                                     F2Smem<FMT>::kStageBytes);
     constexpr bool kStaged = F2Smem<FMT>::kStaged;
     __shared__ cpx red[F2_THREADS / 32];
     const int t = threadIdx.x;
 
-    for (int i = t; i < F2_TW_ELEMS; i += F2_THREADS) TP[i] = tables[i];
+    for (int i = t; i < F2_TP; i += F2_THREADS) TP[i] = tables[i];
     int f = blockIdx.x;
     if (kStaged && t == 0) {
         mbar_init(bar, 1);
@@ -129,9 +133,9 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
         }
         f2_phase1_store(t, E, v);
         __syncthreads();
-        f2_phase2(t, E, T2);
+        f2_phase2(t, E);
         __syncthreads();
-        f2_phase3(t, E, out + (size_t)f * F2_N);
+        f2_phase3(t, E, F2DevTw(), out + (size_t)f * F2_N);
     }
 }
 
@@ -148,8 +152,9 @@ static cudaError_t prep_fmt() {
     return prep_one<FMT, 3>();
 }
 
-cudaError_t fft16k2_prepare() {
+cudaError_t fft16k2_prepare(const cpx* host_tables) {
     cudaError_t e;
+    if ((e = cudaMemcpyToSymbol(c_f2_t2, host_tables + F2_TP, F2_T2 * sizeof(cpx))) != cudaSuccess) return e;
     if ((e = prep_fmt<FMT_CU8>()) != cudaSuccess) return e;
     if ((e = prep_fmt<FMT_CS16>()) != cudaSuccess) return e;
     return prep_fmt<FMT_CF32>();

@@ -4,7 +4,7 @@
 //
 //   n = 512 a + 16 b + c           k = ka + 32 kb + 1024 kc        (a, b, ka, kb < 32; c, kc < 16)
 //   phase 1: DFT32 over a   thread t = 16 b + c          twiddle W_N^(t ka)
-//   phase 2: DFT32 over b   thread t = 16 ka + c         twiddle W_512^(c kb)
+//   phase 2: DFT32 over b   thread t = 16 ka + c         (twiddle W_512^(c kb) applied by phase 3 on load)
 //   phase 3: DFT16 over c   thread t -> (ka, kb) pairs p = t and t + 512, ka = p & 31, kb = p >> 5
 //            then |X|^2, fftshift folded into the store index
 // Exchange buffer E[ka][row][c] with plane pitch 513 complex (odd pitch mod 16): every phase's
@@ -73,10 +73,12 @@ struct Ingest2<FMT_CU8> {
     typedef uint16_t raw_t;
     SDRB_HD static cpx cvt(uint16_t r) {
 #if defined(__CUDA_ARCH__)
-        // 0x4B0000bb is the float 2^23 + bb: two PRMTs instead of two I2Fs
-        const float fi = __uint_as_float(__byte_perm((unsigned)r, 0x4B000000u, 0x7440)) - 8388608.0f;
-        const float fq = __uint_as_float(__byte_perm((unsigned)r, 0x4B000000u, 0x7441)) - 8388608.0f;
-        return mk(__fmaf_rn(fi, 0.0078125f, -127.4f * 0.0078125f), __fmaf_rn(fq, 0.0078125f, -127.4f * 0.0078125f));
+        // the byte placed at bits 16..23 of a float word is b * 2^-133 exactly (sub-normal or first binade);
+        // fma(that, 2^126, -127.4f/128) = round((b - 127.4f) / 128): ONE instruction per component
+        const float fi = __uint_as_float(__byte_perm((unsigned)r, 0u, 0x4044));
+        const float fq = __uint_as_float(__byte_perm((unsigned)r, 0u, 0x4144));
+        return mk(__fmaf_rn(fi, 8.50705917302346158658e37f, -127.4f * 0.0078125f),
+                  __fmaf_rn(fq, 8.50705917302346158658e37f, -127.4f * 0.0078125f));
 #else
         const float fi = (float)(int)(r & 0xffu), fq = (float)(int)(r >> 8);
         return mk((fi - 127.4f) * 0.0078125f, (fq - 127.4f) * 0.0078125f);
@@ -142,8 +144,8 @@ SDRB_HD void f2_phase1_store(int t, cpx* E, const cpx* v) {
     for (int k = 0; k < 32; k++) E[k * F2_PITCH + t] = v[slot32(k)];
 }
 
-// ---- phase 2: DFT32 over b for (ka, c), twiddle W_512^(c kb), in place
-SDRB_HD void f2_phase2(int t, cpx* E, const cpx* T2) {
+// ---- phase 2: DFT32 over b for (ka, c), in place (its twiddle W_512^(c kb) is applied by phase 3 on load)
+SDRB_HD void f2_phase2(int t, cpx* E) {
     const int ka = t >> 4, c = t & 15;
     cpx* base = E + ka * F2_PITCH + c;
     cpx v[32];
@@ -151,21 +153,23 @@ SDRB_HD void f2_phase2(int t, cpx* E, const cpx* T2) {
     for (int b = 0; b < 32; b++) v[b] = base[b * 16];
     fft32(v);
 #pragma unroll
-    for (int k = 1; k < 32; k++) v[slot32(k)] = cmul(v[slot32(k)], T2[k * 16 + c]);
-#pragma unroll
     for (int k = 0; k < 32; k++) base[k * 16] = v[slot32(k)];
 }
 
-// ---- phase 3: DFT16 over c for two (ka, kb) pairs, power, fftshift, store
-SDRB_HD void f2_phase3(int t, const cpx* E, float* __restrict__ out) {
+// ---- phase 3: twiddle W_512^(c kb) on load (kb is uniform over a warp: the device functor reads the
+// constant bank, one broadcast per value instead of a 256-byte shared-memory wavefront pair), DFT16 over c
+// for two (ka, kb) pairs, power, fftshift, store
+template <class TW>
+SDRB_HD void f2_phase3(int t, const cpx* E, TW tw, float* __restrict__ out) {
 #pragma unroll
     for (int h = 0; h < 2; h++) {
         const int p = t + 512 * h;
         const int ka = p & 31, kb = p >> 5;
         const cpx* base = E + ka * F2_PITCH + kb * 16;
         cpx v[16];
+        v[0] = base[0];
 #pragma unroll
-        for (int c = 0; c < 16; c++) v[c] = base[c];
+        for (int c = 1; c < 16; c++) v[c] = cmul(base[c], tw(kb, c));
         fft16(v);
         const int k0 = ka + 32 * kb;
 #pragma unroll

@@ -95,7 +95,7 @@ struct SsbParams {
 // fft16k2.cu : second-generation 16K kernel (512 threads x 32 points, TMA-staged input)
 cudaError_t launch_fft16k2(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
                            int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);
-cudaError_t fft16k2_prepare();
+cudaError_t fft16k2_prepare(const cpx* host_tables);   // make_f2_tables() layout; T2 goes to the constant bank
 // fft16k3.cu : third-generation 16K kernel (packed FP32 pairs, same decomposition and staging)
 cudaError_t launch_fft16k3(int fmt, const void* iq, float* power, const unsigned char* tables, int n_frames,
                            int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);

@@ -69,8 +69,9 @@ int main() {
             f2_phase1<FMT_CU8>(t, raw.data(), TP, v);
             f2_phase1_store(t, E2.data(), v);
         }
-        for (int t = 0; t < F2_THREADS; t++) f2_phase2(t, E2.data(), T2b);
-        for (int t = 0; t < F2_THREADS; t++) f2_phase3(t, E2.data(), out2.data());
+        for (int t = 0; t < F2_THREADS; t++) f2_phase2(t, E2.data());
+        auto tw = [T2b](int kb, int c) { return T2b[kb * 16 + c]; };
+        for (int t = 0; t < F2_THREADS; t++) f2_phase3(t, E2.data(), tw, out2.data());
         double maxrel2 = 0;
         for (int k = 0; k < N; k++) {
             double p = Xr[k] * Xr[k] + Xi[k] * Xi[k];
