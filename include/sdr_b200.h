@@ -46,6 +46,13 @@ typedef enum { SDRB_CU8 = 0, SDRB_CS16 = 1, SDRB_CF32 = 2 } sdrb_format;
 
 #define SDRB_STAGE_FFT 1u   /* FFTProcessor::process       src/dsp/fft_process.cpp:42-105 */
 #define SDRB_STAGE_SSB 2u   /* processSSB_opt              src/ssb/ssb_demod_opt.cpp:221-296 */
+/* the two beacon-pulse detectors that consume the path's outputs. */
+#define SDRB_STAGE_SPECTRAL_PULSE 4u /* SpectralPulseDetector::process per reading (needs SDRB_STAGE_FFT)
+                                        src/dsp/spectral_pulse_detector.cpp:10-13, call site
+                                        src/sdr-bridge-java-soapy.cpp:477-487 */
+#define SDRB_STAGE_AUDIO_PULSE 8u    /* AudioPulseDetector::process(pcm) per reading (needs SDRB_STAGE_SSB)
+                                        src/ssb/audio_pulse_detector.cpp:112-125, call site
+                                        src/ssb/ssb_processor.cpp:109-113 */
 
 /* Per-context configuration, shared by all streams of the context.
  * First block = FftProcessorConfig (src/dsp/fft_process.h:20-26) + the BridgeConfig
@@ -94,6 +101,37 @@ typedef struct {
     int32_t nRef;
     int32_t reserved;
 } sdrb_frame_result;
+
+/* AudioPulseDetector::Config (src/ssb/audio_pulse_detector.h:20-38), field for field. */
+typedef struct {
+    float   sampleRate, fMin, fMax, fsEnergy, smoothCutoff, zDefaultS, tTargetInit, dtTolS;
+    float   snrMin, snrRhythm, snrStrong, dispersionMax;
+    int32_t sumNMax;
+    float   liveWindowT, liveDivisor;
+    int32_t noiseRefFar, noiseRefNear;
+} sdrb_audio_pulse_config;
+
+/* One record per (stream, reading) [x channel for the NCO bank: (stream, channel, reading)]:
+ * the state both detectors expose after that reading's process() call. */
+typedef struct {
+    /* SpectralPulseDetector -> (FIJ)V payload (src/sdr-bridge-java-soapy.cpp:480-486) */
+    float   spectralSnrSigma;      /* the frame's best1kHzSnrSigma as handed to process() */
+    int32_t spectralLiveEtat;      /* liveEtat() 0..5 */
+    int64_t spectralEstFreqHz;     /* llround(estimatedFreqHz()) */
+    float   spectralEstFreqHzF;    /* estimatedFreqHz() (src/dsp/spectral_pulse_detector.cpp:173-196) */
+    int32_t spectralLevel;         /* PulseLevel 0..3 */
+    int32_t spectralLocked;
+    float   spectralLastSnr;       /* lastPulseStrength() */
+    float   spectralTTarget;       /* lockedPeriodS() */
+    /* AudioPulseDetector -> (FI)V payload (src/ssb/ssb_processor.cpp:110-113) */
+    float   audioLastSnr;          /* lastPulseStrength() */
+    int32_t audioLiveEtat;
+    int32_t audioLevel;
+    int32_t audioLocked;
+    float   audioTTarget;
+    int32_t overflow;              /* ROI store overflow count (never in the reference: deques grow) */
+    int32_t reserved;
+} sdrb_pulse_result;
 
 /* What the configuration resolves to: bin geometry of evaluateSignalStrength
  * (src/dsp/fft_process.cpp:125-139,160,191-216,232) and the SSB chain's parameters
@@ -168,6 +206,18 @@ int  sdrb_get_power_all(sdrb_ctx* ctx, float* host_out, size_t capacity_floats);
  * (x ssbChannels when the NCO bank is on: [stream][channel][block][m]). */
 int  sdrb_pcm_device(sdrb_ctx* ctx, const int16_t** dev_ptr);
 int  sdrb_get_pcm(sdrb_ctx* ctx, int16_t* host_out, size_t capacity_samples);
+
+/* ---- pulse detectors -------------------------------------------------- */
+/* Defaults of AudioPulseDetector::Config. */
+void sdrb_audio_pulse_config_default(sdrb_audio_pulse_config* cfg);
+/* SSBProcessor::setPulseConfig (src/ssb/ssb_processor.cpp:69-74,90-96): every stream's audio detector
+ * is rebuilt from cfg (state reset) before the next reading. */
+int  sdrb_set_pulse_config(sdrb_ctx* ctx, const sdrb_audio_pulse_config* cfg);
+/* Records of the last sdrb_process that carried a *_PULSE stage.  Spectral fields are indexed
+ * [stream][reading]; with an NCO bank the audio fields are [stream][channel][reading] and the
+ * spectral fields are valid in channel 0's records. */
+int  sdrb_get_pulse_results(sdrb_ctx* ctx, sdrb_pulse_result* host_out, size_t capacity_records);
+int  sdrb_pulse_results_device(sdrb_ctx* ctx, const sdrb_pulse_result** dev_ptr);
 
 /* ---- per-stream state (checkpoint / resume) ----------------------------- */
 /* Opaque blob: three biquad states, tracking memory, detection ring, frame counter. */

@@ -7,6 +7,7 @@ import numpy as np
 
 CU8, CS16, CF32 = 0, 1, 2
 STAGE_FFT, STAGE_SSB = 1, 2
+STAGE_SPECTRAL_PULSE, STAGE_AUDIO_PULSE = 4, 8
 _HERE = os.path.dirname(os.path.abspath(__file__))
 lib_path = os.path.join(_HERE, "libsdr_b200.so")
 
@@ -45,6 +46,27 @@ class FrameResult(C.Structure):
 RESULT_DTYPE = np.dtype(FrameResult)
 
 
+class AudioPulseConfig(C.Structure):
+    """sdrb_audio_pulse_config = AudioPulseDetector::Config (src/ssb/audio_pulse_detector.h:20-38)."""
+    _fields_ = [(k, C.c_float) for k in ("sampleRate", "fMin", "fMax", "fsEnergy", "smoothCutoff", "zDefaultS",
+                                         "tTargetInit", "dtTolS", "snrMin", "snrRhythm", "snrStrong",
+                                         "dispersionMax")] + [("sumNMax", C.c_int32)] + \
+               [("liveWindowT", C.c_float), ("liveDivisor", C.c_float), ("noiseRefFar", C.c_int32),
+                ("noiseRefNear", C.c_int32)]
+
+
+class PulseResult(C.Structure):
+    _fields_ = [("spectralSnrSigma", C.c_float), ("spectralLiveEtat", C.c_int32), ("spectralEstFreqHz", C.c_int64),
+                ("spectralEstFreqHzF", C.c_float), ("spectralLevel", C.c_int32), ("spectralLocked", C.c_int32),
+                ("spectralLastSnr", C.c_float), ("spectralTTarget", C.c_float),
+                ("audioLastSnr", C.c_float), ("audioLiveEtat", C.c_int32), ("audioLevel", C.c_int32),
+                ("audioLocked", C.c_int32), ("audioTTarget", C.c_float), ("overflow", C.c_int32),
+                ("reserved", C.c_int32)]
+
+
+PULSE_DTYPE = np.dtype(PulseResult)
+
+
 class Plan(C.Structure):
     _fields_ = [("n", C.c_int32), ("focusLo", C.c_int32), ("focusHi", C.c_int32), ("focusLen", C.c_int32),
                 ("winBins1k", C.c_int32), ("nWin", C.c_int32), ("nBottom", C.c_int32),
@@ -73,6 +95,10 @@ EXPORTS = {
     "sdrb_process_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p]),
     "sdrb_get_results": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "sdrb_results_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "sdrb_audio_pulse_config_default": (None, [C.POINTER(AudioPulseConfig)]),
+    "sdrb_set_pulse_config": (C.c_int, [C.c_void_p, C.POINTER(AudioPulseConfig)]),
+    "sdrb_get_pulse_results": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    "sdrb_pulse_results_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "sdrb_power_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "sdrb_get_power": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "sdrb_get_power_all": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
@@ -114,6 +140,12 @@ def _check(rc, ctx=None):
     if rc < 0:
         raise SdrbError(rc, (lib.sdrb_last_error(ctx) or b"").decode())
     return rc
+
+
+def audio_pulse_config_default():
+    c = AudioPulseConfig()
+    lib.sdrb_audio_pulse_config_default(C.byref(c))
+    return c
 
 
 def plan_config(cfg):
@@ -201,6 +233,20 @@ class Context:
         out = np.zeros((self.n_streams, self.last_blocks), dtype=RESULT_DTYPE)
         _check(lib.sdrb_get_results(self._h, out.ctypes.data_as(C.c_void_p), out.size), self._h)
         return out
+
+    def pulse_results(self):
+        """[n_streams, last_blocks] records ([n_streams, channels, last_blocks] with an NCO bank)."""
+        ch = max(1, int(self.cfg.ssbChannels))
+        shape = (self.n_streams, self.last_blocks) if ch == 1 else (self.n_streams, ch, self.last_blocks)
+        out = np.zeros(shape, dtype=PULSE_DTYPE)
+        _check(lib.sdrb_get_pulse_results(self._h, out.ctypes.data_as(C.c_void_p), out.size), self._h)
+        return out
+
+    def set_pulse_config(self, cfg=None):
+        """SSBProcessor::setPulseConfig: rebuild every audio detector (None = the reference defaults)."""
+        if cfg is None:
+            cfg = audio_pulse_config_default()
+        _check(lib.sdrb_set_pulse_config(self._h, C.byref(cfg)), self._h)
 
     def power(self, stream, block):
         out = np.empty(self.cfg.samplesPerReading, dtype=np.float32)

@@ -10,6 +10,7 @@
 #include "fft_tables.h"
 #include "host_design.h"
 #include "internal.h"
+#include "pulse.h"
 #include "nco.cuh"
 #include "synth.cuh"
 
@@ -76,6 +77,13 @@ struct sdrb_ctx {
     uint32_t* d_inc1 = nullptr;
     float* d_win = nullptr;
     cpx* d_front = nullptr;
+    // pulse detectors
+    sdrb_audio_pulse_config au_user = {};
+    bool au_user_set = false;
+    PulseCfg sp_cfg = {}, au_cfg = {};
+    PulseState *d_sp_state = nullptr, *d_au_state = nullptr;
+    float *d_sp_e = nullptr, *d_sp_f = nullptr, *d_au_e = nullptr;
+    sdrb_pulse_result* d_pulse = nullptr;
     // last call
     int last_blocks = 0;
     unsigned last_stages = 0;
@@ -113,7 +121,9 @@ static void free_buffers(sdrb_ctx* c) {
                      (void**)&c->d_fft_state, (void**)&c->d_ssb_state, &c->d_start,
                      (void**)&c->d_a48, (void**)&c->d_pcm, (void**)&c->d_taps, (void**)&c->d_tw, (void**)&c->d_sa,
                      (void**)&c->d_sb, (void**)&c->d_est_scratch, (void**)&c->d_inc1, (void**)&c->d_win,
-                     (void**)&c->d_front, (void**)&c->d_fb_tables, (void**)&c->d_fbA};
+                     (void**)&c->d_front, (void**)&c->d_fb_tables, (void**)&c->d_fbA,
+                     (void**)&c->d_sp_state, (void**)&c->d_au_state, (void**)&c->d_sp_e, (void**)&c->d_sp_f,
+                     (void**)&c->d_au_e, (void**)&c->d_pulse};
     for (void** p : ptrs) {
         if (*p) cudaFree(*p);
         *p = nullptr;
@@ -291,6 +301,54 @@ static int upload_ssb(sdrb_ctx* ctx) {
     return SDRB_OK;
 }
 
+// (Re)build the detectors' configuration and, once their buffers exist, reset their state
+// (SpectralPulseDetector::reset / AudioPulseDetector construction, ssb_processor.cpp:90-96).
+static int reset_pulse(sdrb_ctx* ctx, bool spectral, bool audio) {
+    if (spectral) pulse_cfg_spectral(&ctx->sp_cfg, ctx->cfg.sampleRate, ctx->cfg.samplesPerReading);
+    if (audio) {
+        if (!ctx->au_user_set) sdrb_audio_pulse_config_default(&ctx->au_user);
+        pulse_cfg_audio(&ctx->au_cfg, &ctx->au_user);
+    }
+    if (spectral && ctx->d_sp_state) {
+        PulseState init;
+        pulse_state_init(&init, ctx->sp_cfg);
+        std::vector<PulseState> v((size_t)ctx->n_streams, init);
+        CK(cudaMemcpy(ctx->d_sp_state, v.data(), v.size() * sizeof(PulseState), cudaMemcpyHostToDevice));
+    }
+    if (audio && ctx->d_au_state) {
+        // a new audio configuration may change the history length: the ring is sized for it
+        if (ctx->d_au_e) { cudaFree(ctx->d_au_e); ctx->d_au_e = nullptr; }
+        const size_t units = (size_t)ctx->n_streams * ctx->channels;
+        CK(cudaMalloc(&ctx->d_au_e, units * ctx->au_cfg.ringCap * sizeof(float)));
+        PulseState init;
+        pulse_state_init(&init, ctx->au_cfg);
+        std::vector<PulseState> v(units, init);
+        CK(cudaMemcpy(ctx->d_au_state, v.data(), v.size() * sizeof(PulseState), cudaMemcpyHostToDevice));
+    }
+    return SDRB_OK;
+}
+
+static int ensure_pulse_buffers(sdrb_ctx* ctx, unsigned stages) {
+    const size_t S = (size_t)ctx->n_streams, units = S * ctx->channels;
+    if (!ctx->d_pulse) {
+        CK(cudaMalloc(&ctx->d_pulse, units * ctx->max_blocks * sizeof(sdrb_pulse_result)));
+        CK(cudaMemset(ctx->d_pulse, 0, units * ctx->max_blocks * sizeof(sdrb_pulse_result)));
+    }
+    if ((stages & SDRB_STAGE_SPECTRAL_PULSE) && !ctx->d_sp_state) {
+        CK(cudaMalloc(&ctx->d_sp_state, S * sizeof(PulseState)));
+        CK(cudaMalloc(&ctx->d_sp_e, S * ctx->sp_cfg.ringCap * sizeof(float)));
+        CK(cudaMalloc(&ctx->d_sp_f, S * ctx->sp_cfg.ringCap * sizeof(float)));
+        int rc = reset_pulse(ctx, true, false);
+        if (rc != SDRB_OK) return rc;
+    }
+    if ((stages & SDRB_STAGE_AUDIO_PULSE) && !ctx->d_au_state) {
+        CK(cudaMalloc(&ctx->d_au_state, units * sizeof(PulseState)));
+        int rc = reset_pulse(ctx, false, true);
+        if (rc != SDRB_OK) return rc;
+    }
+    return SDRB_OK;
+}
+
 static int reset_state(sdrb_ctx* ctx) {
     std::vector<FftStreamState> fs(ctx->n_streams);
     for (auto& s : fs) {
@@ -305,7 +363,7 @@ static int reset_state(sdrb_ctx* ctx) {
     ctx->ssb_samples = 0;
     ctx->last_blocks = 0;
     ctx->last_stages = 0;
-    return SDRB_OK;
+    return reset_pulse(ctx, true, true);
 }
 
 extern "C" {
@@ -437,8 +495,12 @@ static int validate_process(sdrb_ctx* ctx, const void* iq, int n_blocks, unsigne
     if (!iq) return fail(ctx, SDRB_ERR_ARG, "iq is NULL");
     if (n_blocks < 1 || n_blocks > ctx->max_blocks)
         return fail(ctx, SDRB_ERR_ARG, "n_blocks %d outside [1, %d]", n_blocks, ctx->max_blocks);
-    if ((stages & ~(SDRB_STAGE_FFT | SDRB_STAGE_SSB)) || stages == 0)
-        return fail(ctx, SDRB_ERR_ARG, "stages must be a combination of SDRB_STAGE_FFT | SDRB_STAGE_SSB");
+    if ((stages & ~(SDRB_STAGE_FFT | SDRB_STAGE_SSB | SDRB_STAGE_SPECTRAL_PULSE | SDRB_STAGE_AUDIO_PULSE)) || stages == 0)
+        return fail(ctx, SDRB_ERR_ARG, "stages must be a combination of SDRB_STAGE_FFT | SDRB_STAGE_SSB | SDRB_STAGE_*_PULSE");
+    if ((stages & SDRB_STAGE_SPECTRAL_PULSE) && !(stages & SDRB_STAGE_FFT))
+        return fail(ctx, SDRB_ERR_ARG, "SDRB_STAGE_SPECTRAL_PULSE consumes the FFT records: add SDRB_STAGE_FFT");
+    if ((stages & SDRB_STAGE_AUDIO_PULSE) && !(stages & SDRB_STAGE_SSB))
+        return fail(ctx, SDRB_ERR_ARG, "SDRB_STAGE_AUDIO_PULSE consumes the PCM: add SDRB_STAGE_SSB");
     const int n = ctx->cfg.samplesPerReading;
     const size_t bps = sdrb_format_bytes(ctx->cfg.inputFormat);
     if ((stages & SDRB_STAGE_FFT) && (!is_pow2(n) || n < 2 || n > (1 << 24)))
@@ -455,6 +517,8 @@ static int validate_process(sdrb_ctx* ctx, const void* iq, int n_blocks, unsigne
         }
         if ((rc = ensure_ssb_buffers(ctx)) != SDRB_OK) return rc;
     }
+    if ((stages & (SDRB_STAGE_SPECTRAL_PULSE | SDRB_STAGE_AUDIO_PULSE)) && (rc = ensure_pulse_buffers(ctx, stages)) != SDRB_OK)
+        return rc;
     return SDRB_OK;
 }
 
@@ -551,6 +615,23 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
                               static_cast<float4*>(ctx->d_start) + f0s * C, ctx->d_ssb_state + (size_t)s0 * C,
                               ctx->d_a48 + f0s * C * m, ctx->d_pcm + f0s * C * m, ns, ctx->channels, n_blocks,
                               ctx->ssb_samples, st, &launches));
+        }
+    }
+    if (stages & (SDRB_STAGE_SPECTRAL_PULSE | SDRB_STAGE_AUDIO_PULSE)) {
+        const size_t C = (size_t)ctx->channels;
+        sdrb_pulse_result* out = ctx->d_pulse + f0s * C;
+        CK(cudaMemsetAsync(out, 0, (size_t)frames * C * sizeof(sdrb_pulse_result), st));
+        if (stages & SDRB_STAGE_SPECTRAL_PULSE) {
+            CK(launch_pulse_spectral(ctx->d_results + f0s, ctx->d_sp_state + s0, ctx->d_sp_e + (size_t)s0 * ctx->sp_cfg.ringCap,
+                                     ctx->d_sp_f + (size_t)s0 * ctx->sp_cfg.ringCap, ctx->sp_cfg, out, ns, n_blocks,
+                                     ctx->channels, st));
+            launches += 1;
+        }
+        if ((stages & SDRB_STAGE_AUDIO_PULSE) && ctx->ssb.m > 0) {
+            CK(launch_pulse_audio(ctx->d_pcm + f0s * C * ctx->ssb.m, ctx->d_au_state + (size_t)s0 * C,
+                                  ctx->d_au_e + (size_t)s0 * C * ctx->au_cfg.ringCap, ctx->au_cfg, out, ns * ctx->channels,
+                                  n_blocks, ctx->ssb.m, st));
+            launches += 1;
         }
     }
     ctx->launches += (uint64_t)launches;
@@ -651,6 +732,44 @@ int sdrb_get_results(sdrb_ctx* ctx, sdrb_frame_result* host_out, size_t capacity
     CK(cudaSetDevice(ctx->device));
     CK(cudaMemcpyAsync(host_out, ctx->d_results, nrec * sizeof(sdrb_frame_result), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    return SDRB_OK;
+}
+
+void sdrb_audio_pulse_config_default(sdrb_audio_pulse_config* c) {
+    if (!c) return;
+    // AudioPulseDetector::Config defaults (src/ssb/audio_pulse_detector.h:20-38)
+    c->sampleRate = 48000.f; c->fMin = 1500.f; c->fMax = 4000.f; c->fsEnergy = 100.f; c->smoothCutoff = 5.f;
+    c->zDefaultS = 0.666f; c->tTargetInit = 1.75f; c->dtTolS = 0.150f;
+    c->snrMin = 1.0f; c->snrRhythm = 1.1f; c->snrStrong = 2.0f; c->dispersionMax = 1.3f; c->sumNMax = 7;
+    c->liveWindowT = 4.0f; c->liveDivisor = 3.0f; c->noiseRefFar = 80; c->noiseRefNear = 40;
+}
+
+int sdrb_set_pulse_config(sdrb_ctx* ctx, const sdrb_audio_pulse_config* cfg) {
+    if (!ctx || !cfg) return SDRB_ERR_ARG;
+    if (!ctx->configured) return fail(ctx, SDRB_ERR_STATE, "sdrb_set_pulse_config before sdrb_configure");
+    if (!(cfg->fsEnergy > 0.f) || !(cfg->sampleRate > 0.f) || cfg->fsEnergy > 1.0e5f)
+        return fail(ctx, SDRB_ERR_ARG, "audio pulse config: sampleRate and fsEnergy must be positive (fsEnergy <= 1e5)");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->au_user = *cfg;
+    ctx->au_user_set = true;
+    return reset_pulse(ctx, false, true);
+}
+
+int sdrb_get_pulse_results(sdrb_ctx* ctx, sdrb_pulse_result* host_out, size_t capacity_records) {
+    if (!ctx || !ctx->configured || !(ctx->last_stages & (SDRB_STAGE_SPECTRAL_PULSE | SDRB_STAGE_AUDIO_PULSE)))
+        return fail(ctx, SDRB_ERR_STATE, "no pulse results: call sdrb_process with a SDRB_STAGE_*_PULSE stage first");
+    const size_t nrec = (size_t)ctx->n_streams * ctx->channels * ctx->last_blocks;
+    if (!host_out || capacity_records < nrec) return fail(ctx, SDRB_ERR_ARG, "pulse buffer holds %zu < %zu records", capacity_records, nrec);
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(host_out, ctx->d_pulse, nrec * sizeof(sdrb_pulse_result), cudaMemcpyDeviceToHost));
+    return SDRB_OK;
+}
+
+int sdrb_pulse_results_device(sdrb_ctx* ctx, const sdrb_pulse_result** dev_ptr) {
+    if (!ctx || !dev_ptr || !ctx->d_pulse) return fail(ctx, SDRB_ERR_STATE, "no pulse results");
+    *dev_ptr = ctx->d_pulse;
     return SDRB_OK;
 }
 

@@ -42,13 +42,15 @@ def lib():
 class OraclePulse:
     """audio=False: SpectralPulseDetector(fs_energy); audio=True: AudioPulseDetector()."""
 
-    def __init__(self, audio, fs_energy=None):
+    def __init__(self, audio, fs_energy=None, overrides=None):
         o = lib()
         cfg = PulseCfg()
         if audio:
             o.sdr_oracle_pulse_cfg_audio(C.byref(cfg))
         else:
             o.sdr_oracle_pulse_cfg_spectral(C.byref(cfg), fs_energy)
+        for k, v in (overrides or {}).items():
+            setattr(cfg, k, v)
         self.h = o.sdr_oracle_pulse_create(C.byref(cfg), int(audio))
         self.audio = audio
 
