@@ -41,8 +41,13 @@ typedef enum {
 /* Wire formats of one complex sample (interleaved I,Q).
  *  CU8 : RTL-SDR offset binary; f = (b - 127.4f) * (1/128.f)     src/ssb/ssb_demod_opt.cpp:33-44
  *  CS16: LimeSDR-style; f = s * 2^-15  (LimeSuite is a missing submodule: convention, parity unpinned)
- *  CF32: what SoapySDR hands the reference today ("CF32")        src/sdr-bridge-java-soapy.cpp:262-263 */
-typedef enum { SDRB_CU8 = 0, SDRB_CS16 = 1, SDRB_CF32 = 2 } sdrb_format;
+ *  CF32: what SoapySDR hands the reference today ("CF32")        src/sdr-bridge-java-soapy.cpp:262-263
+*  RU16: Airspy raw ADC stream, SURVEY.md 8(f) row 1: REAL 12-bit samples in uint16 at twice the complex
+ *        rate (two words per complex output sample), turned into IQ by the libairspy converter chain
+ *        (x-2048)/2048, DC removal, fs/4 translation, 47-tap half-band, delay
+ *        third_party/libairspy/libairspy/src/airspy.c:311-321, iqconverter_float.c:418-475
+ *        with its state (DC average, filter history) carried per stream across calls. */
+typedef enum { SDRB_CU8 = 0, SDRB_CS16 = 1, SDRB_CF32 = 2, SDRB_RU16 = 3 } sdrb_format;
 
 #define SDRB_STAGE_FFT 1u   /* FFTProcessor::process       src/dsp/fft_process.cpp:42-105 */
 #define SDRB_STAGE_SSB 2u   /* processSSB_opt              src/ssb/ssb_demod_opt.cpp:221-296 */

@@ -237,3 +237,21 @@ void sdr_ref_apd_process(void* h, const int16_t* pcm, int n, float* out) {
 }
 
 }  /* extern "C" */
+
+/* ------------------------------ Airspy real->IQ front end ------------------------------ */
+extern "C" {
+#include "iqconverter_float.h"
+}
+#include "filters.h"
+
+extern "C" {
+void* sdr_ref_airspy_create(void) { return iqconverter_float_create(HB_KERNEL_FLOAT, HB_KERNEL_FLOAT_LEN); }
+void sdr_ref_airspy_destroy(void* h) { iqconverter_float_free(static_cast<iqconverter_float_t*>(h)); }
+/* convert_samples_float is static in airspy.c (which needs libusb): its one-line body is restated here
+ * (third_party/libairspy/libairspy/src/airspy.c:311-321, SAMPLE_SCALE = 1/2048 from :58-62); the converter
+ * itself is the reference's own iqconverter_float.c. */
+void sdr_ref_airspy_process(void* h, const uint16_t* raw, int n_real, float* out) {
+    for (int i = 0; i < n_real; i++) out[i] = (raw[i] - 2048) * (1.0f / (1 << 11));
+    iqconverter_float_process(static_cast<iqconverter_float_t*>(h), out, n_real);
+}
+}

@@ -5,7 +5,7 @@ import os
 
 import numpy as np
 
-CU8, CS16, CF32 = 0, 1, 2
+CU8, CS16, CF32, RU16 = 0, 1, 2, 3
 STAGE_FFT, STAGE_SSB = 1, 2
 STAGE_SPECTRAL_PULSE, STAGE_AUDIO_PULSE = 4, 8
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -133,7 +133,7 @@ def format_bytes(fmt):
 
 def format_dtype(fmt):
     """numpy dtype and per-sample width of a wire format: [.., n, 2] of u8 / i16 / f32."""
-    return {CU8: np.uint8, CS16: np.int16, CF32: np.float32}[fmt]
+    return {CU8: np.uint8, CS16: np.int16, CF32: np.float32, RU16: np.uint16}[fmt]
 
 
 def _check(rc, ctx=None):

@@ -84,6 +84,10 @@ struct sdrb_ctx {
     PulseState *d_sp_state = nullptr, *d_au_state = nullptr;
     float *d_sp_e = nullptr, *d_sp_f = nullptr, *d_au_e = nullptr;
     sdrb_pulse_result* d_pulse = nullptr;
+    // Airspy real->IQ front end (inputFormat SDRB_RU16)
+    AirspyStreamState* d_air_state = nullptr;
+    float* d_air_T = nullptr;
+    cpx* d_air_iq = nullptr;
     // last call
     int last_blocks = 0;
     unsigned last_stages = 0;
@@ -123,7 +127,8 @@ static void free_buffers(sdrb_ctx* c) {
                      (void**)&c->d_sb, (void**)&c->d_est_scratch, (void**)&c->d_inc1, (void**)&c->d_win,
                      (void**)&c->d_front, (void**)&c->d_fb_tables, (void**)&c->d_fbA,
                      (void**)&c->d_sp_state, (void**)&c->d_au_state, (void**)&c->d_sp_e, (void**)&c->d_sp_f,
-                     (void**)&c->d_au_e, (void**)&c->d_pulse};
+                     (void**)&c->d_au_e, (void**)&c->d_pulse, (void**)&c->d_air_state, (void**)&c->d_air_T,
+                     (void**)&c->d_air_iq};
     for (void** p : ptrs) {
         if (*p) cudaFree(*p);
         *p = nullptr;
@@ -135,7 +140,7 @@ extern "C" {
 int sdrb_abi_version(void) { return SDRB_ABI_VERSION; }
 
 size_t sdrb_format_bytes(int format) {
-    return format == SDRB_CU8 ? 2 : (format == SDRB_CS16 ? 4 : (format == SDRB_CF32 ? 8 : 0));
+    return format == SDRB_CU8 ? 2 : (format == SDRB_CS16 || format == SDRB_RU16 ? 4 : (format == SDRB_CF32 ? 8 : 0));
 }
 
 const char* sdrb_last_error(const sdrb_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
@@ -226,7 +231,7 @@ static int check_config(sdrb_ctx* ctx, const sdrb_config* cfg) {
     if (!cfg) return fail(ctx, SDRB_ERR_ARG, "config is NULL");
     if (cfg->samplesPerReading < 1) return fail(ctx, SDRB_ERR_ARG, "samplesPerReading must be >= 1");
     if (cfg->sampleRate == 0) return fail(ctx, SDRB_ERR_ARG, "sampleRate must be > 0");
-    if (cfg->inputFormat < SDRB_CU8 || cfg->inputFormat > SDRB_CF32)
+    if (cfg->inputFormat < SDRB_CU8 || cfg->inputFormat > SDRB_RU16)
         return fail(ctx, SDRB_ERR_ARG, "inputFormat %d is not a sdrb_format", cfg->inputFormat);
     if (cfg->fftWindow < 0 || cfg->fftWindow > 1) return fail(ctx, SDRB_ERR_ARG, "fftWindow must be 0 (rectangular) or 1 (Hann)");
     if (cfg->ssbChannels < 0 || cfg->ssbChannels > 4096) return fail(ctx, SDRB_ERR_ARG, "ssbChannels must be in [0, 4096]");
@@ -363,6 +368,7 @@ static int reset_state(sdrb_ctx* ctx) {
     ctx->ssb_samples = 0;
     ctx->last_blocks = 0;
     ctx->last_stages = 0;
+    if (ctx->d_air_state) CK(cudaMemset(ctx->d_air_state, 0, (size_t)ctx->n_streams * sizeof(AirspyStreamState)));
     return reset_pulse(ctx, true, true);
 }
 
@@ -517,6 +523,14 @@ static int validate_process(sdrb_ctx* ctx, const void* iq, int n_blocks, unsigne
         }
         if ((rc = ensure_ssb_buffers(ctx)) != SDRB_OK) return rc;
     }
+    if (ctx->cfg.inputFormat == SDRB_RU16 && !ctx->d_air_state) {
+        if (n % 4) return fail(ctx, SDRB_ERR_UNSUPPORTED, "SDRB_RU16 needs samplesPerReading %% 4 == 0");
+        const size_t S = (size_t)ctx->n_streams, real = 2 * (size_t)ctx->max_blocks * n;
+        CK(cudaMalloc(&ctx->d_air_state, S * sizeof(AirspyStreamState)));
+        CK(cudaMemset(ctx->d_air_state, 0, S * sizeof(AirspyStreamState)));
+        CK(cudaMalloc(&ctx->d_air_T, S * (AIRSPY_TAIL + real) * sizeof(float)));
+        CK(cudaMalloc(&ctx->d_air_iq, S * (real / 2) * sizeof(cpx)));
+    }
     if ((stages & (SDRB_STAGE_SPECTRAL_PULSE | SDRB_STAGE_AUDIO_PULSE)) && (rc = ensure_pulse_buffers(ctx, stages)) != SDRB_OK)
         return rc;
     return SDRB_OK;
@@ -526,11 +540,22 @@ static int validate_process(sdrb_ctx* ctx, const void* iq, int n_blocks, unsigne
 // d_iq points at stream s0's first sample; device outputs are laid out [n_streams][n_blocks][...].
 static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_blocks, unsigned stages,
                        cudaStream_t st, bool time_fft) {
-    const int n = ctx->cfg.samplesPerReading, fmt = ctx->cfg.inputFormat;
-    const size_t bps = sdrb_format_bytes(fmt);
+    const int n = ctx->cfg.samplesPerReading;
+    int fmt = ctx->cfg.inputFormat;
     const int frames = ns * n_blocks;
     const size_t f0s = (size_t)s0 * n_blocks;   // first frame of the range
     int launches = 0;
+    if (fmt == SDRB_RU16) {
+        // Airspy: raw real ADC words -> cf32 through the libairspy converter chain (state carried per stream),
+        // then the CF32 kernels.  The intermediate is laid out for THIS call's n_blocks.
+        const long long real = 2LL * n_blocks * n;
+        cpx* iq_out = ctx->d_air_iq + f0s * n;
+        CK(launch_airspy_front(static_cast<const uint16_t*>(d_iq), ctx->d_air_state + s0,
+                               ctx->d_air_T + (size_t)s0 * (AIRSPY_TAIL + real), iq_out, ns, real, st, &launches));
+        d_iq = iq_out;
+        fmt = FMT_CF32;
+    }
+    const size_t bps = sdrb_format_bytes(fmt);
     if (stages & SDRB_STAGE_FFT) {
         float* power = ctx->d_power + f0s * n;
         if (time_fft && ctx->fftPath != 1) CK(cudaEventRecord(ctx->ev0, st));

@@ -91,7 +91,20 @@ struct SsbParams {
     BiquadCoef rf, hp, bp;
 };
 
+// ---------------------------------------------------------------- Airspy real->IQ front end
+// Carried converter state (iqconverter_float_t: avg, fir_queue, delay_line) as the last 48 translated
+// samples: 24 even ones for the half-band FIR (23 needed), 24 odd ones for the 12-sample delay.
+constexpr int AIRSPY_TAIL = 48;
+struct AirspyStreamState {
+    float avg;
+    float tail[AIRSPY_TAIL];   // oldest first
+    float pad[15];
+};
+
 // ---------------------------------------------------------------- launchers
+// airspy.cu : raw 12-bit real samples (uint16, 2 per complex output) -> cf32 [streams][n_real/2]
+cudaError_t launch_airspy_front(const uint16_t* d_raw, AirspyStreamState* d_state, float* d_T, cpx* d_iq,
+                                int n_streams, long long n_real, cudaStream_t st, int* launches);
 // fft16k2.cu : second-generation 16K kernel (512 threads x 32 points, TMA-staged input)
 cudaError_t launch_fft16k2(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
                            int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);

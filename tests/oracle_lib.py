@@ -57,7 +57,7 @@ class SsbxState(C.Structure):
 
 def build_oracle():
     """(Re)build the C restatement; cheap, so done on demand."""
-    srcs = [os.path.join(ORACLE_DIR, f) for f in ("sdr_oracle.c", "sdr_oracle_ext.c", "sdr_oracle_pulse.c", "sdr_oracle.h",
+    srcs = [os.path.join(ORACLE_DIR, f) for f in ("sdr_oracle.c", "sdr_oracle_ext.c", "sdr_oracle_pulse.c", "sdr_oracle_airspy.c", "sdr_oracle.h",
                                                 "sdr_oracle_pulse.h")]
     if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", ORACLE_DIR, "liboracle"], stdout=subprocess.DEVNULL)

@@ -1,0 +1,64 @@
+"""GPU parity of the Airspy real->IQ front end (inputFormat SDRB_RU16) through
+the C-ABI: raw 12-bit ADC words in, the FFT path's spectrum / records and the SSB path's PCM out, against
+oracle/sdr_oracle_airspy.c (pinned bit-exactly against the reference's iqconverter_float.c) followed by
+the pinned FFT / SSB oracle.  The converter is bit-exact, so downstream tolerances are the CF32 path's."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from test_oracle_airspy import AirspyState, oracle_airspy, synth_adc
+
+pytestmark = pytest.mark.gpu
+
+
+def _oracle_iq(raw_blocks):
+    """raw_blocks: [B, 2n] uint16 of ONE stream -> [B, n, 2] float32, state carried over the blocks."""
+    o = oracle_airspy()
+    st = AirspyState()
+    o.sdr_oracle_airspy_init(C.byref(st))
+    out = np.zeros(raw_blocks.shape, np.float32)
+    for b in range(raw_blocks.shape[0]):
+        chunk = np.ascontiguousarray(raw_blocks[b])
+        o.sdr_oracle_airspy_process(C.byref(st), chunk.ctypes.data, chunk.size, out[b].ctypes.data)
+    return out.reshape(raw_blocks.shape[0], -1, 2)
+
+
+@pytest.mark.parametrize("n,fs,S,B,calls", [(16384, 10_000_000, 3, 4, 3), (65536, 10_000_000, 2, 2, 2), (4096, 2_500_000, 2, 8, 2)])
+def test_airspy_fft_path_matches_oracle(sdrb, gpu_ctx, n, fs, S, B, calls):
+    fc = 430_000_000
+    cfg = sdrb.Config(fc, fs, n, 25, inputFormat=sdrb.RU16)
+    gpu_ctx.configure(cfg, S, B)
+    raw = np.stack([synth_adc(2 * n * B * calls, 100 + s, dc=20 + 7 * s) for s in range(S)]).reshape(S, calls, B, 2 * n)
+    iq_ref = np.stack([_oracle_iq(raw[s].reshape(calls * B, 2 * n)) for s in range(S)]).reshape(S, calls, B, n, 2)
+    for c in range(calls):
+        gpu_ctx.process(np.ascontiguousarray(raw[:, c].reshape(S, B, n, 2)), B, sdrb.STAGE_FFT)
+        res = gpu_ctx.results()
+        for s in range(S):
+            of = ol.OracleFft(fc, fs, n, 25) if c == 0 else None
+            for b in range(B):
+                ref_p = ol.oracle_power(np.ascontiguousarray(iq_ref[s, c, b]))
+                got_p = gpu_ctx.power(s, b)
+                total = float(ref_p.astype(np.float64).sum())
+                tol = 1e-5 * ref_p + 6e-7 * np.sqrt(ref_p) * np.sqrt(total) + 1e-9 * total / n
+                assert np.all(np.abs(got_p - ref_p) <= tol), (c, s, b)
+                if of is not None:
+                    e = of.evaluate(got_p)
+                    assert int(res[s, b]["peakBin"]) == e["peakBin"]
+                    assert abs(float(res[s, b]["meanSnrDb"]) - e["meanSnrDb"]) < 0.01
+
+
+def test_airspy_ssb_pcm_matches_oracle(sdrb, gpu_ctx):
+    n, fs, S, B = 16384, 2_500_000, 2, 4
+    cfg = sdrb.Config(430_000_000, fs, n, 5, inputFormat=sdrb.RU16)
+    gpu_ctx.configure(cfg, S, B)
+    raw = np.stack([synth_adc(2 * n * B, 300 + s) for s in range(S)]).reshape(S, B, 2 * n)
+    gpu_ctx.process(np.ascontiguousarray(raw.reshape(S, B, n, 2)), B, sdrb.STAGE_SSB)
+    pcm = gpu_ctx.pcm()
+    for s in range(S):
+        iq = _oracle_iq(raw[s])
+        os_ = ol.OracleSsb()
+        for b in range(B):
+            exp = os_.process(np.ascontiguousarray(iq[b]), fs, 1, 1)
+            assert np.abs(pcm[s, b].astype(int) - exp.astype(int)).max() <= 1, (s, b)
