@@ -171,7 +171,7 @@ int sdrb_create(int device, sdrb_ctx** out) {
     const char* chunk_env = getenv("SDRB_EST_CHUNK");
     ctx->est_chunk = chunk_env ? atoi(chunk_env) : 0;   // measured: chunking for L2 residency loses (0.67 vs 0.45 ms per step)
     const char* gen = getenv("SDRB_FFT16K");
-    ctx->fft16k_gen = (gen && gen[0] >= '2' && gen[0] <= '4') ? gen[0] - '0' : 2;
+    ctx->fft16k_gen = (gen && gen[0] >= '2' && gen[0] <= '5') ? gen[0] - '0' : 2;
     const std::vector<cpx> t16 = make_f2_tables();
     const std::vector<cpx> t4 = make_f4_tables();
     const std::vector<unsigned char> t3 = make_f3_tables();
@@ -183,6 +183,7 @@ int sdrb_create(int device, sdrb_ctx** out) {
         (e = cudaMalloc(&ctx->d_tables16k4, t4.size() * sizeof(cpx))) != cudaSuccess ||
         (e = cudaMemcpy(ctx->d_tables16k4, t4.data(), t4.size() * sizeof(cpx), cudaMemcpyHostToDevice)) != cudaSuccess ||
         (e = fft16k4_prepare(t4.data())) != cudaSuccess ||
+        (e = fft16k5_prepare(t4.data())) != cudaSuccess ||
         (e = cudaMalloc(&ctx->d_sine, SYNTH_SINE_N * sizeof(int16_t))) != cudaSuccess ||
         (e = cudaMemcpy(ctx->d_sine, synth_sine_table(), SYNTH_SINE_N * sizeof(int16_t), cudaMemcpyHostToDevice)) != cudaSuccess) {
         fail(nullptr, SDRB_ERR_CUDA, "table upload: %s", cudaGetErrorString(e));
@@ -570,9 +571,11 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
                 const int nf = frames - f0 < chunk ? frames - f0 : chunk;
                 const void* src = static_cast<const unsigned char*>(d_iq) + (size_t)f0 * n * bps;
                 if (time_fft && f0 == 0) CK(cudaEventRecord(ctx->ev0, st));
-                if (ctx->fft16k_gen == 4)
+                if (ctx->fft16k_gen == 5 && !ctx->front)
+                    CK(launch_fft16k5(fmt, src, power + (size_t)f0 * n, ctx->d_tables16k4, nf, ctx->sm_count, st));
+                else if (ctx->fft16k_gen == 4)
                     CK(launch_fft16k4(fmt, src, power + (size_t)f0 * n, ctx->d_tables16k4, nf, ctx->sm_count, st, ctx->front, ctx->d_win));
-                else if (ctx->fft16k_gen == 2)
+                else if (ctx->fft16k_gen == 2 || ctx->fft16k_gen == 5)
                     CK(launch_fft16k2(fmt, src, power + (size_t)f0 * n, ctx->d_tables16k, nf, ctx->sm_count, st, ctx->front, ctx->d_win));
                 else
                     CK(launch_fft16k3(fmt, src, power + (size_t)f0 * n, ctx->d_tables16k3, nf, ctx->sm_count, st, ctx->front, ctx->d_win));

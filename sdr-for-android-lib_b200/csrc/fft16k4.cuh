@@ -205,4 +205,56 @@ SDRB_HD void f4_phase3(int t, const cpx* E, TW3 tw3, float* __restrict__ out) {
     }
 }
 
+// ---- the same phases 2 and 3 cut into load / compute / store pieces (both columns in 32 registers), so
+// that a kernel can group its shared-memory accesses into explicit exchange sections (fft16k5.cu)
+SDRB_HD void f4_p2_load(int t, const cpx* E, cpx* v) {
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int q = t + 256 * h;
+        const cpx* base = E + (q >> 4) * F4_PITCH + (q & 15);
+#pragma unroll
+        for (int b = 0; b < 16; b++) v[16 * h + b] = base[b * 16];
+    }
+}
+SDRB_HD void f4_p2_compute(cpx* v) {
+    fft16(v);
+    fft16(v + 16);
+}
+SDRB_HD void f4_p2_store(int t, cpx* E, const cpx* v) {
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int q = t + 256 * h;
+        cpx* base = E + (q >> 4) * F4_PITCH + (q & 15);
+#pragma unroll
+        for (int kb = 0; kb < 16; kb++) base[kb * 16] = v[16 * h + rev16(kb)];
+    }
+}
+SDRB_HD void f4_p3_load(int t, const cpx* E, cpx* v) {
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int q = t + 256 * h;
+        const cpx* base = E + (q & 31) * F4_PITCH + (q >> 5) * 16;
+#pragma unroll
+        for (int c = 0; c < 16; c++) v[16 * h + c] = base[c];
+    }
+}
+template <int P, class TW3>
+SDRB_HD void f4_p3_finish(int t, cpx* v, TW3 tw3, float* __restrict__ out) {
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int q = t + 256 * h;
+        const int ka = q & 31, kb = q >> 5;
+        cpx* w = v + 16 * h;
+#pragma unroll
+        for (int c = 1; c < 16; c++) w[c] = cmul(w[c], tw3(kb, c));
+        fft16(w);
+        const int k0 = 2 * (ka + 32 * kb) + P;
+#pragma unroll
+        for (int kc = 0; kc < 16; kc++) {
+            const cpx x = w[rev16(kc)];
+            out[(k0 + 1024 * kc + 8192) & 16383] = x.x * x.x + x.y * x.y;
+        }
+    }
+}
+
 }  // namespace sdrb

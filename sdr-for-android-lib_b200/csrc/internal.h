@@ -117,6 +117,10 @@ cudaError_t fft16k3_prepare();
 cudaError_t launch_fft16k4(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
                            int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);
 cudaError_t fft16k4_prepare(const cpx* host_tables);
+// fft16k5.cu : fifth-generation 16K kernel (the two jobs of fft16k4 as ping-ponging warp groups of one CTA)
+cudaError_t launch_fft16k5(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
+                           int sm_count, cudaStream_t st);
+cudaError_t fft16k5_prepare(const cpx* host_tables);
 // fft_any.cu : generic power-of-two path (N != 16384)
 cudaError_t launch_fft_generic(int fmt, const void* iq, float* power, cpx* scratch_a, cpx* scratch_b,
                                const cpx* twiddles, int n, int n_frames, cudaStream_t st, int* launches);

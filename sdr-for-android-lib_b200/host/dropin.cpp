@@ -87,7 +87,9 @@ void FFTProcessor::process(const std::complex<float>* input_buf, uint32_t input_
     ensureContext(static_cast<int>(input_len));
     if (sdr_bridge_internal::isCenterFrequencyChanged.exchange(false))
         SDRB_TRY(ctx_, sdrb_set_center_frequency(ctx_, -1, cfg_.centerFrequency));
-    SDRB_TRY(ctx_, sdrb_process_host(ctx_, input_buf, 1, SDRB_STAGE_FFT, &last_, spectrum_.data(), nullptr));
+    SDRB_TRY(ctx_, sdrb_process_host(ctx_, input_buf, 1, SDRB_STAGE_FFT | SDRB_STAGE_SPECTRAL_PULSE, &last_,
+                                     spectrum_.data(), nullptr));
+    SDRB_TRY(ctx_, sdrb_get_pulse_results(ctx_, &pulse_, 1));
 }
 
 // ------------------------------------------------------------------ processSSB_opt
@@ -119,9 +121,28 @@ void sdrbSsbReset() {
 
 bool lastBlockContainsPulse() { return false; }
 
+namespace {
+void ssb_run(std::vector<std::complex<float>>& iq, uint32_t sampleRate, bool upperSideband,
+             std::vector<int16_t>& pcmOut, int mode, bool with_pulse, const sdrb_audio_pulse_config* new_cfg,
+             sdrb_pulse_result* pulse_out);
+}
+
 void processSSB_opt(std::vector<std::complex<float>> iq, uint32_t sampleRate, bool upperSideband,
                     std::vector<int16_t>& pcmOut, bool& pulse, int mode) {
     (void)pulse;                                    // never written: src/ssb/ssb_demod_opt.cpp:221-296
+    ssb_run(iq, sampleRate, upperSideband, pcmOut, mode, false, nullptr, nullptr);
+}
+
+void sdrbSsbProcessWithPulse(std::vector<std::complex<float>> iq, uint32_t sampleRate, bool upperSideband,
+                             std::vector<int16_t>& pcmOut, int mode, const sdrb_audio_pulse_config* new_cfg,
+                             sdrb_pulse_result* pulse_out) {
+    ssb_run(iq, sampleRate, upperSideband, pcmOut, mode, true, new_cfg, pulse_out);
+}
+
+namespace {
+void ssb_run(std::vector<std::complex<float>>& iq, uint32_t sampleRate, bool upperSideband,
+             std::vector<int16_t>& pcmOut, int mode, bool with_pulse, const sdrb_audio_pulse_config* new_cfg,
+             sdrb_pulse_result* pulse_out) {
     SsbSingleton& S = ssb_one();
     std::lock_guard<std::mutex> lock(S.mu);         // the reference is non-re-entrant (statics)
     pcmOut.clear();
@@ -144,9 +165,12 @@ void processSSB_opt(std::vector<std::complex<float>> iq, uint32_t sampleRate, bo
     const int m = sdrb_pcm_per_block(S.ctx);
     if (m < 0) raise(S.ctx, "sdrb_pcm_per_block", m);
     pcmOut.resize(static_cast<size_t>(m));
-    SDRB_TRY(S.ctx, sdrb_process_host(S.ctx, iq.data(), 1, SDRB_STAGE_SSB, nullptr, nullptr,
-                                      m ? pcmOut.data() : nullptr));
+    if (new_cfg) SDRB_TRY(S.ctx, sdrb_set_pulse_config(S.ctx, new_cfg));
+    const unsigned stages = SDRB_STAGE_SSB | (with_pulse ? SDRB_STAGE_AUDIO_PULSE : 0u);
+    SDRB_TRY(S.ctx, sdrb_process_host(S.ctx, iq.data(), 1, stages, nullptr, nullptr, m ? pcmOut.data() : nullptr));
+    if (with_pulse && pulse_out) SDRB_TRY(S.ctx, sdrb_get_pulse_results(S.ctx, pulse_out, 1));
 }
+}  // namespace
 
 // ------------------------------------------------------------------ SSBProcessor
 SSBProcessor::SSBProcessor() : mode_src_([] {
@@ -168,6 +192,21 @@ void SSBProcessor::startProcessing(PcmDataCallback pcm_cb) {
     if (running_.exchange(true)) return;            // already running: ignored like :28-31
     on_pcm_ = std::move(pcm_cb);
     worker_ = std::thread([this] { workerLoop(); });
+}
+
+void SSBProcessor::startProcessing(PcmDataCallback pcm_cb, std::function<void(float, int)> pulse_cb) {
+    if (running_) return;
+    on_pulse_ = std::move(pulse_cb);                // :36-49
+    startProcessing(std::move(pcm_cb));
+}
+
+void SSBProcessor::setPulseConfig(const AudioPulseDetector::Config& c) {
+    std::lock_guard<std::mutex> lock(mu_);           // applied by the worker before the next block, :69-74,90-96
+    pending_cfg_ = sdrb_audio_pulse_config{c.sampleRate, c.fMin, c.fMax, c.fsEnergy, c.smoothCutoff, c.zDefaultS,
+                                           c.tTargetInit, c.dtTolS, c.snrMin, c.snrRhythm, c.snrStrong,
+                                           c.dispersionMax, c.sumNMax, c.liveWindowT, c.liveDivisor, c.noiseRefFar,
+                                           c.noiseRefNear};
+    pending_cfg_set_ = true;
 }
 
 void SSBProcessor::stopProcessing() {
@@ -193,6 +232,8 @@ void SSBProcessor::workerLoop() {
     for (;;) {
         SSB_Data job;
         int mode;
+        bool have_cfg = false;
+        sdrb_audio_pulse_config new_cfg{};
         {
             std::unique_lock<std::mutex> lock(mu_);
             cv_.wait(lock, [this] { return !pending_.empty() || !running_; });
@@ -203,10 +244,14 @@ void SSBProcessor::workerLoop() {
             job = std::move(pending_.front());
             pending_.pop_front();
             mode = mode_src_();
+            have_cfg = pending_cfg_set_;
+            if (have_cfg) { new_cfg = pending_cfg_; pending_cfg_set_ = false; }
         }
         std::vector<int16_t> pcm;
-        bool pulse = false;
-        processSSB_opt(std::move(job.iq), job.sampleRate, true, pcm, pulse, mode);   // :103
+        sdrb_pulse_result pr{};
+        // processSSB_opt (:103) + pulseDetector_.process(pcm) (:109) in one GPU call
+        sdrbSsbProcessWithPulse(std::move(job.iq), job.sampleRate, true, pcm, mode, have_cfg ? &new_cfg : nullptr, &pr);
         if (on_pcm_ && !pcm.empty()) on_pcm_(pcm);                                      // :105-107
+        if (on_pulse_) on_pulse_(pr.audioLastSnr, pr.audioLiveEtat);                    // :110-113
     }
 }

@@ -65,7 +65,13 @@ int main(int argc, char** argv) {
         ssb.setSoundModeSource([mode] { return mode; });
         std::vector<std::vector<int16_t>> queued;
         std::mutex qm;
-        ssb.startProcessing([&](const std::vector<int16_t>& pcm) { std::lock_guard<std::mutex> l(qm); queued.push_back(pcm); });
+        int pulse_calls = 0, pulse_bad = 0;
+        ssb.setPulseConfig(AudioPulseDetector::Config{});
+        ssb.startProcessing([&](const std::vector<int16_t>& pcm) { std::lock_guard<std::mutex> l(qm); queued.push_back(pcm); },
+                            [&](float strength, int etat) {   // (FI)V payload, src/ssb/ssb_processor.cpp:110-113
+                                pulse_calls++;
+                                if (!(strength >= 0.f) || etat < 0 || etat > 5) pulse_bad++;
+                            });
         for (int b = 0; b < B; b++) {
             ssb.enqueueData(std::vector<std::complex<float>>(iq + (size_t)b * n, iq + (size_t)(b + 1) * n), fs);
             for (int spin = 0; spin < 20000; spin++) {   // pace like a live source: never overflow the 3-deep queue
@@ -74,7 +80,9 @@ int main(int argc, char** argv) {
             }
         }
         ssb.stopProcessing();
-        int32_t same = (int)queued.size() == B && ssb.droppedBlocks() == 0;
+        int32_t same = (int)queued.size() == B && ssb.droppedBlocks() == 0 && pulse_calls == B && pulse_bad == 0;
+        // the spectral detector saw every frame's best-1 kHz sigma
+        same = same && fft.lastPulse().spectralSnrSigma == fft.getBest1kHzSnrSigma() && fft.lastPulse().spectralLiveEtat >= 0;
         for (int b = 0; same && b < B; b++) same = queued[b] == direct[b];
         put(f, &same, sizeof same);
     } catch (const std::exception& e) {

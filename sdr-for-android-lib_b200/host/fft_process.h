@@ -61,6 +61,11 @@ public:
 
     // additive: the whole record of the last frame (frame-local internals included)
     const sdrb_frame_result& lastRecord() const { return last_; }
+    // additive: SpectralPulseDetector state after the last frame.  The bridge's
+    //   spectralPulseDetector.process(best1kHzSnrSigma, best1kFreqHz); liveEtat(); estimatedFreqHz()
+    // (src/sdr-bridge-java-soapy.cpp:477-487) becomes a read of this record: the detector runs on the GPU
+    // in the same call (SDRB_STAGE_SPECTRAL_PULSE).
+    const sdrb_pulse_result& lastPulse() const { return pulse_; }
     // additive: CUDA device of the context created by the first process() (default 0)
     void setDevice(int device) { device_ = device; }
 
@@ -72,5 +77,6 @@ private:
     int ctx_n_ = 0;                  // FFT length the context is configured for
     sdrb_ctx* ctx_ = nullptr;
     sdrb_frame_result last_{};
+    sdrb_pulse_result pulse_{};
     std::vector<float> spectrum_;
 };

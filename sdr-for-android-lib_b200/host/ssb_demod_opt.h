@@ -23,3 +23,11 @@ bool lastBlockContainsPulse();
 // reset that forgets the carried filter state (the reference can only do that by restarting).
 void sdrbSsbSetDevice(int device);
 void sdrbSsbReset();
+
+// additive: processSSB_opt followed by the AudioPulseDetector step the SSB worker runs on the PCM
+// (src/ssb/ssb_processor.cpp:103-113), in one GPU call; *pulse_out receives the detector's state after
+// this block.  new_cfg (may be NULL) rebuilds the detector first, like setPulseConfig.
+#include "../../include/sdr_b200.h"
+void sdrbSsbProcessWithPulse(std::vector<std::complex<float>> iq, uint32_t sampleRate, bool upperSideband,
+                             std::vector<int16_t>& pcmOut, int mode, const sdrb_audio_pulse_config* new_cfg,
+                             sdrb_pulse_result* pulse_out);

@@ -3,9 +3,9 @@
 // drop-oldest, :58-60) feeding a worker thread that runs processSSB_opt(upper = true,
 // mode = BridgeConfig sound mode) and hands the PCM to the callback (:99-107).
 //
-// The audio pulse detector that the reference runs after the callback (:109-113) is a
-// SURVEY.md 8(f) "next" row; until it is built here the pulse callback overload is not offered
-// (nothing is faked).  The sound mode comes from setSoundModeSource(); when this header is
+// The audio pulse detector that the reference runs after the callback (:109-113) runs on the GPU in
+// the same call (SDRB_STAGE_AUDIO_PULSE); its (lastPulseStrength, liveEtat) pair goes to the pulse
+// callback exactly like :110-113, and setPulseConfig rebuilds it like :69-74,90-96.  The sound mode comes from setSoundModeSource(); when this header is
 // compiled inside the reference tree (SDRB_USE_BRIDGE_CONFIG defined) it defaults to
 // BridgeConfig::getInstance().getSoundMode() exactly like src/ssb/ssb_processor.cpp:101.
 #pragma once
@@ -18,6 +18,9 @@
 #include <mutex>
 #include <thread>
 #include <vector>
+
+#include "../../include/sdr_b200.h"
+#include "audio_pulse_detector.h"
 
 struct SSB_Data {
     std::vector<std::complex<float>> iq;
@@ -32,6 +35,9 @@ public:
     ~SSBProcessor();
 
     void startProcessing(PcmDataCallback pcm_cb);
+    void startProcessing(PcmDataCallback pcm_cb, std::function<void(float, int)> pulse_cb);   // :23, :36-49
+    void setPulseConfig(const AudioPulseDetector::Config& cfg);                               // :69-74
+    float getAmbientEnergy() const { return 0.f; }                                            // src/ssb/ssb_processor.h:34
     void stopProcessing();
     void enqueueData(std::vector<std::complex<float>>&& iq_data, uint32_t sample_rate);
     float getCurrentRatio() const { return 0.f; }          // src/ssb/ssb_processor.h:35
@@ -43,6 +49,9 @@ public:
 private:
     void workerLoop();
     PcmDataCallback on_pcm_;
+    std::function<void(float, int)> on_pulse_;
+    sdrb_audio_pulse_config pending_cfg_{};
+    bool pending_cfg_set_ = false;
     std::function<int()> mode_src_;
     std::deque<SSB_Data> pending_;
     std::mutex mu_;
