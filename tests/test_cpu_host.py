@@ -158,3 +158,14 @@ def test_dropin_front_end_exports_reference_interface():
     undefined = [l.split()[-1] for l in syms.splitlines() if " U " in l]
     assert any(u.startswith("sdrb_process_host") for u in undefined)
     assert not any(u.startswith("cuda") or u.startswith("cu") and u[2:3].isupper() for u in undefined)
+
+
+def test_bridge_chunker_and_replay(tmp_path):
+    """host/iq_chunker.h: exact blocks from ragged reads, drop-oldest at 20, 60 ms
+    consumer wait, file replay and batch assembly — the reader thread of src/sdr-bridge-java-soapy.cpp:496-575."""
+    import subprocess
+    exe = str(tmp_path / "chunker_test")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-pthread", "-I", os.path.join(ROOT, "sdr-for-android-lib_b200", "host"),
+                    "-o", exe, os.path.join(ROOT, "tests", "cpp", "chunker_test.cpp")], check=True)
+    r = subprocess.run([exe, str(tmp_path / "cap.iq")], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "chunker OK" in r.stdout, r.stdout + r.stderr
