@@ -193,6 +193,20 @@ def run_reference_arm(args):
 
 
 # ----------------------------------------------------------------------------- our arm
+FFT_KERNEL = {"3": "k_fft16k3<CU8>", "4": "k_fft16k4<CU8>", "5": "k_fft16k5<CU8>"}.get(
+    os.environ.get("SDRB_FFT16K", "2")[:1], "k_fft16k2<CU8>")
+
+
+def ncu_traffic_bytes():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, from the committed
+    `ncu --set full` capture of this same command (profiles/r01_traffic.json); None if not captured."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            return json.load(f).get(FFT_KERNEL)
+    except (OSError, ValueError):
+        return None
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -317,7 +331,7 @@ def run_ours(args):
                        "l2": f"{n_batches} alternating batches of {S * B * n * BYTES_IN >> 20} MiB in / "
                              f"{S * B * n * 4 >> 20} MiB out per step (> 126 MB L2)"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "kernel": "k_fft16k2<CU8>",
+                         "frac": achieved / peak, "traffic": ncu_traffic_bytes(), "kernel": FFT_KERNEL,
                          "kernel_ms": k_ms, "readings_per_launch": fft_frames,
                          "algorithmic_bytes_per_launch": ALGO_BYTES * fft_frames * n,
                          "peak_source": peak_src},

@@ -125,13 +125,13 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
             f2_phase1_load<FMT>(t, in + (size_t)f * F2_N, v);
         }
         if (FRONT) f2_front<FRONT>(t, v, win, red);
-        f2_phase1_compute(t, TP, v);
-        __syncthreads();  // E is free (previous phase 3 done) and the stage has been consumed
+        fft32(v);
+        __syncthreads();  // E is free (previous phase 3 has read it) and the stage has been consumed
         if (kStaged && t == 0 && f + (int)gridDim.x < n_frames) {
             mbar_expect_tx(bar, F2Smem<FMT>::kStageBytes);
             bulk_g2s(stage, in + (size_t)(f + gridDim.x) * F2_N, F2Smem<FMT>::kStageBytes, bar);
         }
-        f2_phase1_store(t, E, v);
+        f2_phase1_twiddle_store(t, TP, v, E);   // twiddle W_N^(t ka) and exchange store, interleaved
         __syncthreads();
         f2_phase2(t, E);
         __syncthreads();

@@ -134,6 +134,22 @@ SDRB_HD void f2_phase1_compute(int t, const cpx* TP, cpx* v) {
         v[slot32(k)] = cmul(v[slot32(k)], w[k]);
     }
 }
+// The same twiddle pass with the exchange store folded in: each value is stored as soon as it is final, so the
+// 32 stores spread over the twiddle arithmetic instead of bursting into the load/store queue after it.
+SDRB_HD void f2_phase1_twiddle_store(int t, const cpx* TP, cpx* v, cpx* E) {
+    cpx P[5];
+#pragma unroll
+    for (int j = 0; j < 5; j++) P[j] = TP[j * 512 + t];
+    cpx w[32];
+    E[t] = v[0];
+#pragma unroll
+    for (int k = 1; k < 32; k++) {
+        const int low = k & (-k);
+        const int j = low == 1 ? 0 : (low == 2 ? 1 : (low == 4 ? 2 : (low == 8 ? 3 : 4)));
+        w[k] = (k == low) ? P[j] : cmul(w[k - low], P[j]);
+        E[k * F2_PITCH + t] = cmul(v[slot32(k)], w[k]);
+    }
+}
 template <int FMT>
 SDRB_HD void f2_phase1(int t, const typename Ingest2<FMT>::raw_t* in, const cpx* TP, cpx* v) {
     f2_phase1_load<FMT>(t, in, v);

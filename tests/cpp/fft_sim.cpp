@@ -66,8 +66,9 @@ int main() {
         std::vector<float> out2(N, -1.0f);
         for (int t = 0; t < F2_THREADS; t++) {
             cpx v[32];
-            f2_phase1<FMT_CU8>(t, raw.data(), TP, v);
-            f2_phase1_store(t, E2.data(), v);
+            f2_phase1_load<FMT_CU8>(t, raw.data(), v);   // the kernel's sequence: load, DFT32, twiddle + store
+            fft32(v);
+            f2_phase1_twiddle_store(t, TP, v, E2.data());
         }
         for (int t = 0; t < F2_THREADS; t++) f2_phase2(t, E2.data());
         auto tw = [T2b](int kb, int c) { return T2b[kb * 16 + c]; };
