@@ -27,7 +27,7 @@ struct StateBlobHeader {
     int32_t n_streams, rfMode;
     uint64_t ssb_samples;     // NCO phase origin of the extended SSB chain
 };
-constexpr int kMaxChunks = 8;
+constexpr int kMaxChunks = 32;
 constexpr uint32_t kBlobMagic = 0x53445242u;  // "SDRB"
 }  // namespace
 
@@ -107,7 +107,8 @@ struct sdrb_ctx {
     cudaEvent_t ev_chunk[4] = {}, ev_aux = nullptr;
     // host-to-host pipeline (sdrb_process_host)
     cudaStream_t s_in = nullptr, s_out = nullptr;
-    cudaEvent_t ev_in[8] = {}, ev_done[8] = {};
+    cudaEvent_t ev_in[32] = {}, ev_done[32] = {};
+    int host_chunks = 8;        // SDRB_HOST_CHUNKS: pipeline depth of sdrb_process_host
 };
 
 static int fail(sdrb_ctx* c, int code, const char* fmt, ...) {
@@ -177,6 +178,8 @@ int sdrb_create(int device, sdrb_ctx** out) {
     // constant tables: 16K twiddles and the synthetic source's sine table
     const char* chunk_env = getenv("SDRB_EST_CHUNK");
     ctx->est_chunk = chunk_env ? atoi(chunk_env) : 0;   // measured: chunking for L2 residency loses (0.67 vs 0.45 ms per step)
+    const char* hc_env = getenv("SDRB_HOST_CHUNKS");
+    if (hc_env) ctx->host_chunks = atoi(hc_env);
     const char* ov_env = getenv("SDRB_EST_OVERLAP");
     ctx->est_overlap = ov_env && ov_env[0] == '1';
     const char* gen = getenv("SDRB_FFT16K");
@@ -749,7 +752,8 @@ int sdrb_process_host(sdrb_ctx* ctx, const void* iq_host, int n_blocks, unsigned
             CK(cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming));
         }
     }
-    const int chunks = S < kMaxChunks ? S : kMaxChunks;
+    const int want = ctx->host_chunks < 1 ? 1 : (ctx->host_chunks > kMaxChunks ? kMaxChunks : ctx->host_chunks);
+    const int chunks = S < want ? S : want;
     const size_t stream_in = (size_t)n_blocks * n * bps;          // bytes of one stream's IQ
     const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 0;
     cudaStream_t st = ctx->stream;
