@@ -47,15 +47,26 @@ k_airspy_dc(const uint16_t* __restrict__ raw, AirspyStreamState* __restrict__ st
     const uint4* in = reinterpret_cast<const uint4*>(raw + (size_t)s * n_real);
     float4* out = reinterpret_cast<float4*>(t + AIRSPY_TAIL);
     const long long n8 = n_real >> 3;
-    for (long long i = 0; i < n8; i++) {
-        const uint4 w = __ldg(in + i);
-        float4 a, b;
-        a.x = air_step(w.x & 0xffffu, avg, 0); a.y = air_step(w.x >> 16, avg, 1);
-        a.z = air_step(w.y & 0xffffu, avg, 2); a.w = air_step(w.y >> 16, avg, 3);
-        b.x = air_step(w.z & 0xffffu, avg, 0); b.y = air_step(w.z >> 16, avg, 1);
-        b.z = air_step(w.w & 0xffffu, avg, 2); b.w = air_step(w.w >> 16, avg, 3);
-        out[2 * i] = a;
-        out[2 * i + 1] = b;
+    // the recurrence is latency-bound on its own (three dependent operations per sample); the loads must not add
+    // to that chain, so eight 16-byte loads (64 samples) are in flight ahead of the arithmetic
+    constexpr int PF = 8;
+    uint4 w[PF];
+#pragma unroll
+    for (int k = 0; k < PF; k++) w[k] = k < n8 ? __ldg(in + k) : make_uint4(0, 0, 0, 0);
+    for (long long i = 0; i < n8; i += PF) {
+#pragma unroll
+        for (int k = 0; k < PF; k++) {
+            if (i + k >= n8) break;
+            const uint4 c = w[k];
+            if (i + k + PF < n8) w[k] = __ldg(in + i + k + PF);
+            float4 a, b;
+            a.x = air_step(c.x & 0xffffu, avg, 0); a.y = air_step(c.x >> 16, avg, 1);
+            a.z = air_step(c.y & 0xffffu, avg, 2); a.w = air_step(c.y >> 16, avg, 3);
+            b.x = air_step(c.z & 0xffffu, avg, 0); b.y = air_step(c.z >> 16, avg, 1);
+            b.z = air_step(c.w & 0xffffu, avg, 2); b.w = air_step(c.w >> 16, avg, 3);
+            out[2 * (i + k)] = a;
+            out[2 * (i + k) + 1] = b;
+        }
     }
     st->avg = avg;
     // the new tail: the last AIRSPY_TAIL translated samples (this thread wrote them; n_real >= AIRSPY_TAIL or

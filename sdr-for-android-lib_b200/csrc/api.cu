@@ -476,6 +476,7 @@ static int ensure_fft_buffers(sdrb_ctx* ctx) {
         size_t group = kFourStepL2Bytes / ((size_t)n * sizeof(cpx));
         if (group < 1) group = 1;
         if (group > frames) group = frames;
+        if (group < frames) group = (size_t)fft_big_best_group(n, (int)group);
         ctx->fb_group = (int)group;
         CK(cudaMalloc(&ctx->d_fbA, group * (size_t)n * sizeof(cpx)));
         if (ctx->front) CK(cudaMalloc(&ctx->d_front, group * (size_t)n * sizeof(cpx)));

@@ -63,30 +63,50 @@ k_fbA(const typename Ingest2<FMT>::raw_t* __restrict__ in, cpx* __restrict__ A, 
     fbA_pass1<R>(t, S, TLO, THI, TB, n2_0, A + frame * N);
 }
 
+// Persistent: a CTA walks row groups (tile = frame * L/16 + group; the groups of A' are contiguous, so the tile's
+// source is A + tile * kElemsB).  Once pass 1 has pulled its values into registers the shared-memory tile is free,
+// so the bulk copy of the NEXT tile is issued there and lands under pass 1's arithmetic and global stores.
 template <int R>
 __global__ void __launch_bounds__(FbGeom<R>::kThreads)
-k_fbB(const cpx* __restrict__ A, float* __restrict__ out, const cpx* __restrict__ tables) {
+k_fbB(const cpx* __restrict__ A, float* __restrict__ out, const cpx* __restrict__ tables, int n_tiles) {
     typedef FbGeom<R> G;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     cpx* W = reinterpret_cast<cpx*>(smem_raw);
     cpx* TL = W + G::kElemsB;
     unsigned long long* bar = reinterpret_cast<unsigned long long*>(TL + G::kTL);
     const int t = threadIdx.x;
-    const size_t frame = blockIdx.y;
-    const int g = blockIdx.x;
     constexpr size_t N = (size_t)G::L * G::L;
+    constexpr int kGroups = G::L / 16;
     constexpr unsigned kBytes = G::kElemsB * sizeof(cpx);
+    int tile = blockIdx.x;
     if (t == 0) {
         fb_mbar_init(bar, 1);
-        fb_mbar_expect_tx(bar, kBytes);
-        fb_bulk_g2s(W, A + frame * N + (size_t)g * G::kElemsB, kBytes, bar);
+        if (tile < n_tiles) {
+            fb_mbar_expect_tx(bar, kBytes);
+            fb_bulk_g2s(W, A + (size_t)tile * G::kElemsB, kBytes, bar);
+        }
     }
     for (int i = t; i < G::kTL; i += G::kThreads) TL[i] = tables[i];
     __syncthreads();
-    fb_mbar_wait(bar, 0);
-    fbB_pass0<R>(t, W, TL);
-    __syncthreads();
-    fbB_pass1<R>(t, W, g * 16, out + frame * N);
+    unsigned parity = 0;
+    for (; tile < n_tiles; tile += gridDim.x) {
+        fb_mbar_wait(bar, parity);
+        parity ^= 1u;
+        fbB_pass0<R>(t, W, TL);
+        __syncthreads();
+        cpx v[R];
+        fbB_pass1_load<R>(t, W, v);
+        __syncthreads();   // every thread holds its values: the tile buffer is free
+        const int next = tile + (int)gridDim.x;
+        if (t == 0 && next < n_tiles) {
+            // pass 0 wrote the tile through the generic proxy; order those writes before the async-proxy refill
+            asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+            fb_mbar_expect_tx(bar, kBytes);
+            fb_bulk_g2s(W, A + (size_t)next * G::kElemsB, kBytes, bar);
+        }
+        const int frame = tile / kGroups, g = tile % kGroups;
+        fbB_pass1_finish<R>(t, v, g * 16, out + (size_t)frame * N);
+    }
 }
 
 template <int R>
@@ -124,8 +144,45 @@ static cudaError_t fb_launch(int fmt, const void* iq, float* power, cpx* A, cons
         case FMT_CF32: k_fbA<R, FMT_CF32><<<grid, G::kThreads, FbSmem<R>::kA, st>>>(static_cast<const cpx*>(iq), A, tables); break;
         default: return cudaErrorInvalidValue;
     }
-    k_fbB<R><<<grid, G::kThreads, FbSmem<R>::kB, st>>>(A, power, tables);
+    // persistent rows kernel: as many CTAs as fit (R = 32: one 128 KiB tile per SM; R = 16: 32 KiB tiles, several per SM)
+    static int ctas_per_sm = 0, sms = 0;
+    if (!ctas_per_sm) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, k_fbB<R>, G::kThreads, FbSmem<R>::kB) != cudaSuccess ||
+            ctas_per_sm < 1)
+            ctas_per_sm = 1;
+    }
+    const int n_tiles = (G::L / 16) * n_frames;
+    const int gridB = n_tiles < ctas_per_sm * sms ? n_tiles : ctas_per_sm * sms;
+    k_fbB<R><<<gridB, G::kThreads, FbSmem<R>::kB, st>>>(A, power, tables, n_tiles);
     return cudaGetLastError();
+}
+
+// Frames per group (<= max_group, the L2 budget) whose row-group count fills whole waves of the persistent
+// rows kernel best: the kernel runs ceil(tiles / slots) rounds, so a group just over a multiple of `slots`
+// wastes most of a round (1M points, 12 frames: 768 tiles on 148 slots = 5.19 -> 6 rounds; 9 frames: 3.89 -> 4).
+template <int R>
+static int fb_best_group(int max_group) {
+    typedef FbGeom<R> G;
+    int dev = 0, sms = 148, cps = 1;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cps, k_fbB<R>, G::kThreads, FbSmem<R>::kB) != cudaSuccess || cps < 1) cps = 1;
+    const int slots = sms * cps, per_frame = G::L / 16;
+    int best = max_group;
+    double best_eff = 0.0;
+    for (int g = max_group; g >= 1 && g >= max_group / 2; g--) {
+        const int tiles = g * per_frame, rounds = (tiles + slots - 1) / slots;
+        const double eff = (double)tiles / ((double)rounds * slots);
+        if (eff > best_eff + 1e-9) { best_eff = eff; best = g; }
+    }
+    return best;
+}
+int fft_big_best_group(int n, int max_group) {
+    if (max_group <= 1) return 1;
+    return n == 65536 ? fb_best_group<16>(max_group) : (n == 1048576 ? fb_best_group<32>(max_group) : max_group);
 }
 
 // n_frames <= the number of frames the intermediate A holds (the caller loops over groups).

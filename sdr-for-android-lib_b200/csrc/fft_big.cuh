@@ -123,13 +123,16 @@ SDRB_HD void fbB_pass0(int t, cpx* W, const cpx* TL) {
 // ---- kernel B, pass 1: row rho = t % 16, block b1 = t / 16.  DFT_R over q gives
 // X[k1 + L k2], k2 = b1 + R k'; power (:85) and fftshift (:92-97) folded into the store.
 template <int R>
-SDRB_HD void fbB_pass1(int t, const cpx* W, int k1_0, float* __restrict__ out_frame) {
+SDRB_HD void fbB_pass1_load(int t, const cpx* W, cpx* v) {
+    const int rho = t & 15, b1 = t >> 4;
+#pragma unroll
+    for (int q = 0; q < R; q++) v[q] = W[(q + R * b1) * 16 + rho];
+}
+template <int R>
+SDRB_HD void fbB_pass1_finish(int t, cpx* v, int k1_0, float* __restrict__ out_frame) {
     typedef FbGeom<R> G;
     constexpr int N = G::L * G::L;
     const int rho = t & 15, b1 = t >> 4;
-    cpx v[R];
-#pragma unroll
-    for (int q = 0; q < R; q++) v[q] = W[(q + R * b1) * 16 + rho];
     RadixReg<R>::fft(v);
 #pragma unroll
     for (int k = 0; k < R; k++) {
@@ -137,6 +140,12 @@ SDRB_HD void fbB_pass1(int t, const cpx* W, int k1_0, float* __restrict__ out_fr
         const int bin = (k1_0 + rho) + G::L * (b1 + R * k);
         out_frame[(bin + N / 2) & (N - 1)] = x.x * x.x + x.y * x.y;
     }
+}
+template <int R>
+SDRB_HD void fbB_pass1(int t, const cpx* W, int k1_0, float* __restrict__ out_frame) {
+    cpx v[R];
+    fbB_pass1_load<R>(t, W, v);
+    fbB_pass1_finish<R>(t, v, k1_0, out_frame);
 }
 
 }  // namespace sdrb

@@ -132,6 +132,7 @@ cudaError_t launch_fft_front(int fmt, const void* iq, cpx* out, const float* win
 cudaError_t fft_big_prepare();
 bool fft_big_supports(int n);
 int fft_big_table_elems(int n);
+int fft_big_best_group(int n, int max_group);   // frames per L2-resident group that fill whole waves of the rows kernel
 cudaError_t launch_fft_big(int fmt, const void* iq, float* power, cpx* A, const cpx* tables, int n, int n_frames,
                            cudaStream_t st);
 // estimator.cu
