@@ -85,8 +85,8 @@ k_band_scan(const float* __restrict__ power, const EstGeometry* __restrict__ geo
                                          : power + (size_t)frame * g.n + lo;
     float sum = 0.0f, maxP = seg == 0 ? -1.0f : 0.0f;
     int maxIdx = 0;
-#pragma unroll 8
-    for (int i = 0; i < len; i++) {
+#pragma unroll 32
+    for (int i = 0; i < len; i++) {   // 32 loads in flight: the scan is bound by memory latency, not by the adds
         const float v = p[i];
         sum = __fadd_rn(sum, v);
         if (v > maxP) { maxP = v; maxIdx = i; }
@@ -100,7 +100,7 @@ k_band_scan(const float* __restrict__ power, const EstGeometry* __restrict__ geo
         for (int i = 0; i < W; i++) run = __fadd_rn(run, p[i]);
         float best = run;
         int bestStart = 0;
-#pragma unroll 8
+#pragma unroll 16
         for (int s = 1; s + W - 1 < len; s++) {
             run = __fadd_rn(run, __fsub_rn(p[s + W - 1], p[s - 1]));
             if (run > best) { best = run; bestStart = s; }
