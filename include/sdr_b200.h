@@ -225,7 +225,9 @@ int  sdrb_get_pulse_results(sdrb_ctx* ctx, sdrb_pulse_result* host_out, size_t c
 int  sdrb_pulse_results_device(sdrb_ctx* ctx, const sdrb_pulse_result** dev_ptr);
 
 /* ---- per-stream state (checkpoint / resume) ----------------------------- */
-/* Opaque blob: three biquad states, tracking memory, detection ring, frame counter. */
+/* Opaque blob: three biquad states, tracking memory, detection ring, frame counter.  The pulse detectors'
+ * histories and the Airspy converter state are NOT part of the blob: they restart with sdrb_configure /
+ * sdrb_reset_state (the reference's detectors restart with setPulseConfig / reset() in the same way). */
 size_t sdrb_state_bytes(const sdrb_ctx* ctx);
 int  sdrb_save_state(sdrb_ctx* ctx, void* host_blob, size_t bytes);
 int  sdrb_load_state(sdrb_ctx* ctx, const void* host_blob, size_t bytes);

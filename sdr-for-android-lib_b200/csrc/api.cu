@@ -169,7 +169,7 @@ int sdrb_create(int device, sdrb_ctx** out) {
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
-        (e = fft16k3_prepare()) != cudaSuccess || (e = fft_big_prepare()) != cudaSuccess || (e = estimator_prepare()) != cudaSuccess) {
+        (e = fft_big_prepare()) != cudaSuccess || (e = estimator_prepare()) != cudaSuccess) {
         fail(nullptr, SDRB_ERR_CUDA, "context setup: %s", cudaGetErrorString(e));
         delete ctx;
         return SDRB_ERR_CUDA;
@@ -190,6 +190,7 @@ int sdrb_create(int device, sdrb_ctx** out) {
     if ((e = cudaMalloc(&ctx->d_tables16k, t16.size() * sizeof(cpx))) != cudaSuccess ||
         (e = cudaMemcpy(ctx->d_tables16k, t16.data(), t16.size() * sizeof(cpx), cudaMemcpyHostToDevice)) != cudaSuccess ||
         (e = fft16k2_prepare(t16.data())) != cudaSuccess ||
+        (e = fft16k3_prepare(t3.data())) != cudaSuccess ||
         (e = cudaMalloc(&ctx->d_tables16k3, t3.size())) != cudaSuccess ||
         (e = cudaMemcpy(ctx->d_tables16k3, t3.data(), t3.size(), cudaMemcpyHostToDevice)) != cudaSuccess ||
         (e = cudaMalloc(&ctx->d_tables16k4, t4.size() * sizeof(cpx))) != cudaSuccess ||

@@ -11,6 +11,11 @@
 
 namespace sdrb {
 
+__constant__ pw4 c_f3_t2[F3_T2];   // [kb'][c]  (W_512^(c kb'), W_512^(c (kb' + 16)))
+struct F3DevTw {
+    __device__ __forceinline__ pw4 operator()(int kbp, int c) const { return c_f3_t2[kbp * 16 + c]; }
+};
+
 namespace {
 __device__ __forceinline__ unsigned f3_smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void f3_mbar_init(void* bar, unsigned count) {
@@ -88,7 +93,6 @@ k_fft16k3(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
     pf* RE = reinterpret_cast<pf*>(smem_raw);
     pf* IM = RE + F3_PLANE_UNITS;
     cpx* TP = reinterpret_cast<cpx*>(smem_raw + F3_E_BYTES);
-    pw4* T2 = reinterpret_cast<pw4*>(smem_raw + F3_E_BYTES + F3_TP * 8);
     raw_t* stage = reinterpret_cast<raw_t*>(smem_raw + F3_E_BYTES + F3_TABLE_BYTES);
     unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem_raw + F3_E_BYTES + F3_TABLE_BYTES +
                                                                     F3Smem<FMT>::kStageBytes);
@@ -124,18 +128,18 @@ k_fft16k3(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
         if (FRONT) f3_front<FRONT>(t, v, win, red);
         // phase-1 arithmetic needs no shared memory: it overlaps the slower warps' phase 3 of the
         // previous transform; only the stores wait for the exchange buffer to be free
-        c2 y[16];
-        f3_phase1_compute(t, v, TP, y);
+        c2 z[16];
+        f3_phase1_fft(v, z);
         __syncthreads();  // exchange buffer free (previous phase 3 done), stage consumed by every thread
         if (kStaged && t == 0 && f + (int)gridDim.x < n_frames) {
             f3_mbar_expect_tx(bar, F3Smem<FMT>::kStageBytes);
             f3_bulk_g2s(stage, in + (size_t)(f + gridDim.x) * F3_N, F3Smem<FMT>::kStageBytes, bar);
         }
-        f3_phase1_store(t, y, reinterpret_cast<float*>(RE), reinterpret_cast<float*>(IM));
+        f3_phase1_twiddle_store(t, z, TP, reinterpret_cast<float*>(RE), reinterpret_cast<float*>(IM));
         __syncthreads();
-        f3_phase2(t, RE, IM, T2);
+        f3_phase2(t, RE, IM);
         __syncthreads();
-        f3_phase3(t, RE, IM, out + (size_t)f * F3_N);
+        f3_phase3(t, RE, IM, F3DevTw(), out + (size_t)f * F3_N);
     }
 }
 
@@ -152,8 +156,9 @@ static cudaError_t f3_prep_fmt() {
     return f3_prep_one<FMT, 3>();
 }
 
-cudaError_t fft16k3_prepare() {
+cudaError_t fft16k3_prepare(const unsigned char* host_tables) {
     cudaError_t e;
+    if ((e = cudaMemcpyToSymbol(c_f3_t2, host_tables + F3_TP * 8, F3_T2 * sizeof(pw4))) != cudaSuccess) return e;
     if ((e = f3_prep_fmt<FMT_CU8>()) != cudaSuccess) return e;
     if ((e = f3_prep_fmt<FMT_CS16>()) != cudaSuccess) return e;
     return f3_prep_fmt<FMT_CF32>();

@@ -182,6 +182,46 @@ SDRB_HD void f3_phase1_compute(int t, c2* v, const cpx* TP, c2* y) {
 #pragma unroll
     for (int k = 0; k < 16; k++) y[k] = c2mul(z[k], qre[k], qim[k]);
 }
+// The same phase 1 cut for the kernel: arithmetic up to the DIT tail (no shared memory), then twiddle and
+// exchange stores interleaved value by value, so the stores spread over the twiddle arithmetic.
+SDRB_HD void f3_phase1_fft(c2* v, c2* z) {
+    c2fft16(v);
+    f3_dit_tail(v, z);
+}
+SDRB_HD void f3_phase1_twiddle_store(int t, const c2* z, const cpx* TP, float* RE, float* IM) {
+    cpx P[5];
+#pragma unroll
+    for (int j = 0; j < 5; j++) P[j] = TP[j * 512 + t];
+    const int b = t >> 4, c = t & 15;
+    const int base = ((b >> 1) * 16 + c) * 2 + (b & 1);
+    pf qre[16], qim[16];
+    qre[0] = mkp(1.0f, P[4].x);
+    qim[0] = mkp(0.0f, P[4].y);
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        if (k > 0) {
+            const int low = k & (-k);
+            const int j = low == 1 ? 0 : (low == 2 ? 1 : (low == 4 ? 2 : 3));
+            if (k == low) {
+                const cpx h = cmul(P[j], P[4]);
+                qre[k] = mkp(P[j].x, h.x);
+                qim[k] = mkp(P[j].y, h.y);
+            } else {
+                c2 a;
+                a.re = qre[k - low];
+                a.im = qim[k - low];
+                a = c2mulc(a, P[j].x, P[j].y);
+                qre[k] = a.re;
+                qim[k] = a.im;
+            }
+        }
+        const c2 y = c2mul(z[k], qre[k], qim[k]);
+        RE[k * (2 * F3_PITCH) + base] = y.re.x;
+        IM[k * (2 * F3_PITCH) + base] = y.im.x;
+        RE[(k + 16) * (2 * F3_PITCH) + base] = y.re.y;
+        IM[(k + 16) * (2 * F3_PITCH) + base] = y.im.y;
+    }
+}
 SDRB_HD void f3_phase1_store(int t, const c2* y, float* RE, float* IM) {
     const int b = t >> 4, c = t & 15;
     const int base = ((b >> 1) * 16 + c) * 2 + (b & 1);   // float index inside a ka plane
@@ -199,9 +239,8 @@ SDRB_HD void f3_phase1(int t, c2* v, const cpx* TP, float* RE, float* IM) {
     f3_phase1_store(t, y, RE, IM);
 }
 
-// ---- phase 2: thread t = 16 ka + c, DFT32 over b, worlds (b even, b odd), twiddle
-// W_512^(c kb); in place: unit (ka, j, c) in, unit (ka, k, c) = (X2[kb = k], X2[kb = k + 16]) out.
-SDRB_HD void f3_phase2(int t, pf* RE, pf* IM, const pw4* T2) {
+// ---- phase 2: thread t = 16 ka + c, DFT32 over b, worlds (b even, b odd); in place: unit (ka, j, c) in, unit (ka, k, c) = (X2[kb = k], X2[kb = k + 16]) out.
+SDRB_HD void f3_phase2(int t, pf* RE, pf* IM) {
     const int ka = t >> 4, c = t & 15;
     pf* re = RE + f3_unit(ka, 0, c);
     pf* im = IM + f3_unit(ka, 0, c);
@@ -212,24 +251,30 @@ SDRB_HD void f3_phase2(int t, pf* RE, pf* IM, const pw4* T2) {
     c2 z[16];
     f3_dit_tail(v, z);
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        const pw4 w = T2[k * 16 + c];
-        const c2 y = c2mul(z[k], w.re, w.im);
-        re[k * 16] = y.re;
-        im[k * 16] = y.im;
+    for (int k = 0; k < 16; k++) {   // the twiddle W_512^(c kb) is applied by phase 3 on load
+        re[k * 16] = z[k].re;
+        im[k * 16] = z[k].im;
     }
 }
 
 // ---- phase 3: thread t: ka = t & 31, kb' = t >> 5; DFT16 over c of the columns kb' (world A)
 // and kb' + 16 (world B); re*re + im*im (src/dsp/fft_process.cpp:85); bin k lands at
 // (k + N/2) mod N (:92-97).
-SDRB_HD void f3_phase3(int t, const pf* RE, const pf* IM, float* __restrict__ out) {
+// tw(kb', c) returns the pair (W_512^(c kb'), W_512^(c (kb' + 16))); kb' is uniform over a warp, so the device
+// functor reads the constant bank (broadcast) instead of shared memory.
+template <class TW>
+SDRB_HD void f3_phase3(int t, const pf* RE, const pf* IM, TW tw, float* __restrict__ out) {
     const int ka = t & 31, kbp = t >> 5;
     const pf* re = RE + f3_unit(ka, kbp, 0);
     const pf* im = IM + f3_unit(ka, kbp, 0);
     c2 v[16];
 #pragma unroll
     for (int c = 0; c < 16; c++) { v[c].re = re[c]; v[c].im = im[c]; }
+#pragma unroll
+    for (int c = 1; c < 16; c++) {
+        const pw4 w = tw(kbp, c);
+        v[c] = c2mul(v[c], w.re, w.im);
+    }
     c2fft16(v);
     const int k0 = ka + 32 * kbp;
 #pragma unroll
@@ -259,14 +304,15 @@ template <>
 struct Ingest3<FMT_CU8> {
     typedef uint16_t raw_t;
     __device__ __forceinline__ static c2 cvt2(uint16_t r0, uint16_t r1) {
-        const pf mi = mkp(__uint_as_float(__byte_perm((unsigned)r0, 0x4B000000u, 0x7440)),
-                          __uint_as_float(__byte_perm((unsigned)r1, 0x4B000000u, 0x7440)));
-        const pf mq = mkp(__uint_as_float(__byte_perm((unsigned)r0, 0x4B000000u, 0x7441)),
-                          __uint_as_float(__byte_perm((unsigned)r1, 0x4B000000u, 0x7441)));
-        const pf k = pdup(0.0078125f), off = pdup(-127.4f * 0.0078125f), m23 = pdup(8388608.0f);
+        // byte at bits 16..23 of a float word = b * 2^-133 exactly; fma(., 2^126, -127.4f/128) rounds once (fft16k2.cuh)
+        const pf mi = mkp(__uint_as_float(__byte_perm((unsigned)r0, 0u, 0x4044)),
+                          __uint_as_float(__byte_perm((unsigned)r1, 0u, 0x4044)));
+        const pf mq = mkp(__uint_as_float(__byte_perm((unsigned)r0, 0u, 0x4144)),
+                          __uint_as_float(__byte_perm((unsigned)r1, 0u, 0x4144)));
+        const pf k = pdup(8.50705917302346158658e37f), off = pdup(-127.4f * 0.0078125f);
         c2 v;
-        v.re = pfma(psub(mi, m23), k, off);
-        v.im = pfma(psub(mq, m23), k, off);
+        v.re = pfma(mi, k, off);
+        v.im = pfma(mq, k, off);
         return v;
     }
 };

@@ -112,7 +112,7 @@ cudaError_t fft16k2_prepare(const cpx* host_tables);   // make_f2_tables() layou
 // fft16k3.cu : third-generation 16K kernel (packed FP32 pairs, same decomposition and staging)
 cudaError_t launch_fft16k3(int fmt, const void* iq, float* power, const unsigned char* tables, int n_frames,
                            int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);
-cudaError_t fft16k3_prepare();
+cudaError_t fft16k3_prepare(const unsigned char* host_tables);   // make_f3_tables() layout; T2 goes to the constant bank
 // fft16k4.cu : fourth-generation 16K kernel (two 8192-point jobs per transform, 2 CTAs per SM)
 cudaError_t launch_fft16k4(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
                            int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);

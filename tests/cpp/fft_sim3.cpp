@@ -88,10 +88,12 @@ int main() {
     for (int t = 0; t < F3_THREADS; t++) {
         c2 v[16];
         f3_phase1_load<FMT_CF32>(t, in.data(), v);
-        f3_phase1(t, v, TP, reinterpret_cast<float*>(RE.data()), reinterpret_cast<float*>(IM.data()));
+        c2 z[16];   // the kernel's sequence: DFT, then twiddle + store
+        f3_phase1_fft(v, z);
+        f3_phase1_twiddle_store(t, z, TP, reinterpret_cast<float*>(RE.data()), reinterpret_cast<float*>(IM.data()));
     }
-    for (int t = 0; t < F3_THREADS; t++) f3_phase2(t, RE.data(), IM.data(), T2);   // in place per thread
-    for (int t = 0; t < F3_THREADS; t++) f3_phase3(t, RE.data(), IM.data(), out.data());
+    for (int t = 0; t < F3_THREADS; t++) f3_phase2(t, RE.data(), IM.data());   // in place per thread
+    for (int t = 0; t < F3_THREADS; t++) f3_phase3(t, RE.data(), IM.data(), [T2](int kbp, int c) { return T2[kbp * 16 + c]; }, out.data());
     std::vector<std::complex<double>> ref(N);
     double energy = 0;
     for (int i = 0; i < N; i++) { ref[i] = {in[i].x, in[i].y}; energy += std::norm(ref[i]); }
