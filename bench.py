@@ -47,7 +47,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--streams", type=int, default=1024, help="streams per GPU")
-    ap.add_argument("--blocks", type=int, default=8, help="readings per stream per step")
+    ap.add_argument("--blocks", type=int, default=37,
+                    help="readings per stream per step (1024 x 37 = 37888 transforms = 256 whole rounds of 148 SMs)")
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
