@@ -16,6 +16,9 @@
 //                 outputs on skipped / invalid frames) and writes the sdrb_frame_result records.
 // The pooled per-bin mean (:261-262) is a tree sum here (the reference adds sequentially); it
 // only feeds tolerance-checked scalars (0.01 dB), not an index or a sort decision.
+#include <algorithm>
+#include <cstdlib>
+
 #include "internal.h"
 
 namespace sdrb {
@@ -43,13 +46,16 @@ struct BandStat {
 // ---------------------------------------------------------------- k_band_scan
 // Mirrors :146-155 (sum + arg-max), :198-202 (sum + max) and best1kHzMean :163-180 / :310-318
 // (run-sum with +new -old updates, strict >).
-// STAGED: the CTA first copies the bands of its `fpc` frames into shared memory with coalesced
-// loads (the spectra were just written by the FFT kernel and are mostly in HBM: one thread per
-// band walking global memory is latency-bound), then every thread scans its band from there.
+// STAGED: the CTA first brings the bands of its `fpc` frames into shared memory with 4-byte cp.async
+// copies (one warp per band slot, lanes along the band: coalesced, nothing waits on a register, all copies of
+// the CTA are in flight together), then every thread scans its own slot.  Slots are `pitch` floats apart,
+// pitch odd, so the 32 lanes of a warp (32 consecutive slots, same position i) fall on 32 different banks.
+// One thread per band walking global memory instead touches 32 different lines per warp load and is bound by
+// L1 tag lookups and miss latency.
 template <bool STAGED>
 __global__ void __launch_bounds__(128)
 k_band_scan(const float* __restrict__ power, const EstGeometry* __restrict__ geo_p, BandStat* __restrict__ stats,
-            int fpc, int n_frames) {
+            int fpc, int n_frames, int pitch) {
     extern __shared__ float band_smem[];
     __shared__ EstGeometry g;
     {
@@ -63,15 +69,17 @@ k_band_scan(const float* __restrict__ power, const EstGeometry* __restrict__ geo
     const int frame0 = blockIdx.x * fpc;
     const int nf = min(fpc, n_frames - frame0);
     if (STAGED) {
-        for (int f = 0; f < nf; f++) {
-            const float* __restrict__ P = power + (size_t)(frame0 + f) * g.n;
-            float* dst = band_smem + (size_t)f * g.totalBins;
-            for (int seg = 0; seg < nSeg; seg++) {
-                const int lo = seg == 0 ? g.focusLo : g.winLo[seg - 1];
-                const int len = g.segOff[seg + 1] - g.segOff[seg];
-                for (int i = threadIdx.x; i < len; i += blockDim.x) dst[g.segOff[seg] + i] = __ldg(P + lo + i);
-            }
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        for (int slot = warp; slot < nf * nSeg; slot += 4) {
+            const int fl = slot / nSeg, seg = slot - fl * nSeg;
+            const int lo = seg == 0 ? g.focusLo : g.winLo[seg - 1];
+            const int len = g.segOff[seg + 1] - g.segOff[seg];
+            const float* src = power + (size_t)(frame0 + fl) * g.n + lo;
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(band_smem + (size_t)slot * pitch);
+            for (int i = lane; i < len; i += 32)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + 4u * i), "l"(src + i) : "memory");
         }
+        asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
         __syncthreads();
     }
     const int id = threadIdx.x;
@@ -81,8 +89,7 @@ k_band_scan(const float* __restrict__ power, const EstGeometry* __restrict__ geo
     const int lo = seg == 0 ? g.focusLo : g.winLo[seg - 1];
     const int len = g.segOff[seg + 1] - g.segOff[seg];
     const int W = g.winBins1k;
-    const float* __restrict__ p = STAGED ? band_smem + (size_t)fl * g.totalBins + g.segOff[seg]
-                                         : power + (size_t)frame * g.n + lo;
+    const float* __restrict__ p = STAGED ? band_smem + (size_t)id * pitch : power + (size_t)frame * g.n + lo;
     float sum = 0.0f, maxP = seg == 0 ? -1.0f : 0.0f;
     int maxIdx = 0;
 #pragma unroll 32
@@ -156,12 +163,14 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
     const int len = lane <= nWin ? g.segOff[lane + 1] - g.segOff[lane] : 1;
     // dB figures of the bands, one lane per band (:149-155, :203-213)
     float dbA = 0.0f, dbB = 0.0f;   // focus: (absPeakDb candidate, signalPowerDb); window: (meanDb, best1kDb)
-    if (lane == 0) {
-        dbA = db10(bs.maxP);
-        dbB = db10(__fdiv_rn(bs.sum, (float)g.focusLen));
-    } else if (isWin && valid) {
-        dbA = db10(__fdiv_rn(bs.sum, (float)len));
-        dbB = db10(len < W ? __fdiv_rn(bs.sum, (float)len) : __fdiv_rn(bs.bestRun, (float)W));
+    {   // arguments first, then ONE pair of log10 calls for the whole warp (the double log10 is ~130 instructions;
+        // under a lane-0 / window branch it would run four times)
+        const bool want = lane == 0 || (isWin && valid);
+        const float meanP = __fdiv_rn(bs.sum, (float)(lane == 0 ? g.focusLen : len));
+        const float argA = lane == 0 ? bs.maxP : meanP;
+        const float argB = (lane == 0 || len < W) ? meanP : __fdiv_rn(bs.bestRun, (float)W);
+        const float a = db10(want ? argA : 1.0f), b = db10(want ? argB : 1.0f);
+        if (want) { dbA = a; dbB = b; }
     }
     FrameLocal o = {};
     {   // ---- :142-155 focus band
@@ -218,13 +227,18 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
     float* stage = USE_SMEM ? stage_smem + (size_t)warp * pooled_cap : gscratch + (size_t)frame * pooled_cap;
     const float* P = power + (size_t)frame * g.n;
     float part = 0.0f;
-    for (int i = lane; i < pooledN; i += 32) {
-        const int j = (i >= cum[1]) + (i >= cum[2]) + (i >= cum[3]);
-        const int bin = (j == 0 ? plo[0] : (j == 1 ? plo[1] : (j == 2 ? plo[2] : plo[3]))) +
-                        (i - (j == 0 ? 0 : (j == 1 ? cum[1] : (j == 2 ? cum[2] : cum[3]))));
-        const float d = db10_fast(__ldg(P + bin));
-        stage[i] = d;
-        part += d;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {   // quiet window by quiet window: lanes along the window, coalesced
+        if (j < nb) {
+            const float* Pw = P + plo[j];
+            float* sw = stage + cum[j];
+            const int lenj = cum[j + 1] - cum[j];
+            for (int i = lane; i < lenj; i += 32) {
+                const float d = db10_fast(__ldg(Pw + i));
+                sw[i] = d;
+                part += d;
+            }
+        }
     }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(FULL, part, d);
@@ -245,9 +259,9 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
             if ((bits & mask) == prefix) atomicAdd(&hist[(bits >> shift) & 255u], 1);
         }
         __syncwarp();
-        int mine = 0;
+        int h8[8], mine = 0;
 #pragma unroll
-        for (int j = 0; j < 8; j++) mine += hist[8 * lane + j];
+        for (int j = 0; j < 8; j++) { h8[j] = hist[8 * lane + j]; mine += h8[j]; }
         int incl = mine;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -256,16 +270,13 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
         }
         const unsigned cross = __ballot_sync(FULL, incl > k);
         const int L = cross ? __ffs(cross) - 1 : 31;
-        int digit = 0, acc = 0;
-        if (lane == L) {
-            acc = incl - mine;
-            digit = 8 * L;
-            for (int j = 0; j < 7; j++) {
-                const int h = hist[8 * L + j];
-                if (acc + h > k) break;
-                acc += h;
-                digit++;
-            }
+        // inside the crossing lane's 8 bins: the first bin whose running count passes k (the last bin if none does)
+        int digit = 8 * lane, acc = incl - mine;
+        bool open = true;
+#pragma unroll
+        for (int j = 0; j < 7; j++) {
+            open = open && (acc + h8[j] <= k);
+            if (open) { acc += h8[j]; digit++; }
         }
         digit = __shfl_sync(FULL, digit, L);
         acc = __shfl_sync(FULL, acc, L);
@@ -300,11 +311,8 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
     }
 }
 
-// Frame clock (SURVEY.md 8a note T): t = (frame + 1) * n / fs in ns, integer arithmetic.
-__device__ __forceinline__ long long frame_clock_ns(long long frame_index, int n, unsigned fs) {
-    const long long q = (frame_index + 1) * (long long)n;
-    return (q / fs) * 1000000000LL + ((q % fs) * 1000000000LL) / fs;
-}
+// Frame clock (SURVEY.md 8a note T), integer arithmetic: with q = (frame + 1) * n,
+//   frame_clock_ns = (q / fs) * 1e9 + ((q % fs) * 1e9) / fs
 
 // One thread per stream walks its frames in order (:333-378) and emits the result records.
 __global__ void __launch_bounds__(128)
@@ -316,10 +324,29 @@ k_tracker(const FrameLocal* __restrict__ local, const EstGeometry* __restrict__ 
     const EstGeometry& g = *geo_p;
     FftStreamState st = state[s];
     const unsigned fs = (unsigned)g.sampleRateF;
+    // The frame clock t = floor-ns of (frameCounter + 1) * n / fs is carried as whole seconds + a remainder
+    // below fs, advanced by n per frame: the three 64-bit divisions per frame (hundreds of
+    // dependent instructions each) of that formula become one division before the loop and an FP64 quotient with an exact
+    // integer correction per frame.  Same integers.
+    const unsigned long long q0 = (unsigned long long)st.frameCounter * (unsigned long long)g.n;
+    unsigned long long sec = q0 / fs, rem = q0 % fs;
+    const unsigned long long n_div = (unsigned)g.n / fs, n_mod = (unsigned)g.n % fs;
+    const double inv_fs = 1.0 / (double)fs;
+    const FrameLocal* lp = local + (size_t)s * n_blocks;
+    FrameLocal f_next = lp[0];
     for (int b = 0; b < n_blocks; b++) {
-        const FrameLocal f = local[(size_t)s * n_blocks + b];
+        const FrameLocal f = f_next;
+        if (b + 1 < n_blocks) f_next = lp[b + 1];   // in flight while this frame's chain runs
         sdrb_frame_result r = {};
-        const long long now_ns = frame_clock_ns(st.frameCounter, g.n, fs);
+        sec += n_div;
+        rem += n_mod;
+        if (rem >= fs) { rem -= fs; sec++; }
+        const unsigned long long num = rem * 1000000000ULL;             // < 2^62
+        unsigned long long frac = (unsigned long long)((double)num * inv_fs);   // within 1 of the floor
+        const long long left = (long long)(num - frac * fs);
+        if (left < 0) frac--;
+        else if (left >= (long long)fs) frac++;
+        const long long now_ns = (long long)(sec * 1000000000ULL + frac);
         st.frameCounter++;
         r.peakBin = f.peakBin;
         r.nRef = g.nWin;
@@ -404,7 +431,7 @@ static int pooled_cap_of(const EstGeometry& g) {
 }
 
 cudaError_t estimator_prepare() {
-    cudaError_t e = cudaFuncSetAttribute(k_band_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(k_band_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(k_estimator<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 EST_WARPS * EST_SMEM_POOL_FLOATS * (int)sizeof(float));
@@ -428,15 +455,23 @@ cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, const
     BandStat* stats = reinterpret_cast<BandStat*>(scratch) + frame0 * EST_MAX_BANDS;
     const int nSeg = h_geo.nWin + 1;
     if (h_geo.focusLen > 0) {
-        // frames per CTA: one thread per band (<= 128 threads), staged bands within 64 KiB
+        // frames per CTA: one thread per band (<= 128 threads); staged when one frame's slots fit 96 KiB of
+        // shared memory (measured on B200, 37888 frames of the bench geometry: 143 us walking global memory)
         int fpc = 128 / nSeg;
-        const int by_smem = (64 * 1024) / (h_geo.totalBins * (int)sizeof(float));
-        if (by_smem >= 1 && false) {   // measured on B200: staging is slower (129 us vs 37 us), kept for reference
-            if (fpc > by_smem) fpc = by_smem;
-            const size_t smem = (size_t)fpc * h_geo.totalBins * sizeof(float);
-            k_band_scan<true><<<(n_frames + fpc - 1) / fpc, 128, smem, st>>>(power, d_geo, stats, fpc, n_frames);
+        int maxLen = 0;
+        for (int sgi = 0; sgi < nSeg; sgi++) maxLen = std::max(maxLen, h_geo.segOff[sgi + 1] - h_geo.segOff[sgi]);
+        const int pitch = maxLen | 1;
+        const size_t per_frame = (size_t)nSeg * pitch * sizeof(float);
+        static const bool no_stage = getenv("SDRB_BAND_STAGE") && getenv("SDRB_BAND_STAGE")[0] == '0';
+        const int by_smem = (int)((96 * 1024) / per_frame);
+        if (by_smem >= 1 && !no_stage) {
+            // about 40 KiB per CTA keeps five CTAs on an SM: the scan is a dependent chain, it needs warps in flight
+            const int by_occ = std::max(1, (int)((40 * 1024) / per_frame));
+            fpc = std::min(fpc, std::min(by_smem, by_occ));
+            const size_t smem = (size_t)fpc * per_frame;
+            k_band_scan<true><<<(n_frames + fpc - 1) / fpc, 128, smem, st>>>(power, d_geo, stats, fpc, n_frames, pitch);
         } else {
-            k_band_scan<false><<<(n_frames + fpc - 1) / fpc, 128, 0, st>>>(power, d_geo, stats, fpc, n_frames);
+            k_band_scan<false><<<(n_frames + fpc - 1) / fpc, 128, 0, st>>>(power, d_geo, stats, fpc, n_frames, 0);
         }
     }
     const int cap = pooled_cap_of(h_geo);
