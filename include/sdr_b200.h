@@ -224,6 +224,17 @@ int  sdrb_set_pulse_config(sdrb_ctx* ctx, const sdrb_audio_pulse_config* cfg);
 int  sdrb_get_pulse_results(sdrb_ctx* ctx, sdrb_pulse_result* host_out, size_t capacity_records);
 int  sdrb_pulse_results_device(sdrb_ctx* ctx, const sdrb_pulse_result** dev_ptr);
 
+/* Diagnostic of the SDRB_RU16 front end (libairspy iqconverter_float.c:418-431, remove_dc): the DC tracker is
+ * walked in chunks from guessed starts and every chunk is checked against its predecessor's end value; a
+ * chunk whose guess did not land on the sequential value is walked again in order.  Sum over streams since
+ * sdrb_configure / sdrb_reset_state of the chunks that needed the second walk (0 on ordinary noisy ADC data;
+ * the output is bit-exact either way). */
+int  sdrb_airspy_redone_chunks(sdrb_ctx* ctx, uint64_t* out);
+/* The converter's output of the last SDRB_RU16 call: [n_streams][n_blocks][N] interleaved (I, Q) floats, what
+ * iqconverter_float_process leaves in the sample buffer (iqconverter_float.c:471-475) and SoapyAirspy hands
+ * to readStream as CF32.  Synchronises. */
+int  sdrb_get_airspy_iq(sdrb_ctx* ctx, float* host_out, size_t capacity_floats);
+
 /* ---- per-stream state (checkpoint / resume) ----------------------------- */
 /* Opaque blob: three biquad states, tracking memory, detection ring, frame counter.  The pulse detectors'
  * histories and the Airspy converter state are NOT part of the blob: they restart with sdrb_configure /

@@ -99,6 +99,8 @@ EXPORTS = {
     "sdrb_set_pulse_config": (C.c_int, [C.c_void_p, C.POINTER(AudioPulseConfig)]),
     "sdrb_get_pulse_results": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "sdrb_pulse_results_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "sdrb_airspy_redone_chunks": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
+    "sdrb_get_airspy_iq": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "sdrb_power_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "sdrb_get_power": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "sdrb_get_power_all": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
@@ -241,6 +243,18 @@ class Context:
         out = np.zeros(shape, dtype=PULSE_DTYPE)
         _check(lib.sdrb_get_pulse_results(self._h, out.ctypes.data_as(C.c_void_p), out.size), self._h)
         return out
+
+    def airspy_iq(self):
+        """[n_streams, last_blocks, N, 2] float32: the real->IQ converter's output of the last RU16 call."""
+        out = np.zeros((self.n_streams, self.last_blocks, int(self.cfg.samplesPerReading), 2), dtype=np.float32)
+        _check(lib.sdrb_get_airspy_iq(self._h, out.ctypes.data_as(C.c_void_p), out.size), self._h)
+        return out
+
+    def airspy_redone_chunks(self):
+        """Chunks of the RU16 DC pass that were walked a second time (diagnostic; 0 on noisy ADC data)."""
+        n = C.c_uint64(0)
+        _check(lib.sdrb_airspy_redone_chunks(self._h, C.byref(n)), self._h)
+        return int(n.value)
 
     def set_pulse_config(self, cfg=None):
         """SSBProcessor::setPulseConfig: rebuild every audio detector (None = the reference defaults)."""

@@ -88,6 +88,9 @@ struct sdrb_ctx {
     AirspyStreamState* d_air_state = nullptr;
     float* d_air_T = nullptr;
     cpx* d_air_iq = nullptr;
+    float* d_air_work = nullptr;   // per-chunk start / end values of the DC pass
+    size_t air_work_per_stream = 0;
+    int air_chunk = 0, air_warm = 0;
     // last call
     int last_blocks = 0;
     unsigned last_stages = 0;
@@ -136,7 +139,7 @@ static void free_buffers(sdrb_ctx* c) {
                      (void**)&c->d_front, (void**)&c->d_fb_tables, (void**)&c->d_fbA,
                      (void**)&c->d_sp_state, (void**)&c->d_au_state, (void**)&c->d_sp_e, (void**)&c->d_sp_f,
                      (void**)&c->d_au_e, (void**)&c->d_pulse, (void**)&c->d_air_state, (void**)&c->d_air_T,
-                     (void**)&c->d_air_iq};
+                     (void**)&c->d_air_iq, (void**)&c->d_air_work};
     for (void** p : ptrs) {
         if (*p) cudaFree(*p);
         *p = nullptr;
@@ -548,6 +551,9 @@ static int validate_process(sdrb_ctx* ctx, const void* iq, int n_blocks, unsigne
         CK(cudaMemset(ctx->d_air_state, 0, S * sizeof(AirspyStreamState)));
         CK(cudaMalloc(&ctx->d_air_T, S * (AIRSPY_TAIL + real) * sizeof(float)));
         CK(cudaMalloc(&ctx->d_air_iq, S * (real / 2) * sizeof(cpx)));
+        airspy_chunking(&ctx->air_chunk, &ctx->air_warm);
+        ctx->air_work_per_stream = airspy_work_floats(1, (long long)real, ctx->air_chunk);
+        CK(cudaMalloc(&ctx->d_air_work, S * ctx->air_work_per_stream * sizeof(float)));
     }
     if ((stages & (SDRB_STAGE_SPECTRAL_PULSE | SDRB_STAGE_AUDIO_PULSE)) && (rc = ensure_pulse_buffers(ctx, stages)) != SDRB_OK)
         return rc;
@@ -569,7 +575,9 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
         const long long real = 2LL * n_blocks * n;
         cpx* iq_out = ctx->d_air_iq + f0s * n;
         CK(launch_airspy_front(static_cast<const uint16_t*>(d_iq), ctx->d_air_state + s0,
-                               ctx->d_air_T + (size_t)s0 * (AIRSPY_TAIL + real), iq_out, ns, real, st, &launches));
+                               ctx->d_air_T + (size_t)s0 * (AIRSPY_TAIL + real), iq_out,
+                               ctx->d_air_work + (size_t)s0 * ctx->air_work_per_stream, ctx->air_chunk, ctx->air_warm, ns,
+                               real, st, &launches));
         d_iq = iq_out;
         fmt = FMT_CF32;
     }
@@ -845,6 +853,29 @@ int sdrb_get_pulse_results(sdrb_ctx* ctx, sdrb_pulse_result* host_out, size_t ca
 int sdrb_pulse_results_device(sdrb_ctx* ctx, const sdrb_pulse_result** dev_ptr) {
     if (!ctx || !dev_ptr || !ctx->d_pulse) return fail(ctx, SDRB_ERR_STATE, "no pulse results");
     *dev_ptr = ctx->d_pulse;
+    return SDRB_OK;
+}
+
+int sdrb_get_airspy_iq(sdrb_ctx* ctx, float* host_out, size_t capacity_floats) {
+    if (!ctx || !host_out) return fail(ctx, SDRB_ERR_ARG, "null argument");
+    if (!ctx->d_air_iq || ctx->last_blocks <= 0) return fail(ctx, SDRB_ERR_STATE, "no SDRB_RU16 call yet");
+    const size_t need = 2 * (size_t)ctx->n_streams * ctx->last_blocks * ctx->cfg.samplesPerReading;
+    if (capacity_floats < need) return fail(ctx, SDRB_ERR_ARG, "capacity %zu < %zu floats", capacity_floats, need);
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(host_out, ctx->d_air_iq, need * sizeof(float), cudaMemcpyDeviceToHost));
+    return SDRB_OK;
+}
+
+int sdrb_airspy_redone_chunks(sdrb_ctx* ctx, uint64_t* out) {
+    if (!ctx || !out) return fail(ctx, SDRB_ERR_ARG, "null argument");
+    *out = 0;
+    if (!ctx->d_air_state) return SDRB_OK;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    std::vector<AirspyStreamState> h((size_t)ctx->n_streams);
+    CK(cudaMemcpy(h.data(), ctx->d_air_state, h.size() * sizeof(AirspyStreamState), cudaMemcpyDeviceToHost));
+    for (const auto& a : h) *out += a.redone;
     return SDRB_OK;
 }
 

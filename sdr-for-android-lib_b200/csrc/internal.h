@@ -98,13 +98,16 @@ constexpr int AIRSPY_TAIL = 48;
 struct AirspyStreamState {
     float avg;
     float tail[AIRSPY_TAIL];   // oldest first
-    float pad[15];
+    uint32_t redone;           // chunks of the DC pass walked a second time (guessed start did not meet the true one)
+    float pad[14];
 };
 
 // ---------------------------------------------------------------- launchers
 // airspy.cu : raw 12-bit real samples (uint16, 2 per complex output) -> cf32 [streams][n_real/2]
-cudaError_t launch_airspy_front(const uint16_t* d_raw, AirspyStreamState* d_state, float* d_T, cpx* d_iq,
-                                int n_streams, long long n_real, cudaStream_t st, int* launches);
+cudaError_t launch_airspy_front(const uint16_t* d_raw, AirspyStreamState* d_state, float* d_T, cpx* d_iq, float* d_work,
+                                int chunk, int warm, int n_streams, long long n_real, cudaStream_t st, int* launches);
+void airspy_chunking(int* chunk, int* warm);
+size_t airspy_work_floats(int n_streams, long long n_real, int chunk);
 // fft16k2.cu : second-generation 16K kernel (512 threads x 32 points, TMA-staged input)
 cudaError_t launch_fft16k2(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
                            int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);
