@@ -39,7 +39,10 @@ __constant__ float c_hb[12] = {   // even taps 0..22 of HB_KERNEL_FLOAT (filters
 namespace {
 
 __device__ __forceinline__ float air_step(unsigned raw, float& avg, int phase) {
-    float x = __fmul_rn((float)((int)raw - 2048), 1.0f / 2048.0f);   // airspy.c:316, SAMPLE_SCALE :58-62
+    // (raw - 2048) * (1 / 2048) (airspy.c:316, SAMPLE_SCALE :58-62) without the int -> float conversion: the word
+    // dropped into the mantissa of 2^23 is the float 2^23 + raw, and (2^23 + raw) / 2048 - 4097 = (raw - 2048) / 2048
+    // is exact at every step of one fused multiply-add, so the bits are those of the convert-and-multiply.
+    float x = __fmaf_rn(__uint_as_float(0x4B000000u | raw), 1.0f / 2048.0f, -4097.0f);
     x = __fsub_rn(x, avg);                                           // iqconverter_float.c:425
     avg = __fadd_rn(avg, __fmul_rn(0.01f, x));                       // :426
     // translate_fs_4 (:459-464): -s, -s*hbc, s, s*hbc with hbc = 0.5 (exact)
