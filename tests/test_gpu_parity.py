@@ -167,6 +167,36 @@ def test_ssb_pcm_parity(sdrb, gpu_ctx, fmt, n, fs, mode, upper, B):
             assert np.abs(pcm).max() > 50
 
 
+def test_ssb_pcm_parity_on_extreme_cf32_input(sdrb, gpu_ctx):
+    """cf32 input with bursts far outside any SDR's range (1e33, 1e-30, exact zeros): the AGC's sqrt / divide leave
+    the range the branch-free sequences of k_ssb_main are used for and the library-sequence path takes over; the
+    PCM must stay the oracle's (finite arithmetic throughout, so the reference's behaviour is defined)."""
+    n, fs, S, B = 16384, 2_000_000, 3, 3
+    cfg = sdrb.Config(FC, fs, n, 5, soundMode=1, inputFormat=2, upperSideband=1)
+    iq = make_iq(sdrb, 2, fs, 40, S, B, n).copy()
+    f = iq.view(np.float32).reshape(S, B, n, 2)
+    rng = np.random.default_rng(3)
+    for s in range(S):
+        for b in range(B):
+            at = rng.integers(0, n - 64, 6)
+            f[s, b, at[0]:at[0] + 40] *= np.float32(1e33)      # |y| beyond 2^80 for a few hundred samples
+            f[s, b, at[1]:at[1] + 9, 0] = np.float32(-3e33)
+            f[s, b, at[2]:at[2] + 64] *= np.float32(1e-30)
+            f[s, b, at[3]:at[3] + 64] = 0.0
+            f[s, b, at[4], 0] = np.float32(3e37)
+    gpu_ctx.configure(cfg, S, B)
+    gpu_ctx.process(iq, B, sdrb.STAGE_SSB)
+    pcm = gpu_ctx.pcm()
+    worst = 0
+    for s in range(S):
+        o = ol.OracleSsb()
+        for b in range(B):
+            exp = o.process(ol.to_cf32(iq[s, b], 2), fs, 1, 1)
+            d = np.abs(pcm[s, b].astype(np.int32) - exp.astype(np.int32))
+            worst = max(worst, int(d.max(initial=0)))
+    assert worst <= 1, worst
+
+
 def test_calls_are_continuous_and_batch_independent(sdrb, gpu_ctx):
     """Blocks split over several calls == one call; stream i of a batch == the same stream alone;
     state save/load reproduces the continuation."""
