@@ -88,6 +88,8 @@ struct sdrb_ctx {
     AirspyStreamState* d_air_state = nullptr;
     float* d_air_T = nullptr;
     cpx* d_air_iq = nullptr;
+    float* d_agc = nullptr;        // post-AGC samples [streams][blocks][N] between k_ssb_agc and k_ssb_fir
+    bool agc_tried = false;
     float* d_air_work = nullptr;   // per-chunk start / end values of the DC pass
     size_t air_work_per_stream = 0;
     int air_chunk = 0, air_warm = 0;
@@ -139,7 +141,8 @@ static void free_buffers(sdrb_ctx* c) {
                      (void**)&c->d_front, (void**)&c->d_fb_tables, (void**)&c->d_fbA,
                      (void**)&c->d_sp_state, (void**)&c->d_au_state, (void**)&c->d_sp_e, (void**)&c->d_sp_f,
                      (void**)&c->d_au_e, (void**)&c->d_pulse, (void**)&c->d_air_state, (void**)&c->d_air_T,
-                     (void**)&c->d_air_iq, (void**)&c->d_air_work};
+                     (void**)&c->d_air_iq, (void**)&c->d_air_work, (void**)&c->d_agc};
+    c->agc_tried = false;
     for (void** p : ptrs) {
         if (*p) cudaFree(*p);
         *p = nullptr;
@@ -512,6 +515,19 @@ static int ensure_ssb_buffers(sdrb_ctx* ctx) {
     const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 1;
     if (!ctx->d_a48) CK(cudaMalloc(&ctx->d_a48, frames * m * sizeof(float)));
     if (!ctx->d_pcm) CK(cudaMalloc(&ctx->d_pcm, frames * m * sizeof(int16_t)));
+    // scratch of the split AGC / decimator pair (reference-exact chain only): one float per input sample.
+    // Without it (SDRB_SSB_SPLIT=0, or no memory) the fused k_ssb_main runs.
+    if (!ctx->d_agc && !ctx->ssb_ext && !ctx->agc_tried) {
+        ctx->agc_tried = true;
+        const char* e = getenv("SDRB_SSB_SPLIT");
+        if (!(e && e[0] == '0')) {
+            const size_t bytes = (size_t)ctx->n_streams * ctx->max_blocks * ctx->cfg.samplesPerReading * sizeof(float);
+            if (cudaMalloc(&ctx->d_agc, bytes) != cudaSuccess) {
+                cudaGetLastError();
+                ctx->d_agc = nullptr;
+            }
+        }
+    }
     return SDRB_OK;
 }
 
@@ -689,8 +705,8 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
         const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 0;
         if (!ctx->ssb_ext) {
             CK(launch_ssb(fmt, d_iq, ctx->ssb, ctx->d_taps, static_cast<float2*>(ctx->d_start) + f0s,
-                          ctx->d_ssb_state + s0, ctx->d_a48 + f0s * m, ctx->d_pcm + f0s * m, ns, n_blocks, st,
-                          &launches));
+                          ctx->d_ssb_state + s0, ctx->d_a48 + f0s * m, ctx->d_pcm + f0s * m,
+                          ctx->d_agc ? ctx->d_agc + f0s * (size_t)n : nullptr, ns, n_blocks, st, &launches));
         } else {
             const size_t C = (size_t)ctx->channels;
             CK(launch_ssb_ext(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_inc1, ctx->inc2, ctx->cfg.ssbTrueSideband != 0,

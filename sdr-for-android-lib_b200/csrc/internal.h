@@ -149,7 +149,7 @@ cudaError_t launch_tracker(const FrameLocal* d_local, const EstGeometry* d_geo, 
 // ssb.cu.  d_taps is the [decim][ssb_smax] slot-major tap table.
 int ssb_smax(const SsbParams& P);
 cudaError_t launch_ssb(int fmt, const void* iq, const SsbParams& P, const float* d_taps, float2* d_start,
-                       SsbStreamState* d_state, float* d_a48, int16_t* d_pcm, int n_streams, int n_blocks,
+                       SsbStreamState* d_state, float* d_a48, int16_t* d_pcm, float* d_agc, int n_streams, int n_blocks,
                        cudaStream_t st, int* launches);
 cudaError_t launch_ssb_audio(const float* d_a48, const SsbParams& P, SsbStreamState* d_state, int16_t* d_pcm,
                              int n_streams, int n_blocks, cudaStream_t st);
