@@ -515,13 +515,13 @@ static int ensure_ssb_buffers(sdrb_ctx* ctx) {
     const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 1;
     if (!ctx->d_a48) CK(cudaMalloc(&ctx->d_a48, frames * m * sizeof(float)));
     if (!ctx->d_pcm) CK(cudaMalloc(&ctx->d_pcm, frames * m * sizeof(int16_t)));
-    // scratch of the split AGC / decimator pair (reference-exact chain only): one float per input sample.
+    // scratch of the split AGC / decimator pair: one float per input sample (and per channel of an NCO bank).
     // Without it (SDRB_SSB_SPLIT=0, or no memory) the fused k_ssb_main runs.
-    if (!ctx->d_agc && !ctx->ssb_ext && !ctx->agc_tried) {
+    if (!ctx->d_agc && !ctx->agc_tried) {
         ctx->agc_tried = true;
         const char* e = getenv("SDRB_SSB_SPLIT");
         if (!(e && e[0] == '0')) {
-            const size_t bytes = (size_t)ctx->n_streams * ctx->max_blocks * ctx->cfg.samplesPerReading * sizeof(float);
+            const size_t bytes = frames * (size_t)ctx->cfg.samplesPerReading * sizeof(float);   // frames includes the channels
             if (cudaMalloc(&ctx->d_agc, bytes) != cudaSuccess) {
                 cudaGetLastError();
                 ctx->d_agc = nullptr;
@@ -711,7 +711,8 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
             const size_t C = (size_t)ctx->channels;
             CK(launch_ssb_ext(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_inc1, ctx->inc2, ctx->cfg.ssbTrueSideband != 0,
                               static_cast<float4*>(ctx->d_start) + f0s * C, ctx->d_ssb_state + (size_t)s0 * C,
-                              ctx->d_a48 + f0s * C * m, ctx->d_pcm + f0s * C * m, ns, ctx->channels, n_blocks,
+                              ctx->d_a48 + f0s * C * m, ctx->d_pcm + f0s * C * m,
+                              ctx->d_agc ? ctx->d_agc + f0s * C * (size_t)n : nullptr, ns, ctx->channels, n_blocks,
                               ctx->ssb_samples, st, &launches));
         }
     }

@@ -156,8 +156,11 @@ cudaError_t launch_ssb_audio(const float* d_a48, const SsbParams& P, SsbStreamSt
 // ssb_ext.cu : NCO channel bank + Weaver sideband selection (extension stages)
 cudaError_t launch_ssb_ext(int fmt, const void* iq, const SsbParams& P, const float* d_taps, const uint32_t* d_inc1,
                            uint32_t inc2, int true_sideband, float4* d_start, SsbStreamState* d_state, float* d_a48,
-                           int16_t* d_pcm, int n_streams, int channels, int n_blocks, unsigned long long base_samples,
-                           cudaStream_t st, int* launches);
+                           int16_t* d_pcm, float* d_agc, int n_streams, int channels, int n_blocks,
+                           unsigned long long base_samples, cudaStream_t st, int* launches);
+// ssb.cu : 255-tap decimator over post-AGC samples [n_frames][P.n] -> [n_frames][P.m]
+cudaError_t launch_ssb_fir(const float* xagc, const float* taps, float* a48, const SsbParams& P, int n_frames,
+                           cudaStream_t st);
 // synth.cu
 cudaError_t launch_synth(int fmt, uint32_t fs, int first_stream, int n_streams, int64_t first_sample,
                          int64_t n_samples, void* d_out, const int16_t* d_sine, cudaStream_t st);

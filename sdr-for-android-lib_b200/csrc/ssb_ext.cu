@@ -226,6 +226,116 @@ k_ssbx_main(const void* __restrict__ iq, const __grid_constant__ SsbParams P, co
     }
 }
 
+// ---------------------------------------------------------------- pass 2, split (see k_ssb_agc / k_ssb_fir in ssb.cu)
+// The main pass in sweeps over a 64-byte chunk, without the decimator: post-AGC samples go to xagc [vf][n].
+template <int FMT, bool TSB>
+__global__ void __launch_bounds__(SSBX_WARPS * 32)
+k_ssbx_agc(const void* __restrict__ iq, const __grid_constant__ SsbParams P, const uint32_t* __restrict__ inc1_tab,
+           uint32_t inc2, const float4* __restrict__ start, float* __restrict__ xagc, int n_streams, int channels,
+           int n_blocks, unsigned long long base_samples) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    constexpr int NS = 4 * SsbIngest<FMT>::kPerVec;
+    constexpr int OP = NS + 4;
+    __shared__ const unsigned char* rows_all[SSBX_WARPS][32];
+    __shared__ __align__(16) float s_out[SSBX_WARPS][32 * OP];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t nvf = (size_t)n_streams * channels * n_blocks;
+    const size_t vf0 = ((size_t)blockIdx.x * SSBX_WARPS + warp) * 32;
+    const size_t vf = vf0 + lane;
+    const bool live = vf < nvf;
+    const size_t vfc = live ? vf : nvf - 1;
+    const size_t v = vfc / n_blocks, b = vfc % n_blocks;
+    const size_t block_bytes = (size_t)P.n * sizeof(typename Ingest<FMT>::raw_t);
+    rows_all[warp][lane] = static_cast<const unsigned char*>(iq) + ((v / channels) * n_blocks + b) * block_bytes;
+    __syncthreads();
+    if (vf0 >= nvf) return;
+    TileStreamX ts = {rows_all[warp], smem + warp * 2 * SSB_TILE_BYTES, lane};
+    const int nchunks = (int)(block_bytes / SSB_ROW_BYTES);
+    const float oma = __fsub_rn(1.0f, P.dcAlpha);
+    const uint32_t inc1 = inc1_tab[v % channels];
+    const unsigned long long k0 = base_samples + (unsigned long long)b * (unsigned long long)P.n;
+    const float4 s0 = start[vfc];
+    SsbxLane L = {};
+    L.iz1 = s0.x; L.iz2 = s0.y; L.qz1 = s0.z; L.qz2 = s0.w;
+    L.ph1 = (uint32_t)((unsigned long long)inc1 * k0);
+    L.ph2 = (uint32_t)((unsigned long long)inc2 * k0);
+    float gain = 1.0f;
+    const float omFast = __fsub_rn(1.0f, P.agcFast), omSlow = __fsub_rn(1.0f, P.agcSlow);
+    const bool tgt_ok = ssb_moderate(P.agcTarget);
+    float* tile = s_out[warp];
+    constexpr int LPR = NS / 4, RPI = 32 / LPR;
+
+    ts.issue(0, 0);
+    for (int c = 0; c < nchunks; c++) {
+        if (c + 1 < nchunks) { ts.issue(c + 1, (c + 1) & 1); cp_async_wait<1>(); }
+        else cp_async_wait<0>();
+        __syncwarp();
+        const uint4* row = ts.row(c & 1);
+        float a[NS], des[NS];
+#pragma unroll
+        for (int vv = 0; vv < 4; vv++) {
+            const uint4 d = row[vv];
+#pragma unroll
+            for (int j = 0; j < SsbIngest<FMT>::kPerVec; j++) {
+                float I, Q, yi, yq;
+                SsbIngest<FMT>::get(d, j, I, Q);
+                ssbx_front<TSB>(L, I, Q, P, oma, inc1, yi, yq);
+                float av;
+                if (TSB) {   // Weaver second mix: Re{(yI + j yQ) exp(+/- j theta2)}, doubled
+                    float c2, s2;
+                    nco_cs(L.ph2, c2, s2);
+                    L.ph2 += inc2;
+                    const float p = __fmul_rn(yi, c2), w = __fmul_rn(yq, s2);
+                    const float u = P.upper ? __fsub_rn(p, w) : __fadd_rn(p, w);
+                    av = __fadd_rn(u, u);
+                } else {
+                    av = P.upper ? __fadd_rn(yi, yi) : __fsub_rn(yi, yi);
+                }
+                a[vv * SsbIngest<FMT>::kPerVec + j] = av;
+            }
+        }
+        bool ok = tgt_ok;
+#pragma unroll
+        for (int i = 0; i < NS; i++) {
+            const float mag = __fadd_rn(fabsf(a[i]), 1e-8f);
+            ok = ok && ssb_moderate(mag);
+            des[i] = ssb_div_rn(P.agcTarget, __fadd_rn(ssb_sqrt_rn(mag), 1e-6f));
+        }
+        if (!ok) {
+#pragma unroll 1
+            for (int i = 0; i < NS; i++) {
+                float ai = 0.0f;
+#pragma unroll
+                for (int k = 0; k < NS; k++) if (k == i) ai = a[k];
+                const float mag = __fadd_rn(fabsf(ai), 1e-8f);
+                const float dsr = __fdiv_rn(P.agcTarget, __fadd_rn(__fsqrt_rn(mag), 1e-6f));
+#pragma unroll
+                for (int k = 0; k < NS; k++) if (k == i) des[k] = dsr;
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < NS; i++) {
+            const bool fast = des[i] < gain;
+            gain = __fadd_rn(__fmul_rn(gain, fast ? omFast : omSlow), __fmul_rn(des[i], fast ? P.agcFast : P.agcSlow));
+            const float x = __fmul_rn(a[i], gain);
+            a[i] = x < -1.0f ? -1.0f : (1.0f < x ? 1.0f : x);
+        }
+        float4* mine = reinterpret_cast<float4*>(tile + lane * OP);
+#pragma unroll
+        for (int k = 0; k < LPR; k++) mine[k] = make_float4(a[4 * k], a[4 * k + 1], a[4 * k + 2], a[4 * k + 3]);
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < LPR; i++) {
+            const int r = i * RPI + lane / LPR, col = lane % LPR;
+            const size_t fr = vf0 + r;
+            if (fr < nvf)
+                *reinterpret_cast<float4*>(xagc + fr * (size_t)P.n + (size_t)c * NS + 4 * col) =
+                    *reinterpret_cast<const float4*>(tile + r * OP + 4 * col);
+        }
+        __syncwarp();
+    }
+}
+
 // ---------------------------------------------------------------- launch
 template <int FMT, int SMAX, bool TSB>
 static cudaError_t launch_mainx_t(const void* iq, const SsbParams& P, const float* taps, const uint32_t* inc1,
@@ -256,26 +366,34 @@ static cudaError_t launch_mainx_f(int smax, const void* iq, const SsbParams& P, 
 
 template <int FMT, bool TSB>
 static cudaError_t launch_ssbx_f(const void* iq, const SsbParams& P, const float* d_taps, const uint32_t* d_inc1,
-                                 uint32_t inc2, float4* d_start, SsbStreamState* d_state, float* d_a48, int S, int C,
-                                 int B, unsigned long long base, cudaStream_t st) {
+                                 uint32_t inc2, float4* d_start, SsbStreamState* d_state, float* d_a48, float* d_agc,
+                                 int S, int C, int B, unsigned long long base, cudaStream_t st) {
     const size_t nv = (size_t)S * C;
     k_ssbx_state<FMT, TSB><<<(unsigned)((nv + 31) / 32), 32, 2 * SSB_TILE_BYTES, st>>>(iq, P, d_inc1, d_start, d_state,
                                                                                       S, C, B, base);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
+    const size_t nvf = nv * B;
+    if (d_agc && nvf < (1ull << 31)) {
+        const int grid = (int)((nvf + SSBX_WARPS * 32 - 1) / (SSBX_WARPS * 32));
+        k_ssbx_agc<FMT, TSB><<<grid, SSBX_WARPS * 32, (size_t)SSBX_WARPS * 2 * SSB_TILE_BYTES, st>>>(
+            iq, P, d_inc1, inc2, d_start, d_agc, S, C, B, base);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        return launch_ssb_fir(d_agc, d_taps, d_a48, P, (int)nvf, st);
+    }
     return launch_mainx_f<FMT, TSB>(ssb_smax(P), iq, P, d_taps, d_inc1, inc2, d_start, d_a48, S, C, B, base, st);
 }
 
 cudaError_t launch_ssb_ext(int fmt, const void* iq, const SsbParams& P, const float* d_taps, const uint32_t* d_inc1,
                            uint32_t inc2, int true_sideband, float4* d_start, SsbStreamState* d_state, float* d_a48,
-                           int16_t* d_pcm, int n_streams, int channels, int n_blocks, unsigned long long base_samples,
-                           cudaStream_t st, int* launches) {
+                           int16_t* d_pcm, float* d_agc, int n_streams, int channels, int n_blocks,
+                           unsigned long long base_samples, cudaStream_t st, int* launches) {
     if (n_streams <= 0 || channels <= 0 || n_blocks <= 0) return cudaSuccess;
     cudaError_t e;
 #define SDRB_X(F)                                                                                                      \
-    (true_sideband ? launch_ssbx_f<F, true>(iq, P, d_taps, d_inc1, inc2, d_start, d_state, d_a48, n_streams, channels, \
+    (true_sideband ? launch_ssbx_f<F, true>(iq, P, d_taps, d_inc1, inc2, d_start, d_state, d_a48, d_agc, n_streams, channels, \
                                             n_blocks, base_samples, st)                                                \
-                   : launch_ssbx_f<F, false>(iq, P, d_taps, d_inc1, inc2, d_start, d_state, d_a48, n_streams, channels, \
+                   : launch_ssbx_f<F, false>(iq, P, d_taps, d_inc1, inc2, d_start, d_state, d_a48, d_agc, n_streams, channels, \
                                              n_blocks, base_samples, st))
     switch (fmt) {
         case FMT_CU8: e = SDRB_X(FMT_CU8); break;
@@ -285,7 +403,7 @@ cudaError_t launch_ssb_ext(int fmt, const void* iq, const SsbParams& P, const fl
     }
 #undef SDRB_X
     if (e != cudaSuccess) return e;
-    if (launches) *launches += 2;
+    if (launches) *launches += (d_agc && P.m > 0) ? 3 : 2;
     if (P.m > 0) {
         e = launch_ssb_audio(d_a48, P, d_state, d_pcm, n_streams * channels, n_blocks, st);
         if (launches) (*launches)++;
