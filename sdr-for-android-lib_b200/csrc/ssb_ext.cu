@@ -41,6 +41,18 @@ struct TileStreamX {
     __device__ __forceinline__ const uint4* row(int stage) const {
         return reinterpret_cast<const uint4*>(tile + stage * SSB_TILE_BYTES + lane * SSB_ROW_PITCH);
     }
+    __device__ __forceinline__ void prologue(int nchunks) {
+        for (int k = 0; k < SSB_STAGES - 1; k++) {
+            if (k < nchunks) issue(k, k);
+            else cp_async_commit();
+        }
+    }
+    __device__ __forceinline__ void advance(int c, int nchunks) {
+        const int ahead = c + SSB_STAGES - 1;
+        if (ahead < nchunks) issue(ahead, ahead % SSB_STAGES);
+        else cp_async_commit();
+        cp_async_wait<SSB_STAGES - 1>();
+    }
 };
 
 struct SsbxLane {
@@ -107,17 +119,16 @@ k_ssbx_state(const void* __restrict__ iq, const __grid_constant__ SsbParams P, c
     SsbxLane L = {};
     L.iz1 = state[vc].rf_z1; L.iz2 = state[vc].rf_z2; L.qz1 = state[vc].pad0; L.qz2 = state[vc].pad1;
     L.ph1 = (uint32_t)((unsigned long long)inc1 * base_samples);
-    ts.issue(0, 0);
+    ts.prologue(nchunks);
     int cb = 0, b = 0;
     for (int c = 0; c < nchunks; c++) {
-        if (c + 1 < nchunks) { ts.issue(c + 1, (c + 1) & 1); cp_async_wait<1>(); }
-        else cp_async_wait<0>();
+        ts.advance(c, nchunks);
         __syncwarp();
         if (cb == 0) {
             L.dcr = L.dci = 0.0f;
             if (live) start[v * n_blocks + b] = make_float4(L.iz1, L.iz2, L.qz1, L.qz2);
         }
-        const uint4* row = ts.row(c & 1);
+        const uint4* row = ts.row(c % SSB_STAGES);
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             const uint4 d = row[q];
@@ -142,7 +153,7 @@ k_ssbx_main(const void* __restrict__ iq, const __grid_constant__ SsbParams P, co
             float* __restrict__ a48, int n_streams, int channels, int n_blocks, unsigned long long base_samples) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ const unsigned char* rows_all[SSBX_WARPS][32];
-    float* hT = reinterpret_cast<float*>(smem + SSBX_WARPS * 2 * SSB_TILE_BYTES);
+    float* hT = reinterpret_cast<float*>(smem + SSBX_WARPS * SSB_STAGES * SSB_TILE_BYTES);
     for (int i = threadIdx.x; i < P.decim * SMAX; i += SSBX_WARPS * 32) hT[i] = taps[i];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const size_t nvf = (size_t)n_streams * channels * n_blocks;
@@ -155,7 +166,7 @@ k_ssbx_main(const void* __restrict__ iq, const __grid_constant__ SsbParams P, co
     rows_all[warp][lane] = static_cast<const unsigned char*>(iq) + ((v / channels) * n_blocks + b) * block_bytes;
     __syncthreads();
     if (vf0 >= nvf) return;
-    TileStreamX ts = {rows_all[warp], smem + warp * 2 * SSB_TILE_BYTES, lane};
+    TileStreamX ts = {rows_all[warp], smem + warp * SSB_STAGES * SSB_TILE_BYTES, lane};
     const int nchunks = (int)(block_bytes / SSB_ROW_BYTES);
     const float oma = __fsub_rn(1.0f, P.dcAlpha);
     const uint32_t inc1 = inc1_tab[v % channels];
@@ -174,12 +185,11 @@ k_ssbx_main(const void* __restrict__ iq, const __grid_constant__ SsbParams P, co
     int r = 0, q = 0;
     float* out = a48 + vfc * (size_t)P.m;
 
-    ts.issue(0, 0);
+    ts.prologue(nchunks);
     for (int c = 0; c < nchunks; c++) {
-        if (c + 1 < nchunks) { ts.issue(c + 1, (c + 1) & 1); cp_async_wait<1>(); }
-        else cp_async_wait<0>();
+        ts.advance(c, nchunks);
         __syncwarp();
-        const uint4* row = ts.row(c & 1);
+        const uint4* row = ts.row(c % SSB_STAGES);
 #pragma unroll
         for (int vv = 0; vv < 4; vv++) {
             const uint4 d = row[vv];
@@ -249,7 +259,7 @@ k_ssbx_agc(const void* __restrict__ iq, const __grid_constant__ SsbParams P, con
     rows_all[warp][lane] = static_cast<const unsigned char*>(iq) + ((v / channels) * n_blocks + b) * block_bytes;
     __syncthreads();
     if (vf0 >= nvf) return;
-    TileStreamX ts = {rows_all[warp], smem + warp * 2 * SSB_TILE_BYTES, lane};
+    TileStreamX ts = {rows_all[warp], smem + warp * SSB_STAGES * SSB_TILE_BYTES, lane};
     const int nchunks = (int)(block_bytes / SSB_ROW_BYTES);
     const float oma = __fsub_rn(1.0f, P.dcAlpha);
     const uint32_t inc1 = inc1_tab[v % channels];
@@ -265,12 +275,11 @@ k_ssbx_agc(const void* __restrict__ iq, const __grid_constant__ SsbParams P, con
     float* tile = s_out[warp];
     constexpr int LPR = NS / 4, RPI = 32 / LPR;
 
-    ts.issue(0, 0);
+    ts.prologue(nchunks);
     for (int c = 0; c < nchunks; c++) {
-        if (c + 1 < nchunks) { ts.issue(c + 1, (c + 1) & 1); cp_async_wait<1>(); }
-        else cp_async_wait<0>();
+        ts.advance(c, nchunks);
         __syncwarp();
-        const uint4* row = ts.row(c & 1);
+        const uint4* row = ts.row(c % SSB_STAGES);
         float a[NS], des[NS];
 #pragma unroll
         for (int vv = 0; vv < 4; vv++) {
@@ -341,7 +350,7 @@ template <int FMT, int SMAX, bool TSB>
 static cudaError_t launch_mainx_t(const void* iq, const SsbParams& P, const float* taps, const uint32_t* inc1,
                                   uint32_t inc2, const float4* start, float* a48, int S, int C, int B,
                                   unsigned long long base, cudaStream_t st) {
-    const size_t smem = (size_t)SSBX_WARPS * 2 * SSB_TILE_BYTES + (size_t)P.decim * SMAX * sizeof(float);
+    const size_t smem = (size_t)SSBX_WARPS * SSB_STAGES * SSB_TILE_BYTES + (size_t)P.decim * SMAX * sizeof(float);
     cudaError_t e = cudaFuncSetAttribute(k_ssbx_main<FMT, SMAX, TSB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     const size_t nvf = (size_t)S * C * B;
@@ -369,14 +378,17 @@ static cudaError_t launch_ssbx_f(const void* iq, const SsbParams& P, const float
                                  uint32_t inc2, float4* d_start, SsbStreamState* d_state, float* d_a48, float* d_agc,
                                  int S, int C, int B, unsigned long long base, cudaStream_t st) {
     const size_t nv = (size_t)S * C;
-    k_ssbx_state<FMT, TSB><<<(unsigned)((nv + 31) / 32), 32, 2 * SSB_TILE_BYTES, st>>>(iq, P, d_inc1, d_start, d_state,
+    k_ssbx_state<FMT, TSB><<<(unsigned)((nv + 31) / 32), 32, SSB_STAGES * SSB_TILE_BYTES, st>>>(iq, P, d_inc1, d_start, d_state,
                                                                                       S, C, B, base);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     const size_t nvf = nv * B;
     if (d_agc && nvf < (1ull << 31)) {
         const int grid = (int)((nvf + SSBX_WARPS * 32 - 1) / (SSBX_WARPS * 32));
-        k_ssbx_agc<FMT, TSB><<<grid, SSBX_WARPS * 32, (size_t)SSBX_WARPS * 2 * SSB_TILE_BYTES, st>>>(
+        const size_t asmem = (size_t)SSBX_WARPS * SSB_STAGES * SSB_TILE_BYTES;
+        if ((e = cudaFuncSetAttribute(k_ssbx_agc<FMT, TSB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asmem)) != cudaSuccess)
+            return e;
+        k_ssbx_agc<FMT, TSB><<<grid, SSBX_WARPS * 32, asmem, st>>>(
             iq, P, d_inc1, inc2, d_start, d_agc, S, C, B, base);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         return launch_ssb_fir(d_agc, d_taps, d_a48, P, (int)nvf, st);
