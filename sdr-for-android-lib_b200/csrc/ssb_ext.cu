@@ -24,6 +24,7 @@
 namespace sdrb {
 
 // Warp-level streamer whose 32 rows are arbitrary byte ranges (one pointer per lane's row).
+template <int NST>
 struct TileStreamX {
     const unsigned char* const* rowptr;   // this warp's 32 row pointers (shared memory)
     unsigned char* tile;                  // this warp's two tiles
@@ -42,17 +43,18 @@ struct TileStreamX {
         return reinterpret_cast<const uint4*>(tile + stage * SSB_TILE_BYTES + lane * SSB_ROW_PITCH);
     }
     __device__ __forceinline__ void prologue(int nchunks) {
-        for (int k = 0; k < SSB_STAGES - 1; k++) {
+        for (int k = 0; k < NST - 1; k++) {
             if (k < nchunks) issue(k, k);
             else cp_async_commit();
         }
     }
     __device__ __forceinline__ void advance(int c, int nchunks) {
-        const int ahead = c + SSB_STAGES - 1;
-        if (ahead < nchunks) issue(ahead, ahead % SSB_STAGES);
+        const int ahead = c + NST - 1;
+        if (ahead < nchunks) issue(ahead, ahead % NST);
         else cp_async_commit();
-        cp_async_wait<SSB_STAGES - 1>();
+        cp_async_wait<NST - 1>();
     }
+    __device__ __forceinline__ const uint4* cur(int c) const { return row(c % NST); }
 };
 
 struct SsbxLane {
@@ -111,7 +113,7 @@ k_ssbx_state(const void* __restrict__ iq, const __grid_constant__ SsbParams P, c
     const size_t block_bytes = (size_t)P.n * sizeof(typename Ingest<FMT>::raw_t);
     rows[lane] = static_cast<const unsigned char*>(iq) + (vc / channels) * block_bytes * n_blocks;
     __syncwarp();
-    TileStreamX ts = {rows, smem, lane};
+    TileStreamX<SSB_STAGES> ts = {rows, smem, lane};
     const int chunks_per_block = (int)(block_bytes / SSB_ROW_BYTES);
     const int nchunks = chunks_per_block * n_blocks;
     const float oma = __fsub_rn(1.0f, P.dcAlpha);
@@ -128,7 +130,7 @@ k_ssbx_state(const void* __restrict__ iq, const __grid_constant__ SsbParams P, c
             L.dcr = L.dci = 0.0f;
             if (live) start[v * n_blocks + b] = make_float4(L.iz1, L.iz2, L.qz1, L.qz2);
         }
-        const uint4* row = ts.row(c % SSB_STAGES);
+        const uint4* row = ts.cur(c);
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             const uint4 d = row[q];
@@ -153,7 +155,7 @@ k_ssbx_main(const void* __restrict__ iq, const __grid_constant__ SsbParams P, co
             float* __restrict__ a48, int n_streams, int channels, int n_blocks, unsigned long long base_samples) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ const unsigned char* rows_all[SSBX_WARPS][32];
-    float* hT = reinterpret_cast<float*>(smem + SSBX_WARPS * SSB_STAGES * SSB_TILE_BYTES);
+    float* hT = reinterpret_cast<float*>(smem + SSBX_WARPS * SSB_MAIN_STAGES * SSB_TILE_BYTES);
     for (int i = threadIdx.x; i < P.decim * SMAX; i += SSBX_WARPS * 32) hT[i] = taps[i];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const size_t nvf = (size_t)n_streams * channels * n_blocks;
@@ -166,7 +168,7 @@ k_ssbx_main(const void* __restrict__ iq, const __grid_constant__ SsbParams P, co
     rows_all[warp][lane] = static_cast<const unsigned char*>(iq) + ((v / channels) * n_blocks + b) * block_bytes;
     __syncthreads();
     if (vf0 >= nvf) return;
-    TileStreamX ts = {rows_all[warp], smem + warp * SSB_STAGES * SSB_TILE_BYTES, lane};
+    TileStreamX<SSB_MAIN_STAGES> ts = {rows_all[warp], smem + warp * SSB_MAIN_STAGES * SSB_TILE_BYTES, lane};
     const int nchunks = (int)(block_bytes / SSB_ROW_BYTES);
     const float oma = __fsub_rn(1.0f, P.dcAlpha);
     const uint32_t inc1 = inc1_tab[v % channels];
@@ -189,7 +191,7 @@ k_ssbx_main(const void* __restrict__ iq, const __grid_constant__ SsbParams P, co
     for (int c = 0; c < nchunks; c++) {
         ts.advance(c, nchunks);
         __syncwarp();
-        const uint4* row = ts.row(c % SSB_STAGES);
+        const uint4* row = ts.cur(c);
 #pragma unroll
         for (int vv = 0; vv < 4; vv++) {
             const uint4 d = row[vv];
@@ -259,7 +261,7 @@ k_ssbx_agc(const void* __restrict__ iq, const __grid_constant__ SsbParams P, con
     rows_all[warp][lane] = static_cast<const unsigned char*>(iq) + ((v / channels) * n_blocks + b) * block_bytes;
     __syncthreads();
     if (vf0 >= nvf) return;
-    TileStreamX ts = {rows_all[warp], smem + warp * SSB_STAGES * SSB_TILE_BYTES, lane};
+    TileStreamX<SSB_MAIN_STAGES> ts = {rows_all[warp], smem + warp * SSB_MAIN_STAGES * SSB_TILE_BYTES, lane};
     const int nchunks = (int)(block_bytes / SSB_ROW_BYTES);
     const float oma = __fsub_rn(1.0f, P.dcAlpha);
     const uint32_t inc1 = inc1_tab[v % channels];
@@ -279,7 +281,7 @@ k_ssbx_agc(const void* __restrict__ iq, const __grid_constant__ SsbParams P, con
     for (int c = 0; c < nchunks; c++) {
         ts.advance(c, nchunks);
         __syncwarp();
-        const uint4* row = ts.row(c % SSB_STAGES);
+        const uint4* row = ts.cur(c);
         float a[NS], des[NS];
 #pragma unroll
         for (int vv = 0; vv < 4; vv++) {
@@ -350,7 +352,7 @@ template <int FMT, int SMAX, bool TSB>
 static cudaError_t launch_mainx_t(const void* iq, const SsbParams& P, const float* taps, const uint32_t* inc1,
                                   uint32_t inc2, const float4* start, float* a48, int S, int C, int B,
                                   unsigned long long base, cudaStream_t st) {
-    const size_t smem = (size_t)SSBX_WARPS * SSB_STAGES * SSB_TILE_BYTES + (size_t)P.decim * SMAX * sizeof(float);
+    const size_t smem = (size_t)SSBX_WARPS * SSB_MAIN_STAGES * SSB_TILE_BYTES + (size_t)P.decim * SMAX * sizeof(float);
     cudaError_t e = cudaFuncSetAttribute(k_ssbx_main<FMT, SMAX, TSB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     const size_t nvf = (size_t)S * C * B;
@@ -385,7 +387,7 @@ static cudaError_t launch_ssbx_f(const void* iq, const SsbParams& P, const float
     const size_t nvf = nv * B;
     if (d_agc && nvf < (1ull << 31)) {
         const int grid = (int)((nvf + SSBX_WARPS * 32 - 1) / (SSBX_WARPS * 32));
-        const size_t asmem = (size_t)SSBX_WARPS * SSB_STAGES * SSB_TILE_BYTES;
+        const size_t asmem = (size_t)SSBX_WARPS * SSB_MAIN_STAGES * SSB_TILE_BYTES;
         if ((e = cudaFuncSetAttribute(k_ssbx_agc<FMT, TSB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asmem)) != cudaSuccess)
             return e;
         k_ssbx_agc<FMT, TSB><<<grid, SSBX_WARPS * 32, asmem, st>>>(
