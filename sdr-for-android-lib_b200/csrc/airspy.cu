@@ -82,13 +82,14 @@ __device__ __forceinline__ void air_walk(const uint4* __restrict__ in, float4* _
 //
 // A lane walks one chunk, so the 32 lanes of a warp sit 32 KiB (input) / 64 KiB (output) apart: direct 16-byte
 // loads and stores would touch 32 different lines per instruction.  Instead the warp moves PIECES of 32 samples
-// per row: 64 bytes of every row come in with cp.async (4 lanes x 16 B per row, double-buffered), a lane walks
+// per row: 64 bytes of every row come in with cp.async (4 lanes x 16 B per row, four pieces in flight), a lane walks
 // its own row from shared memory, leaves its 32 translated samples in an output tile, and the warp writes the
 // tile out 4 rows x 128 contiguous bytes per instruction.  Row pitches (80 B in, 144 B out) keep the 16-byte
 // accesses of a quarter-warp on distinct banks.
 constexpr int AIRDC_WARPS = 2;
 constexpr int AIRDC_IN_PITCH = 80, AIRDC_OUT_PITCH = 144;
 constexpr int AIRDC_IN_TILE = 32 * AIRDC_IN_PITCH, AIRDC_OUT_TILE = 32 * AIRDC_OUT_PITCH;
+constexpr int AIRDC_STAGES = 4;   // pieces in flight per warp: a 32-sample piece is shorter than a memory round trip
 struct __align__(8) AirRow {
     const uint16_t* in;   // first sample the lane walks (run-in included)
     float* out;           // where the chunk's own first translated sample goes
@@ -99,7 +100,7 @@ __global__ void __launch_bounds__(AIRDC_WARPS * 32)
 k_airspy_dc(const uint16_t* __restrict__ raw, const AirspyStreamState* __restrict__ state, float* __restrict__ T,
             float* __restrict__ from, float* __restrict__ upto, int n_streams, long long n_real, int n_chunks,
             int chunk, int warm) {
-    __shared__ __align__(16) unsigned char s_in[AIRDC_WARPS][2 * AIRDC_IN_TILE];
+    __shared__ __align__(16) unsigned char s_in[AIRDC_WARPS][AIRDC_STAGES * AIRDC_IN_TILE];
     __shared__ __align__(16) unsigned char s_out[AIRDC_WARPS][AIRDC_OUT_TILE];
     __shared__ AirRow s_rows[AIRDC_WARPS][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -147,17 +148,17 @@ k_airspy_dc(const uint16_t* __restrict__ raw, const AirspyStreamState* __restric
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
-    issue(0, 0);
+    for (int k = 0; k < AIRDC_STAGES - 1; k++) {   // one commit group per piece, empty past the end
+        if (k < P) issue(k, k);
+        else asm volatile("cp.async.commit_group;" ::: "memory");
+    }
     for (int p = 0; p < P; p++) {
-        if (p + 1 < P) {
-            issue(p + 1, (p + 1) & 1);
-            asm volatile("cp.async.wait_group 1;" ::: "memory");
-        } else {
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
-        }
+        if (p + AIRDC_STAGES - 1 < P) issue(p + AIRDC_STAGES - 1, (p + AIRDC_STAGES - 1) % AIRDC_STAGES);
+        else asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group %0;" ::"n"(AIRDC_STAGES - 1) : "memory");
         __syncwarp();
         if (32 * p == me.w && live) from[id] = avg;          // the run-in ends on a piece boundary
-        const uint4* row = reinterpret_cast<const uint4*>(tin + (p & 1) * AIRDC_IN_TILE + lane * AIRDC_IN_PITCH);
+        const uint4* row = reinterpret_cast<const uint4*>(tin + (p % AIRDC_STAGES) * AIRDC_IN_TILE + lane * AIRDC_IN_PITCH);
         float4* mine = reinterpret_cast<float4*>(tout + lane * AIRDC_OUT_PITCH);
 #pragma unroll
         for (int q = 0; q < 4; q++) {
