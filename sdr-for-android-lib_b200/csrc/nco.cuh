@@ -5,10 +5,24 @@
 #pragma once
 #include <math.h>
 #include <stdint.h>
+#include <string.h>
 
 #include "fft_core.cuh"
 
 namespace sdrb {
+
+// x with its sign bit XORed by `sign` (0 or 0x80000000): exact negation
+SDRB_HD float nco_flip(float x, uint32_t sign) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(__float_as_uint(x) ^ sign);
+#else
+    uint32_t u;
+    memcpy(&u, &x, 4);
+    u ^= sign;
+    memcpy(&x, &u, 4);
+    return x;
+#endif
+}
 
 // cos/sin of a 32-bit phase (turns * 2^32): quadrant reduction, Cephes minimax polynomials.
 SDRB_HD void nco_cs(uint32_t phase, float& c_out, float& s_out) {
@@ -30,9 +44,13 @@ SDRB_HD void nco_cs(uint32_t phase, float& c_out, float& s_out) {
     cp = fmaf(z, cp, 4.166664568298827e-2f);
     cp = fmaf(z, cp, -0.5f);
     const float c = fmaf(z, cp, 1.0f);
+    // quadrant: (c, s), (-s, c), (-c, -s), (s, -c) for q = 0..3, as one swap and two sign flips (no branches:
+    // a 4-way ?: chain compiled to branches cost the one-warp state pass a cycle per instruction)
     const uint32_t qq = q & 3u;
-    c_out = qq == 0 ? c : (qq == 1 ? -s : (qq == 2 ? -c : s));
-    s_out = qq == 0 ? s : (qq == 1 ? c : (qq == 2 ? -s : -c));
+    const bool swap = (qq & 1u) != 0;
+    const float cc = swap ? s : c, ss = swap ? c : s;
+    c_out = nco_flip(cc, ((qq + 1u) & 2u) << 30);
+    s_out = nco_flip(ss, (qq & 2u) << 30);
 }
 
 // Phase increment of f_hz at sample rate fs (two's complement for negative offsets).
