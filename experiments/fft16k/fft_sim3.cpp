@@ -8,7 +8,7 @@
 #include <set>
 #include <vector>
 
-#include "fft_tables.h"
+#include "fft_tables_exp.h"
 
 using namespace sdrb;
 

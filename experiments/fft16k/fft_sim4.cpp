@@ -7,7 +7,7 @@
 #include <cstdlib>
 #include <vector>
 
-#include "fft_tables.h"
+#include "fft_tables_exp.h"
 
 using namespace sdrb;
 

@@ -41,7 +41,6 @@ struct sdrb_ctx {
     int n_streams = 0, max_blocks = 0;
     int rfMode = -1;            // latched by the first SSB call (static rfFilter, ssb_demod_opt.cpp:261-263)
     int fftPath = 0;
-    int fft16k_gen = 2;         // 2 = scalar-FP32 kernel (default), 3 = packed-FP32 kernel (SDRB_FFT16K=3); same speed, see DESIGN.md 5.1
     EstGeometry geo = {};
     SsbParams ssb = {};
     float taps255[256] = {};
@@ -64,9 +63,10 @@ struct sdrb_ctx {
     float* d_a48 = nullptr;
     int16_t* d_pcm = nullptr;
     float* d_taps = nullptr;
-    cpx* d_tables16k = nullptr;            // v2 tables
-    unsigned char* d_tables16k3 = nullptr;  // v3 tables
-    cpx* d_tables16k4 = nullptr;            // v4 tables (TQ | T3)
+    float* d_tapsE = nullptr;   // rotated tap table of the fused AGC + decimator pass (ssb.cu:k_ssb_main)
+    int ssb_sp = 0;             // its accumulator count; 0 = the decimation factor is outside its range (split pair)
+    cpx* d_tables16k = nullptr;   // 16K kernel tables (TP | T2)
+    int* d_ticket = nullptr;      // transform counter of the 16K kernel when it shares the SMs with the SSB chain
     cpx* d_tw = nullptr;
     cpx *d_sa = nullptr, *d_sb = nullptr;
     cpx* d_fb_tables = nullptr;   // four-step twiddle tables
@@ -110,6 +110,13 @@ struct sdrb_ctx {
     bool est_overlap = false;
     cudaStream_t s_aux = nullptr;
     cudaEvent_t ev_chunk[4] = {}, ev_aux = nullptr;
+    // FFT + SSB in one call: the SSB chain runs on its own stream beside the FFT chain (both read the same raw IQ,
+    // src/sdr-bridge-java-soapy.cpp:441-444 hands one buffer to both processors).  The per-stream state pass is a
+    // latency-bound walk of one warp per 32 streams; under the FFT kernel it costs issue slots only.  SDRB_SSB_FORK=0
+    // serialises the two chains on the caller's stream.
+    bool ssb_fork = true;
+    cudaStream_t s_ssb = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     // host-to-host pipeline (sdrb_process_host)
     cudaStream_t s_in = nullptr, s_out = nullptr;
     cudaEvent_t ev_in[32] = {}, ev_done[32] = {};
@@ -136,7 +143,7 @@ static int fail(sdrb_ctx* c, int code, const char* fmt, ...) {
 static void free_buffers(sdrb_ctx* c) {
     void** ptrs[] = {(void**)&c->d_geo, &c->d_in, (void**)&c->d_power, (void**)&c->d_local, (void**)&c->d_results,
                      (void**)&c->d_fft_state, (void**)&c->d_ssb_state, &c->d_start,
-                     (void**)&c->d_a48, (void**)&c->d_pcm, (void**)&c->d_taps, (void**)&c->d_tw, (void**)&c->d_sa,
+                     (void**)&c->d_a48, (void**)&c->d_pcm, (void**)&c->d_taps, (void**)&c->d_tapsE, (void**)&c->d_tw, (void**)&c->d_sa,
                      (void**)&c->d_sb, (void**)&c->d_est_scratch, (void**)&c->d_inc1, (void**)&c->d_win,
                      (void**)&c->d_front, (void**)&c->d_fb_tables, (void**)&c->d_fbA,
                      (void**)&c->d_sp_state, (void**)&c->d_au_state, (void**)&c->d_sp_e, (void**)&c->d_sp_f,
@@ -175,7 +182,8 @@ int sdrb_create(int device, sdrb_ctx** out) {
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
-        (e = fft_big_prepare()) != cudaSuccess || (e = estimator_prepare()) != cudaSuccess) {
+        (e = fft_big_prepare()) != cudaSuccess || (e = estimator_prepare()) != cudaSuccess ||
+        (e = ssb_prepare()) != cudaSuccess) {
         fail(nullptr, SDRB_ERR_CUDA, "context setup: %s", cudaGetErrorString(e));
         delete ctx;
         return SDRB_ERR_CUDA;
@@ -188,21 +196,13 @@ int sdrb_create(int device, sdrb_ctx** out) {
     if (hc_env) ctx->host_chunks = atoi(hc_env);
     const char* ov_env = getenv("SDRB_EST_OVERLAP");
     ctx->est_overlap = ov_env && ov_env[0] == '1';
-    const char* gen = getenv("SDRB_FFT16K");
-    ctx->fft16k_gen = (gen && gen[0] >= '2' && gen[0] <= '5') ? gen[0] - '0' : 2;
+    const char* fk_env = getenv("SDRB_SSB_FORK");
+    ctx->ssb_fork = !(fk_env && fk_env[0] == '0');
     const std::vector<cpx> t16 = make_f2_tables();
-    const std::vector<cpx> t4 = make_f4_tables();
-    const std::vector<unsigned char> t3 = make_f3_tables();
     if ((e = cudaMalloc(&ctx->d_tables16k, t16.size() * sizeof(cpx))) != cudaSuccess ||
         (e = cudaMemcpy(ctx->d_tables16k, t16.data(), t16.size() * sizeof(cpx), cudaMemcpyHostToDevice)) != cudaSuccess ||
         (e = fft16k2_prepare(t16.data())) != cudaSuccess ||
-        (e = fft16k3_prepare(t3.data())) != cudaSuccess ||
-        (e = cudaMalloc(&ctx->d_tables16k3, t3.size())) != cudaSuccess ||
-        (e = cudaMemcpy(ctx->d_tables16k3, t3.data(), t3.size(), cudaMemcpyHostToDevice)) != cudaSuccess ||
-        (e = cudaMalloc(&ctx->d_tables16k4, t4.size() * sizeof(cpx))) != cudaSuccess ||
-        (e = cudaMemcpy(ctx->d_tables16k4, t4.data(), t4.size() * sizeof(cpx), cudaMemcpyHostToDevice)) != cudaSuccess ||
-        (e = fft16k4_prepare(t4.data())) != cudaSuccess ||
-        (e = fft16k5_prepare(t4.data())) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->d_ticket, sizeof(int))) != cudaSuccess ||
         (e = cudaMalloc(&ctx->d_sine, SYNTH_SINE_N * sizeof(int16_t))) != cudaSuccess ||
         (e = cudaMemcpy(ctx->d_sine, synth_sine_table(), SYNTH_SINE_N * sizeof(int16_t), cudaMemcpyHostToDevice)) != cudaSuccess) {
         fail(nullptr, SDRB_ERR_CUDA, "table upload: %s", cudaGetErrorString(e));
@@ -219,12 +219,14 @@ int sdrb_destroy(sdrb_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     free_buffers(ctx);
     if (ctx->d_tables16k) cudaFree(ctx->d_tables16k);
-    if (ctx->d_tables16k3) cudaFree(ctx->d_tables16k3);
-    if (ctx->d_tables16k4) cudaFree(ctx->d_tables16k4);
+    if (ctx->d_ticket) cudaFree(ctx->d_ticket);
     if (ctx->d_sine) cudaFree(ctx->d_sine);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->s_aux) cudaStreamDestroy(ctx->s_aux);
+    if (ctx->s_ssb) cudaStreamDestroy(ctx->s_ssb);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
     for (auto& e : ctx->ev_chunk) if (e) cudaEventDestroy(e);
     if (ctx->ev_aux) cudaEventDestroy(ctx->ev_aux);
     if (ctx->s_in) cudaStreamDestroy(ctx->s_in);
@@ -263,7 +265,7 @@ static int check_config(sdrb_ctx* ctx, const sdrb_config* cfg) {
     return SDRB_OK;
 }
 
-static int fft_path_for(int n) { return n == F3_N ? 1 : (fft_big_supports(n) ? 2 : 0); }
+static int fft_path_for(int n) { return n == F2_N ? 1 : (fft_big_supports(n) ? 2 : 0); }
 
 extern "C" int sdrb_plan_config(const sdrb_config* cfg, sdrb_plan* out) {
     if (!out) return fail(nullptr, SDRB_ERR_ARG, "plan out is NULL");
@@ -326,6 +328,16 @@ static int upload_ssb(sdrb_ctx* ctx) {
     if (ctx->d_taps) { cudaFree(ctx->d_taps); ctx->d_taps = nullptr; }
     CK(cudaMalloc(&ctx->d_taps, t.size() * sizeof(float)));
     CK(cudaMemcpy(ctx->d_taps, t.data(), t.size() * sizeof(float), cudaMemcpyHostToDevice));
+    // fused AGC + decimator pass (reference-exact chain only): accumulator count and rotated tap table
+    if (ctx->d_tapsE) { cudaFree(ctx->d_tapsE); ctx->d_tapsE = nullptr; }
+    const int kfmt = ctx->cfg.inputFormat == SDRB_RU16 ? (int)FMT_CF32 : ctx->cfg.inputFormat;
+    const char* fe = getenv("SDRB_SSB_FUSED");
+    ctx->ssb_sp = (ctx->ssb_ext || (fe && fe[0] == '0')) ? 0 : ssb_fused_slots(ctx->ssb, kfmt);
+    if (ctx->ssb_sp > 0) {
+        const std::vector<float> te = ssb_fused_tap_table(ctx->taps255, ctx->ssb, ctx->ssb_sp);
+        CK(cudaMalloc(&ctx->d_tapsE, te.size() * sizeof(float)));
+        CK(cudaMemcpy(ctx->d_tapsE, te.data(), te.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
     return SDRB_OK;
 }
 
@@ -516,15 +528,17 @@ static int ensure_ssb_buffers(sdrb_ctx* ctx) {
     if (!ctx->d_a48) CK(cudaMalloc(&ctx->d_a48, frames * m * sizeof(float)));
     if (!ctx->d_pcm) CK(cudaMalloc(&ctx->d_pcm, frames * m * sizeof(int16_t)));
     // scratch of the split AGC / decimator pair: one float per input sample (and per channel of an NCO bank).
-    // Without it (SDRB_SSB_SPLIT=0, or no memory) the fused k_ssb_main runs.
-    if (!ctx->d_agc && !ctx->agc_tried) {
+    // The reference-exact chain needs it only when the fused pass does not take the decimation factor (then it is
+    // required); the extended chain falls back to its own fused kernel without it (SDRB_SSB_SPLIT=0, or no memory).
+    if (!ctx->d_agc && !ctx->agc_tried && (ctx->ssb_ext || ctx->ssb_sp == 0)) {
         ctx->agc_tried = true;
         const char* e = getenv("SDRB_SSB_SPLIT");
-        if (!(e && e[0] == '0')) {
+        if (!ctx->ssb_ext || !(e && e[0] == '0')) {
             const size_t bytes = frames * (size_t)ctx->cfg.samplesPerReading * sizeof(float);   // frames includes the channels
             if (cudaMalloc(&ctx->d_agc, bytes) != cudaSuccess) {
                 cudaGetLastError();
                 ctx->d_agc = nullptr;
+                if (!ctx->ssb_ext) return fail(ctx, SDRB_ERR_NOMEM, "no memory for the %zu-byte AGC scratch of the split SSB pass", bytes);
             }
         }
     }
@@ -598,6 +612,36 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
         fmt = FMT_CF32;
     }
     const size_t bps = sdrb_format_bytes(fmt);
+    // the SSB chain on `ss` (the caller's stream, or the side stream when it runs beside the FFT chain)
+    auto run_ssb = [&](cudaStream_t ss) -> int {
+        const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 0;
+        if (!ctx->ssb_ext) {
+            CK(launch_ssb(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_tapsE, ctx->ssb_sp, static_cast<float2*>(ctx->d_start) + f0s,
+                          ctx->d_ssb_state + s0, ctx->d_a48 + f0s * m, ctx->d_pcm + f0s * m,
+                          ctx->d_agc ? ctx->d_agc + f0s * (size_t)n : nullptr, ns, n_blocks, ss, &launches));
+        } else {
+            const size_t C = (size_t)ctx->channels;
+            CK(launch_ssb_ext(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_inc1, ctx->inc2, ctx->cfg.ssbTrueSideband != 0,
+                              static_cast<float4*>(ctx->d_start) + f0s * C, ctx->d_ssb_state + (size_t)s0 * C,
+                              ctx->d_a48 + f0s * C * m, ctx->d_pcm + f0s * C * m,
+                              ctx->d_agc ? ctx->d_agc + f0s * C * (size_t)n : nullptr, ns, ctx->channels, n_blocks,
+                              ctx->ssb_samples, ss, &launches));
+        }
+        return SDRB_OK;
+    };
+    const bool fork = (stages & SDRB_STAGE_FFT) && (stages & SDRB_STAGE_SSB) && ctx->ssb_fork;
+    if (fork) {
+        if (!ctx->s_ssb) {
+            CK(cudaStreamCreateWithFlags(&ctx->s_ssb, cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+        }
+        CK(cudaEventRecord(ctx->ev_fork, st));
+        CK(cudaStreamWaitEvent(ctx->s_ssb, ctx->ev_fork, 0));
+        int rc = run_ssb(ctx->s_ssb);     // launched first: the state pass takes its SM slots before the FFT CTAs arrive
+        if (rc != SDRB_OK) return rc;
+        CK(cudaEventRecord(ctx->ev_join, ctx->s_ssb));
+    }
     if (stages & SDRB_STAGE_FFT) {
         float* power = ctx->d_power + f0s * n;
         if (time_fft && ctx->fftPath != 1) CK(cudaEventRecord(ctx->ev0, st));
@@ -623,14 +667,8 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
                 const int nf = frames - f0 < chunk ? frames - f0 : chunk;
                 const void* src = static_cast<const unsigned char*>(d_iq) + (size_t)f0 * n * bps;
                 if (time_fft && f0 == 0) CK(cudaEventRecord(ctx->ev0, st));
-                if (ctx->fft16k_gen == 5 && !ctx->front)
-                    CK(launch_fft16k5(fmt, src, power + (size_t)f0 * n, ctx->d_tables16k4, nf, ctx->sm_count, st));
-                else if (ctx->fft16k_gen == 4)
-                    CK(launch_fft16k4(fmt, src, power + (size_t)f0 * n, ctx->d_tables16k4, nf, ctx->sm_count, st, ctx->front, ctx->d_win));
-                else if (ctx->fft16k_gen == 2 || ctx->fft16k_gen == 5)
-                    CK(launch_fft16k2(fmt, src, power + (size_t)f0 * n, ctx->d_tables16k, nf, ctx->sm_count, st, ctx->front, ctx->d_win));
-                else
-                    CK(launch_fft16k3(fmt, src, power + (size_t)f0 * n, ctx->d_tables16k3, nf, ctx->sm_count, st, ctx->front, ctx->d_win));
+                CK(launch_fft16k2(fmt, src, power + (size_t)f0 * n, ctx->d_tables16k, nf, ctx->sm_count, st, ctx->front,
+                                  ctx->d_win, fork ? ctx->d_ticket : nullptr));
                 if (time_fft && f0 == 0) { CK(cudaEventRecord(ctx->ev1, st)); ctx->ev_valid = true; ctx->last_fft_frames = nf; }
                 fft_launches++;
                 if (chunk < frames) {
@@ -701,21 +739,11 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
             launches += 1;
         }
     }
-    if (stages & SDRB_STAGE_SSB) {
-        const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 0;
-        if (!ctx->ssb_ext) {
-            CK(launch_ssb(fmt, d_iq, ctx->ssb, ctx->d_taps, static_cast<float2*>(ctx->d_start) + f0s,
-                          ctx->d_ssb_state + s0, ctx->d_a48 + f0s * m, ctx->d_pcm + f0s * m,
-                          ctx->d_agc ? ctx->d_agc + f0s * (size_t)n : nullptr, ns, n_blocks, st, &launches));
-        } else {
-            const size_t C = (size_t)ctx->channels;
-            CK(launch_ssb_ext(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_inc1, ctx->inc2, ctx->cfg.ssbTrueSideband != 0,
-                              static_cast<float4*>(ctx->d_start) + f0s * C, ctx->d_ssb_state + (size_t)s0 * C,
-                              ctx->d_a48 + f0s * C * m, ctx->d_pcm + f0s * C * m,
-                              ctx->d_agc ? ctx->d_agc + f0s * C * (size_t)n : nullptr, ns, ctx->channels, n_blocks,
-                              ctx->ssb_samples, st, &launches));
-        }
+    if ((stages & SDRB_STAGE_SSB) && !fork) {
+        int rc = run_ssb(st);
+        if (rc != SDRB_OK) return rc;
     }
+    if (fork) CK(cudaStreamWaitEvent(st, ctx->ev_join, 0));
     if (stages & (SDRB_STAGE_SPECTRAL_PULSE | SDRB_STAGE_AUDIO_PULSE)) {
         const size_t C = (size_t)ctx->channels;
         sdrb_pulse_result* out = ctx->d_pulse + f0s * C;

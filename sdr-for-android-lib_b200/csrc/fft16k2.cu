@@ -91,7 +91,7 @@ __device__ __forceinline__ void f2_front(int t, cpx* v, const float* __restrict_
 template <int FMT, int FRONT>
 __global__ void __launch_bounds__(F2_THREADS, 1)
 k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict__ out,
-          const cpx* __restrict__ tables, const float* __restrict__ win, int n_frames) {
+          const cpx* __restrict__ tables, const float* __restrict__ win, int n_frames, int* __restrict__ ticket) {
     typedef typename Ingest2<FMT>::raw_t raw_t;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     cpx* E = reinterpret_cast<cpx*>(smem_raw);
@@ -101,6 +101,7 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
                                                                     F2Smem<FMT>::kStageBytes);
     constexpr bool kStaged = F2Smem<FMT>::kStaged;
     __shared__ cpx red[F2_THREADS / 32];
+    __shared__ int s_next;
     const int t = threadIdx.x;
 
     for (int i = t; i < F2_TP; i += F2_THREADS) TP[i] = tables[i];
@@ -114,8 +115,12 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
     }
     __syncthreads();
 
+    // Which transform a CTA takes next: static round-robin (ticket == nullptr), or the next ticket of a global
+    // counter when other kernels share the SMs (the SSB state pass beside the FFT): a CTA slowed by its
+    // co-tenants then simply takes fewer transforms instead of finishing last.
     unsigned parity = 0;
-    for (; f < n_frames; f += gridDim.x) {
+    int fn;
+    for (; f < n_frames; f = fn) {
         cpx v[32];
         if (kStaged) {
             mbar_wait(bar, parity);
@@ -127,12 +132,17 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
         if (FRONT) f2_front<FRONT>(t, v, win, red);
         fft32(v);
         __syncthreads();  // E is free (previous phase 3 has read it) and the stage has been consumed
-        if (kStaged && t == 0 && f + (int)gridDim.x < n_frames) {
-            mbar_expect_tx(bar, F2Smem<FMT>::kStageBytes);
-            bulk_g2s(stage, in + (size_t)(f + gridDim.x) * F2_N, F2Smem<FMT>::kStageBytes, bar);
+        if (t == 0) {
+            const int nx = ticket ? (int)gridDim.x + atomicAdd(ticket, 1) : f + (int)gridDim.x;
+            s_next = nx;
+            if (kStaged && nx < n_frames) {
+                mbar_expect_tx(bar, F2Smem<FMT>::kStageBytes);
+                bulk_g2s(stage, in + (size_t)nx * F2_N, F2Smem<FMT>::kStageBytes, bar);
+            }
         }
         f2_phase1_twiddle_store(t, TP, v, E);   // twiddle W_N^(t ka) and exchange store, interleaved
         __syncthreads();
+        fn = s_next;   // written before this barrier; rewritten only after the next iteration's first barrier
         f2_phase2(t, E);
         __syncthreads();
         f2_phase3(t, E, F2DevTw(), out + (size_t)f * F2_N);
@@ -162,28 +172,33 @@ cudaError_t fft16k2_prepare(const cpx* host_tables) {
 
 template <int FMT>
 static void launch_fmt(int front, const void* iq, float* power, const cpx* tables, const float* win, int n_frames,
-                       int grid, cudaStream_t st) {
+                       int grid, cudaStream_t st, int* ticket) {
     typedef typename Ingest2<FMT>::raw_t raw_t;
     const raw_t* in = static_cast<const raw_t*>(iq);
     const size_t smem = F2Smem<FMT>::kBytes;
     switch (front & 3) {
-        case 0: k_fft16k2<FMT, 0><<<grid, F2_THREADS, smem, st>>>(in, power, tables, win, n_frames); break;
-        case 1: k_fft16k2<FMT, 1><<<grid, F2_THREADS, smem, st>>>(in, power, tables, win, n_frames); break;
-        case 2: k_fft16k2<FMT, 2><<<grid, F2_THREADS, smem, st>>>(in, power, tables, win, n_frames); break;
-        default: k_fft16k2<FMT, 3><<<grid, F2_THREADS, smem, st>>>(in, power, tables, win, n_frames); break;
+        case 0: k_fft16k2<FMT, 0><<<grid, F2_THREADS, smem, st>>>(in, power, tables, win, n_frames, ticket); break;
+        case 1: k_fft16k2<FMT, 1><<<grid, F2_THREADS, smem, st>>>(in, power, tables, win, n_frames, ticket); break;
+        case 2: k_fft16k2<FMT, 2><<<grid, F2_THREADS, smem, st>>>(in, power, tables, win, n_frames, ticket); break;
+        default: k_fft16k2<FMT, 3><<<grid, F2_THREADS, smem, st>>>(in, power, tables, win, n_frames, ticket); break;
     }
 }
 
 // front: bit 0 = window (win must hold F2_N floats), bit 1 = subtract the block mean
+// ticket: device int for dynamic transform scheduling (zeroed here, on the stream), or nullptr for round-robin
 cudaError_t launch_fft16k2(int fmt, const void* iq, float* power, const cpx* tables, int n_frames, int sm_count,
-                           cudaStream_t st, int front, const float* win) {
+                           cudaStream_t st, int front, const float* win, int* ticket) {
     if (n_frames <= 0) return cudaSuccess;
     if ((front & 1) && !win) return cudaErrorInvalidValue;
     const int grid = n_frames < sm_count ? n_frames : sm_count;
+    if (ticket) {
+        cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(int), st);
+        if (e != cudaSuccess) return e;
+    }
     switch (fmt) {
-        case FMT_CU8: launch_fmt<FMT_CU8>(front, iq, power, tables, win, n_frames, grid, st); break;
-        case FMT_CS16: launch_fmt<FMT_CS16>(front, iq, power, tables, win, n_frames, grid, st); break;
-        case FMT_CF32: launch_fmt<FMT_CF32>(front, iq, power, tables, win, n_frames, grid, st); break;
+        case FMT_CU8: launch_fmt<FMT_CU8>(front, iq, power, tables, win, n_frames, grid, st, ticket); break;
+        case FMT_CS16: launch_fmt<FMT_CS16>(front, iq, power, tables, win, n_frames, grid, st, ticket); break;
+        case FMT_CF32: launch_fmt<FMT_CF32>(front, iq, power, tables, win, n_frames, grid, st, ticket); break;
         default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

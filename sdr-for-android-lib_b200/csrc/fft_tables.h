@@ -4,8 +4,6 @@
 #include <vector>
 
 #include "fft16k2.cuh"
-#include "fft16k3.cuh"
-#include "fft16k4.cuh"
 #include "fft_big.cuh"
 
 namespace sdrb {
@@ -26,33 +24,6 @@ inline std::vector<cpx> make_f2_tables() {
         for (int r = 0; r < 512; r++) TP[j * 512 + r] = twiddle((long long)r << j, F2_N);
     for (int kb = 0; kb < 32; kb++)
         for (int c = 0; c < 16; c++) T2[kb * 16 + c] = twiddle((long long)c * kb, 512);
-    return t;
-}
-
-// Layout (bytes): TP as cpx[5][512] | T2 as pw4[16][16], see fft16k3.cuh
-inline std::vector<unsigned char> make_f3_tables() {
-    std::vector<unsigned char> raw(F3_TABLE_BYTES);
-    cpx* TP = reinterpret_cast<cpx*>(raw.data());
-    pw4* T2 = reinterpret_cast<pw4*>(raw.data() + F3_TP * 8);
-    for (int j = 0; j < 5; j++)
-        for (int r = 0; r < 512; r++) TP[j * 512 + r] = twiddle((long long)r << j, F3_N);
-    for (int k = 0; k < 16; k++)
-        for (int c = 0; c < 16; c++) {
-            const cpx lo = twiddle((long long)c * k, 512), hi = twiddle((long long)c * (k + 16), 512);
-            T2[k * 16 + c].re = mkp(lo.x, hi.x);
-            T2[k * 16 + c].im = mkp(lo.y, hi.y);
-        }
-    return raw;
-}
-
-// Layout: TQ as cpx[6][256] | T3 as cpx[16][16], see fft16k4.cuh
-inline std::vector<cpx> make_f4_tables() {
-    std::vector<cpx> t(F4_TQ + F4_T3);
-    for (int j = 0; j < 5; j++)
-        for (int r = 0; r < 256; r++) t[j * 256 + r] = twiddle((long long)r << j, F4_H);
-    for (int r = 0; r < 256; r++) t[5 * 256 + r] = twiddle(r, F4_N);
-    for (int kb = 0; kb < 16; kb++)
-        for (int c = 0; c < 16; c++) t[F4_TQ + kb * 16 + c] = twiddle((long long)c * kb, 256);
     return t;
 }
 

@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <vector>
+
 #include "../../include/sdr_b200.h"
 #include "fft_core.cuh"
 
@@ -110,20 +112,9 @@ void airspy_chunking(int* chunk, int* warm);
 size_t airspy_work_floats(int n_streams, long long n_real, int chunk);
 // fft16k2.cu : second-generation 16K kernel (512 threads x 32 points, TMA-staged input)
 cudaError_t launch_fft16k2(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
-                           int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);
+                           int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr,
+                           int* ticket = nullptr);
 cudaError_t fft16k2_prepare(const cpx* host_tables);   // make_f2_tables() layout; T2 goes to the constant bank
-// fft16k3.cu : third-generation 16K kernel (packed FP32 pairs, same decomposition and staging)
-cudaError_t launch_fft16k3(int fmt, const void* iq, float* power, const unsigned char* tables, int n_frames,
-                           int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);
-cudaError_t fft16k3_prepare(const unsigned char* host_tables);   // make_f3_tables() layout; T2 goes to the constant bank
-// fft16k4.cu : fourth-generation 16K kernel (two 8192-point jobs per transform, 2 CTAs per SM)
-cudaError_t launch_fft16k4(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
-                           int sm_count, cudaStream_t st, int front = 0, const float* win = nullptr);
-cudaError_t fft16k4_prepare(const cpx* host_tables);
-// fft16k5.cu : fifth-generation 16K kernel (the two jobs of fft16k4 as ping-ponging warp groups of one CTA)
-cudaError_t launch_fft16k5(int fmt, const void* iq, float* power, const cpx* tables, int n_frames,
-                           int sm_count, cudaStream_t st);
-cudaError_t fft16k5_prepare(const cpx* host_tables);
 // fft_any.cu : generic power-of-two path (N != 16384)
 cudaError_t launch_fft_generic(int fmt, const void* iq, float* power, cpx* scratch_a, cpx* scratch_b,
                                const cpx* twiddles, int n, int n_frames, cudaStream_t st, int* launches);
@@ -146,11 +137,16 @@ cudaError_t estimator_prepare();
 size_t estimator_scratch_floats(const EstGeometry& g, int n_frames);
 cudaError_t launch_tracker(const FrameLocal* d_local, const EstGeometry* d_geo, FftStreamState* d_state,
                            sdrb_frame_result* d_results, int n_streams, int n_blocks, cudaStream_t st);
-// ssb.cu.  d_taps is the [decim][ssb_smax] slot-major tap table.
+// ssb.cu.  d_taps is the [decim][ssb_smax] slot-major tap table (split decimator, extended chain);
+// d_tapsE the rotated table of the fused pass (ssb_fused_tap_table), sp = ssb_fused_slots (0: split pair).
 int ssb_smax(const SsbParams& P);
-cudaError_t launch_ssb(int fmt, const void* iq, const SsbParams& P, const float* d_taps, float2* d_start,
-                       SsbStreamState* d_state, float* d_a48, int16_t* d_pcm, float* d_agc, int n_streams, int n_blocks,
-                       cudaStream_t st, int* launches);
+int ssb_fused_slots(const SsbParams& P, int fmt);
+int ssb_fused_rows(const SsbParams& P);
+std::vector<float> ssb_fused_tap_table(const float* h, const SsbParams& P, int sp);
+cudaError_t ssb_prepare();
+cudaError_t launch_ssb(int fmt, const void* iq, const SsbParams& P, const float* d_taps, const float* d_tapsE, int sp,
+                       float2* d_start, SsbStreamState* d_state, float* d_a48, int16_t* d_pcm, float* d_agc,
+                       int n_streams, int n_blocks, cudaStream_t st, int* launches);
 cudaError_t launch_ssb_audio(const float* d_a48, const SsbParams& P, SsbStreamState* d_state, int16_t* d_pcm,
                              int n_streams, int n_blocks, cudaStream_t st);
 // ssb_ext.cu : NCO channel bank + Weaver sideband selection (extension stages)

@@ -21,20 +21,6 @@ def test_fft16k_phase_functions(tmp_path):
     assert r.returncode == 0, r.stdout + r.stderr
 
 
-def test_fft16k_packed_phase_functions(tmp_path):
-    """Third-generation (packed FP32) 16K kernel: spectrum and bank-conflict audit."""
-    r = subprocess.run([_build(tmp_path, "fft_sim3")], capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0, r.stdout + r.stderr
-    assert "0 bad bins, 0 bank conflicts" in r.stdout
-
-
-def test_fft16k_two_job_phase_functions(tmp_path):
-    """Fourth-generation 16K kernel (two 8192-point jobs per transform): spectrum and bank audit."""
-    r = subprocess.run([_build(tmp_path, "fft_sim4")], capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0, r.stdout + r.stderr
-    assert "0 bad bins, 0 bank conflicts" in r.stdout
-
-
 @pytest.mark.parametrize("radix", [16, 32])
 def test_four_step_phase_functions(tmp_path, radix):
     r = subprocess.run([_build(tmp_path, "fft_big_sim"), str(radix)], capture_output=True, text=True, timeout=600)
