@@ -43,9 +43,10 @@ METRIC = "IQ MS/s through FFT+peak+SSB at 1/2/4/8 B200, % HBM roofline, vs host 
 # name -> workload.  S = streams per GPU, B = readings per stream per step.
 WORKLOADS = {
     "default": dict(
-        what="8192 independent RTL-SDR u8 streams per GPU x 8 readings, 2 MS/s: 16384-pt FFT + power/fftshift + peak + "
-             "signal strength + USB demod to int16 PCM (the per-stream work of BASELINE configs[0], batched like configs[1])",
-        S=8192, B=8, n=16384, fs=2_000_000, fmt=CU8, stages=F_FFT | F_SSB, extra={}),
+        what="65536 independent RTL-SDR u8 streams per GPU, one reading of each per step (the reference's own call shape, one "
+             "soapyCallback per reading), 2 MS/s: 16384-pt FFT + power/fftshift + peak + signal strength + USB demod to "
+             "int16 PCM (the per-stream work of BASELINE configs[0], batched like configs[1])",
+        S=65536, B=1, n=16384, fs=2_000_000, fmt=CU8, stages=F_FFT | F_SSB, extra={}),
     "c2": dict(what="1024 independent RTL-SDR u8 streams per GPU, 16384-pt FFT + power/fftshift + peak + signal strength "
                     "only (BASELINE configs[1])",
                S=1024, B=37, n=16384, fs=2_000_000, fmt=CU8, stages=F_FFT, extra={}),
@@ -82,8 +83,9 @@ def parse_args():
     ap.add_argument("--streams", type=int, default=0, help="streams per GPU (0 = the workload's own)")
     ap.add_argument("--blocks", type=int, default=0, help="readings per stream per step (0 = the workload's own)")
     ap.add_argument("--e2e-steps", type=int, default=8)
-    ap.add_argument("--e2e-streams", type=int, default=2048,
-                    help="streams per host-to-host call of the e2e leg (bounds the pinned host memory per rank)")
+    ap.add_argument("--e2e-frames", type=int, default=16384,
+                    help="readings per host-to-host call of the e2e leg (bounds the pinned host memory per rank: 0.5 GiB of "
+                         "u8 IQ in, 1 GiB of spectra out at 16384 points)")
     ap.add_argument("--sustain-seconds", type=float, default=3.0)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -491,7 +493,7 @@ def run_ours(args):
     e2e = None
     peak_rec = None
     if not args.no_e2e:
-        Se = min(S, args.e2e_streams)
+        Se = max(1, min(S, args.e2e_frames // B))
         ch = max(1, int(w["extra"].get("ssbChannels", 1)))
         m = pcm_per_block(n, fs) if stages & F_SSB else 0
         ectx = sdrb.Context(local)

@@ -168,6 +168,13 @@ int  sdrb_set_cuda_stream(sdrb_ctx* ctx, void* cuda_stream);
 /* src/dsp/fft_process.cpp:20-39, src/sdr-bridge-java-soapy.cpp:1123-1128.
  * Allocates device buffers for n_streams x max_blocks readings and resets all per-stream state. */
 int  sdrb_configure(sdrb_ctx* ctx, const sdrb_config* cfg, int n_streams, int max_blocks);
+/* A new geometry (sample rate, block length, focus, mode, centre) for the SAME streams, keeping every carried
+ * state: the reference's FFTProcessor::configure keeps its tracking / detection members (src/dsp/fft_process.cpp:20-39),
+ * the SSB filters are function statics (src/ssb/ssb_demod_opt.cpp:261,277) and the audio pulse detector is a member
+ * of SSBProcessor (src/ssb/ssb_processor.h:52): none of them restarts when the bridge pushes a new configuration.
+ * The spectral pulse detector is rebuilt (its frame rate follows the geometry).  A new centre frequency raises
+ * the isCenterFrequencyChanged side channel.  The channel count cannot change. */
+int  sdrb_replan(sdrb_ctx* ctx, const sdrb_config* cfg, int max_blocks);
 /* setFrequency: new centre for one stream (or all with stream = -1) and raise the
  * isCenterFrequencyChanged side channel (src/sdr-bridge-java-soapy.cpp:897-905, src/sdr-bridge-internal.h:9). */
 int  sdrb_set_center_frequency(sdrb_ctx* ctx, int stream, uint32_t center_hz);

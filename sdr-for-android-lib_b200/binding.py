@@ -9,7 +9,7 @@ CU8, CS16, CF32, RU16 = 0, 1, 2, 3
 STAGE_FFT, STAGE_SSB = 1, 2
 STAGE_SPECTRAL_PULSE, STAGE_AUDIO_PULSE = 4, 8
 _HERE = os.path.dirname(os.path.abspath(__file__))
-lib_path = os.path.join(_HERE, "libsdr_b200.so")
+lib_path = os.environ.get("SDRB_LIB") or os.path.join(_HERE, "libsdr_b200.so")   # SDRB_LIB: A/B builds of the same ABI
 
 
 class SdrbError(RuntimeError):
@@ -85,6 +85,7 @@ EXPORTS = {
     "sdrb_last_error": (C.c_char_p, [C.c_void_p]),
     "sdrb_set_cuda_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "sdrb_configure": (C.c_int, [C.c_void_p, C.POINTER(Config), C.c_int, C.c_int]),
+    "sdrb_replan": (C.c_int, [C.c_void_p, C.POINTER(Config), C.c_int]),
     "sdrb_set_center_frequency": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32]),
     "sdrb_set_focus_range": (C.c_int, [C.c_void_p, C.c_int]),
     "sdrb_set_sound_mode": (C.c_int, [C.c_void_p, C.c_int]),
@@ -198,6 +199,11 @@ class Context:
     def configure(self, cfg, n_streams, max_blocks):
         _check(lib.sdrb_configure(self._h, C.byref(cfg), n_streams, max_blocks), self._h)
         self.cfg, self.n_streams, self.max_blocks = cfg, n_streams, max_blocks
+
+    def replan(self, cfg, max_blocks):
+        """New geometry for the same streams, every carried state kept (sdrb_replan)."""
+        _check(lib.sdrb_replan(self._h, C.byref(cfg), max_blocks), self._h)
+        self.cfg, self.max_blocks = cfg, max_blocks
 
     def set_cuda_stream(self, stream_ptr):
         _check(lib.sdrb_set_cuda_stream(self._h, C.c_void_p(stream_ptr)), self._h)

@@ -16,8 +16,35 @@
 
 using namespace sdrb;
 
+namespace sdrb { thread_local TraceSink* g_trace = nullptr; }
+
 namespace {
 thread_local std::string g_create_error;
+
+// SDRB_TRACE=1: events after every launch group, printed (ms since the call's first mark) by sdrb_sync
+struct EventTrace : sdrb::TraceSink {
+    std::vector<std::pair<std::string, cudaEvent_t>> marks;
+    std::vector<cudaEvent_t> pool;
+    void mark(const char* name, cudaStream_t st) override {
+        cudaEvent_t e;
+        if (!pool.empty()) { e = pool.back(); pool.pop_back(); }
+        else if (cudaEventCreate(&e) != cudaSuccess) return;
+        cudaEventRecord(e, st);
+        marks.emplace_back(name, e);
+    }
+    void dump() {
+        if (marks.empty()) return;
+        cudaEvent_t t0 = marks[0].second;
+        for (auto& m : marks) {
+            float ms = 0.f;
+            if (cudaEventSynchronize(m.second) == cudaSuccess && cudaEventElapsedTime(&ms, t0, m.second) == cudaSuccess)
+                fprintf(stderr, "[sdrb trace] %-22s %8.3f ms\n", m.first.c_str(), ms);
+        }
+        for (auto& m : marks) pool.push_back(m.second);
+        marks.clear();
+    }
+    ~EventTrace() override { for (auto& m : marks) cudaEventDestroy(m.second); for (auto e : pool) cudaEventDestroy(e); }
+};
 
 constexpr size_t kGenericScratchBytes = 256u << 20;  // per ping-pong buffer of the generic FFT
 constexpr size_t kFourStepL2Bytes = 96u << 20;       // four-step intermediate kept within the 126 MB L2
@@ -40,6 +67,8 @@ struct sdrb_ctx {
     sdrb_config cfg = {};
     int n_streams = 0, max_blocks = 0;
     int rfMode = -1;            // latched by the first SSB call (static rfFilter, ssb_demod_opt.cpp:261-263)
+    int effMode = 1;            // last sound mode in 0..2: any other value leaves the reference's file statics as the
+                                // previous call set them (ssb_demod_opt.cpp:17-26,230-255); they start as mode 1
     int fftPath = 0;
     EstGeometry geo = {};
     SsbParams ssb = {};
@@ -114,7 +143,9 @@ struct sdrb_ctx {
     // src/sdr-bridge-java-soapy.cpp:441-444 hands one buffer to both processors).  The per-stream state pass is a
     // latency-bound walk of one warp per 32 streams; under the FFT kernel it costs issue slots only.  SDRB_SSB_FORK=0
     // serialises the two chains on the caller's stream.
+    EventTrace* trace = nullptr;
     bool ssb_fork = true;
+    bool ssb_first = false;     // SDRB_SSB_FIRST=1: launch the SSB chain before the FFT chain (measured slower)
     cudaStream_t s_ssb = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     // host-to-host pipeline (sdrb_process_host)
@@ -196,8 +227,12 @@ int sdrb_create(int device, sdrb_ctx** out) {
     if (hc_env) ctx->host_chunks = atoi(hc_env);
     const char* ov_env = getenv("SDRB_EST_OVERLAP");
     ctx->est_overlap = ov_env && ov_env[0] == '1';
+    const char* tr_env = getenv("SDRB_TRACE");
+    if (tr_env && tr_env[0] == '1') ctx->trace = new EventTrace();
     const char* fk_env = getenv("SDRB_SSB_FORK");
     ctx->ssb_fork = !(fk_env && fk_env[0] == '0');
+    const char* sf_env = getenv("SDRB_SSB_FIRST");
+    ctx->ssb_first = sf_env && sf_env[0] == '1';
     const std::vector<cpx> t16 = make_f2_tables();
     if ((e = cudaMalloc(&ctx->d_tables16k, t16.size() * sizeof(cpx))) != cudaSuccess ||
         (e = cudaMemcpy(ctx->d_tables16k, t16.data(), t16.size() * sizeof(cpx), cudaMemcpyHostToDevice)) != cudaSuccess ||
@@ -236,6 +271,7 @@ int sdrb_destroy(sdrb_ctx* ctx) {
         if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
     }
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+    delete ctx->trace;
     delete ctx;
     return SDRB_OK;
 }
@@ -306,9 +342,10 @@ static int upload_geometry(sdrb_ctx* ctx) {
 }
 
 static int upload_ssb(sdrb_ctx* ctx) {
-    const int rf = ctx->rfMode >= 0 ? ctx->rfMode : ctx->cfg.soundMode;
+    if (ctx->cfg.soundMode >= 0 && ctx->cfg.soundMode <= 2) ctx->effMode = ctx->cfg.soundMode;
+    const int rf = ctx->rfMode >= 0 ? ctx->rfMode : ctx->effMode;
     const bool tsb = ctx->cfg.ssbTrueSideband != 0;
-    design_ssb(ctx->cfg.sampleRate, ctx->cfg.samplesPerReading, rf, ctx->cfg.soundMode, ctx->cfg.upperSideband, tsb,
+    design_ssb(ctx->cfg.sampleRate, ctx->cfg.samplesPerReading, rf, ctx->effMode, ctx->cfg.upperSideband, tsb,
                ctx->ssb, ctx->taps255);
     // NCO increments of the channel bank (extension; oracle/sdr_oracle_ext.c): channel c is tuned to
     // offset + c * spacing; with true sideband the first mix goes to the sideband centre (+/- B/2)
@@ -449,6 +486,48 @@ int sdrb_configure(sdrb_ctx* ctx, const sdrb_config* cfg, int n_streams, int max
     return SDRB_OK;
 }
 
+// A new geometry for the SAME streams with every carried state kept: what the reference does when the bridge
+// pushes a new configuration (FFTProcessor::configure keeps its tracking / detection members, fft_process.cpp:20-39;
+// the SSB filters are function statics and the audio pulse detector a member of SSBProcessor, so they survive any
+// change of sample rate or block length: ssb_demod_opt.cpp:261,277, ssb_processor.h:52).
+int sdrb_replan(sdrb_ctx* ctx, const sdrb_config* cfg, int max_blocks) {
+    if (!ctx || !ctx->configured) return fail(ctx, SDRB_ERR_STATE, "sdrb_replan before sdrb_configure");
+    int rc = check_config(ctx, cfg);
+    if (rc != SDRB_OK) return rc;
+    const int channels = cfg->ssbChannels > 1 ? cfg->ssbChannels : 1;
+    if (channels != ctx->channels) return fail(ctx, SDRB_ERR_ARG, "sdrb_replan cannot change the channel count");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const int S = ctx->n_streams;
+    std::vector<FftStreamState> fs((size_t)S);
+    std::vector<SsbStreamState> ss((size_t)S * channels);
+    CK(cudaMemcpy(fs.data(), ctx->d_fft_state, fs.size() * sizeof(FftStreamState), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(ss.data(), ctx->d_ssb_state, ss.size() * sizeof(SsbStreamState), cudaMemcpyDeviceToHost));
+    const int rfMode = ctx->rfMode;
+    const unsigned long long ssb_samples = ctx->ssb_samples;
+    // the audio detectors do not depend on the geometry (they run at the nominal 48 kHz): detach them from the
+    // context so that sdrb_configure neither frees nor resets them
+    PulseState* au_state = ctx->d_au_state;
+    float* au_e = ctx->d_au_e;
+    ctx->d_au_state = nullptr;
+    ctx->d_au_e = nullptr;
+    rc = sdrb_configure(ctx, cfg, S, max_blocks);
+    if (rc != SDRB_OK) {
+        if (au_state) cudaFree(au_state);
+        if (au_e) cudaFree(au_e);
+        return rc;
+    }
+    ctx->d_au_state = au_state;
+    ctx->d_au_e = au_e;
+    for (auto& f : fs)
+        if (f.centerFrequency != cfg->centerFrequency) { f.centerFrequency = cfg->centerFrequency; f.centerChanged = 1; }
+    CK(cudaMemcpy(ctx->d_fft_state, fs.data(), fs.size() * sizeof(FftStreamState), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->d_ssb_state, ss.data(), ss.size() * sizeof(SsbStreamState), cudaMemcpyHostToDevice));
+    ctx->rfMode = rfMode;
+    ctx->ssb_samples = ssb_samples;
+    return upload_ssb(ctx);
+}
+
 int sdrb_set_center_frequency(sdrb_ctx* ctx, int stream, uint32_t center_hz) {
     if (!ctx || !ctx->configured) return fail(ctx, SDRB_ERR_STATE, "not configured");
     if (stream < -1 || stream >= ctx->n_streams) return fail(ctx, SDRB_ERR_ARG, "stream %d out of range", stream);
@@ -569,7 +648,8 @@ static int validate_process(sdrb_ctx* ctx, const void* iq, int n_blocks, unsigne
     if ((stages & SDRB_STAGE_FFT) && (rc = ensure_fft_buffers(ctx)) != SDRB_OK) return rc;
     if (stages & SDRB_STAGE_SSB) {
         if (ctx->rfMode < 0) {  // first SSB block latches the RF low-pass design
-            ctx->rfMode = ctx->cfg.soundMode;
+            if (ctx->cfg.soundMode >= 0 && ctx->cfg.soundMode <= 2) ctx->effMode = ctx->cfg.soundMode;
+            ctx->rfMode = ctx->effMode;
             if ((rc = upload_ssb(ctx)) != SDRB_OK) return rc;
         }
         if ((rc = ensure_ssb_buffers(ctx)) != SDRB_OK) return rc;
@@ -599,6 +679,11 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
     const int frames = ns * n_blocks;
     const size_t f0s = (size_t)s0 * n_blocks;   // first frame of the range
     int launches = 0;
+    struct TraceArm {
+        TraceArm(TraceSink* t) { g_trace = t; }
+        ~TraceArm() { g_trace = nullptr; }
+    } arm(ctx->trace);
+    trace_mark("call start", st);
     if (fmt == SDRB_RU16) {
         // Airspy: raw real ADC words -> cf32 through the libairspy converter chain (state carried per stream),
         // then the CF32 kernels.  The intermediate is laid out for THIS call's n_blocks.
@@ -618,7 +703,7 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
         if (!ctx->ssb_ext) {
             CK(launch_ssb(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_tapsE, ctx->ssb_sp, static_cast<float2*>(ctx->d_start) + f0s,
                           ctx->d_ssb_state + s0, ctx->d_a48 + f0s * m, ctx->d_pcm + f0s * m,
-                          ctx->d_agc ? ctx->d_agc + f0s * (size_t)n : nullptr, ns, n_blocks, ss, &launches));
+                          ctx->d_agc ? ctx->d_agc + f0s * (size_t)n : nullptr, ns, n_blocks, ctx->sm_count, ss, &launches));
         } else {
             const size_t C = (size_t)ctx->channels;
             CK(launch_ssb_ext(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_inc1, ctx->inc2, ctx->cfg.ssbTrueSideband != 0,
@@ -638,9 +723,11 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
         }
         CK(cudaEventRecord(ctx->ev_fork, st));
         CK(cudaStreamWaitEvent(ctx->s_ssb, ctx->ev_fork, 0));
-        int rc = run_ssb(ctx->s_ssb);     // launched first: the state pass takes its SM slots before the FFT CTAs arrive
-        if (rc != SDRB_OK) return rc;
-        CK(cudaEventRecord(ctx->ev_join, ctx->s_ssb));
+        if (ctx->ssb_first) {
+            int rc = run_ssb(ctx->s_ssb);
+            if (rc != SDRB_OK) return rc;
+            CK(cudaEventRecord(ctx->ev_join, ctx->s_ssb));
+        }
     }
     if (stages & SDRB_STAGE_FFT) {
         float* power = ctx->d_power + f0s * n;
@@ -670,6 +757,7 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
                 CK(launch_fft16k2(fmt, src, power + (size_t)f0 * n, ctx->d_tables16k, nf, ctx->sm_count, st, ctx->front,
                                   ctx->d_win, fork ? ctx->d_ticket : nullptr));
                 if (time_fft && f0 == 0) { CK(cudaEventRecord(ctx->ev1, st)); ctx->ev_valid = true; ctx->last_fft_frames = nf; }
+                trace_mark("fft16k", st);
                 fft_launches++;
                 if (chunk < frames) {
                     cudaStream_t es = st;
@@ -734,16 +822,29 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
                                 ctx->n_streams * ctx->max_blocks, frames, st));
             launches += ctx->geo.focusLen > 0 ? 2 : 1;
         }
+        if (!estimator_done) trace_mark("band scan + estimator", st);
         if (!tracker_done) {
             CK(launch_tracker(ctx->d_local + f0s, ctx->d_geo, ctx->d_fft_state + s0, ctx->d_results + f0s, ns, n_blocks, st));
             launches += 1;
+            trace_mark("tracker", st);
         }
     }
     if ((stages & SDRB_STAGE_SSB) && !fork) {
         int rc = run_ssb(st);
         if (rc != SDRB_OK) return rc;
     }
-    if (fork) CK(cudaStreamWaitEvent(st, ctx->ev_join, 0));
+    if (fork) {
+        // The FFT chain is launched first: its persistent CTAs (one per SM, 181 KiB of shared memory) are resident
+        // before the state pass's one-warp CTAs arrive, which then fit beside them two to an SM; the other way round
+        // an SM that collected three of those has no room for its FFT CTA until they end.
+        if (!ctx->ssb_first) {
+            int rc = run_ssb(ctx->s_ssb);
+            if (rc != SDRB_OK) return rc;
+            CK(cudaEventRecord(ctx->ev_join, ctx->s_ssb));
+        }
+        CK(cudaStreamWaitEvent(st, ctx->ev_join, 0));
+        trace_mark("join", st);
+    }
     if (stages & (SDRB_STAGE_SPECTRAL_PULSE | SDRB_STAGE_AUDIO_PULSE)) {
         const size_t C = (size_t)ctx->channels;
         sdrb_pulse_result* out = ctx->d_pulse + f0s * C;
@@ -849,6 +950,7 @@ int sdrb_sync(sdrb_ctx* ctx) {
     if (!ctx) return SDRB_ERR_ARG;
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->trace) ctx->trace->dump();
     return SDRB_OK;
 }
 

@@ -243,6 +243,9 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(FULL, part, d);
     const float perBinMean = __fdiv_rn(part, (float)pooledN);
+    // the staging loop above indexes lanes relative to each window's start, the loop below absolutely: a lane reads
+    // what another lane wrote, so the writes have to be ordered before the reads (shared or global scratch alike)
+    __syncwarp();
     for (int i = lane; i < pooledN; i += 32) stage[i] = fabsf(__fsub_rn(stage[i], perBinMean));   // :265-266
     __syncwarp();
     // ---- :267-268 median of the gaps: 4-pass radix select on the bit pattern; each lane owns 8 of

@@ -104,6 +104,16 @@ struct AirspyStreamState {
     float pad[14];
 };
 
+// ---------------------------------------------------------------- timeline (SDRB_TRACE=1)
+// Completion time of every launch group on its stream, relative to the start of the call: the launchers drop a
+// CUDA event after each kernel when a trace is armed (api.cu prints it at the next sdrb_sync).  Diagnostic only.
+struct TraceSink {
+    virtual void mark(const char* name, cudaStream_t st) = 0;
+    virtual ~TraceSink() {}
+};
+extern thread_local TraceSink* g_trace;
+inline void trace_mark(const char* name, cudaStream_t st) { if (g_trace) g_trace->mark(name, st); }
+
 // ---------------------------------------------------------------- launchers
 // airspy.cu : raw 12-bit real samples (uint16, 2 per complex output) -> cf32 [streams][n_real/2]
 cudaError_t launch_airspy_front(const uint16_t* d_raw, AirspyStreamState* d_state, float* d_T, cpx* d_iq, float* d_work,
@@ -146,7 +156,7 @@ std::vector<float> ssb_fused_tap_table(const float* h, const SsbParams& P, int s
 cudaError_t ssb_prepare();
 cudaError_t launch_ssb(int fmt, const void* iq, const SsbParams& P, const float* d_taps, const float* d_tapsE, int sp,
                        float2* d_start, SsbStreamState* d_state, float* d_a48, int16_t* d_pcm, float* d_agc,
-                       int n_streams, int n_blocks, cudaStream_t st, int* launches);
+                       int n_streams, int n_blocks, int sm_count, cudaStream_t st, int* launches);
 cudaError_t launch_ssb_audio(const float* d_a48, const SsbParams& P, SsbStreamState* d_state, int16_t* d_pcm,
                              int n_streams, int n_blocks, cudaStream_t st);
 // ssb_ext.cu : NCO channel bank + Weaver sideband selection (extension stages)

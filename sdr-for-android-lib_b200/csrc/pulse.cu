@@ -5,6 +5,12 @@
 // deques are fixed-capacity rings in global memory.  Every float expression keeps the reference's
 // evaluation order; this file is compiled with -fmad=false so no multiply-add is contracted, which makes
 // the detectors bit-identical to the reference built with g++ -O2 on x86-64 (no FMA at baseline).
+//
+// What is whose: the batching (one struct serving both detectors, deques as rings with an overflow counter,
+// biquad state in registers, host-side filter design) is this repository's; `Det::detect_rois` and `Det::est_freq`
+// are statement-for-statement transliterations of the reference's detectRois (spectral_pulse_detector.cpp:47-146,
+// same body in audio_pulse_detector.cpp:145-268) and estimatedFreqHz (:148-196) -- a sequential state machine whose
+// every branch and float expression has to come out bit-identical leaves no freedom in its control flow.
 #include "pulse.h"
 
 #include <cmath>

@@ -81,15 +81,24 @@ void FFTProcessor::ensureContext(int n) {
     spectrum_.assign(static_cast<size_t>(n), 0.0f);
 }
 
+// The reference's process() is void and never throws (bad geometry is a silent early return that leaves the previous
+// outputs in place, src/dsp/fft_process.cpp:139); it runs on the bridge's processing thread, where an exception would
+// end the process.  Failures (no device, out of memory, a CUDA error) are therefore recorded -- lastError(),
+// failedCalls() -- and the previous outputs stay.
 void FFTProcessor::process(const std::complex<float>* input_buf, uint32_t input_len) {
-    if (!have_cfg_) throw std::runtime_error("FFTProcessor::process before configure");
     if (!input_buf || input_len == 0) return;
-    ensureContext(static_cast<int>(input_len));
-    if (sdr_bridge_internal::isCenterFrequencyChanged.exchange(false))
-        SDRB_TRY(ctx_, sdrb_set_center_frequency(ctx_, -1, cfg_.centerFrequency));
-    SDRB_TRY(ctx_, sdrb_process_host(ctx_, input_buf, 1, SDRB_STAGE_FFT | SDRB_STAGE_SPECTRAL_PULSE, &last_,
-                                     spectrum_.data(), nullptr));
-    SDRB_TRY(ctx_, sdrb_get_pulse_results(ctx_, &pulse_, 1));
+    try {
+        if (!have_cfg_) throw std::runtime_error("FFTProcessor::process before configure");
+        ensureContext(static_cast<int>(input_len));
+        if (sdr_bridge_internal::isCenterFrequencyChanged.exchange(false))
+            SDRB_TRY(ctx_, sdrb_set_center_frequency(ctx_, -1, cfg_.centerFrequency));
+        SDRB_TRY(ctx_, sdrb_process_host(ctx_, input_buf, 1, SDRB_STAGE_FFT | SDRB_STAGE_SPECTRAL_PULSE, &last_,
+                                         spectrum_.data(), nullptr));
+        SDRB_TRY(ctx_, sdrb_get_pulse_results(ctx_, &pulse_, 1));
+    } catch (const std::exception& e) {
+        last_error_ = e.what();
+        failed_calls_++;
+    }
 }
 
 // ------------------------------------------------------------------ processSSB_opt
@@ -146,18 +155,22 @@ void ssb_run(std::vector<std::complex<float>>& iq, uint32_t sampleRate, bool upp
     SsbSingleton& S = ssb_one();
     std::lock_guard<std::mutex> lock(S.mu);         // the reference is non-re-entrant (statics)
     pcmOut.clear();
-    if (iq.empty()) return;
+    if (iq.empty() && S.n == 0) return;
     if (!S.ctx) SDRB_TRY(nullptr, sdrb_create(S.device, &S.ctx));
+    // `static size_t sampCount = iq.size(); iq.resize(sampCount);` (src/ssb/ssb_demod_opt.cpp:225-227): the block
+    // length of the FIRST call is frozen; later blocks are cut or zero-extended to it.  sdrbSsbReset() starts over.
+    if (S.n != 0 && static_cast<int>(iq.size()) != S.n) iq.resize(static_cast<size_t>(S.n));
     const int n = static_cast<int>(iq.size());
-    if (n != S.n || sampleRate != S.fs || upperSideband != S.upper) {
-        // first block, or a new block geometry: re-plan, carrying the three filter states over
-        // (they are function statics in the reference and survive everything)
-        std::vector<unsigned char> blob(S.n ? sdrb_state_bytes(S.ctx) : 0);
-        if (!blob.empty()) SDRB_TRY(S.ctx, sdrb_save_state(S.ctx, blob.data(), blob.size()));
+    if (S.n == 0) {
         const sdrb_config c = make_config(0, sampleRate, n, 5, mode, upperSideband);
         SDRB_TRY(S.ctx, sdrb_configure(S.ctx, &c, 1, 1));
-        if (!blob.empty()) SDRB_TRY(S.ctx, sdrb_load_state(S.ctx, blob.data(), blob.size()));
         S.n = n; S.fs = sampleRate; S.upper = upperSideband; S.mode = mode;
+    } else if (sampleRate != S.fs || upperSideband != S.upper) {
+        // a new sample rate (decimation factor) or sideband: re-plan with every carried state kept -- the three
+        // filters are function statics in the reference and the pulse detector a member of SSBProcessor
+        const sdrb_config c = make_config(0, sampleRate, n, 5, mode, upperSideband);
+        SDRB_TRY(S.ctx, sdrb_replan(S.ctx, &c, 1));
+        S.fs = sampleRate; S.upper = upperSideband; S.mode = mode;
     } else if (mode != S.mode) {
         SDRB_TRY(S.ctx, sdrb_set_sound_mode(S.ctx, mode));   // gains/AGC follow, RF low-pass keeps the first mode
         S.mode = mode;
@@ -191,13 +204,15 @@ void SSBProcessor::setSoundModeSource(std::function<int()> src) {
 void SSBProcessor::startProcessing(PcmDataCallback pcm_cb) {
     if (running_.exchange(true)) return;            // already running: ignored like :28-31
     on_pcm_ = std::move(pcm_cb);
+    on_pulse_ = nullptr;                            // pulseCallback_ = nullptr, :33
     worker_ = std::thread([this] { workerLoop(); });
 }
 
 void SSBProcessor::startProcessing(PcmDataCallback pcm_cb, std::function<void(float, int)> pulse_cb) {
-    if (running_) return;
+    if (running_.exchange(true)) return;
+    on_pcm_ = std::move(pcm_cb);
     on_pulse_ = std::move(pulse_cb);                // :36-49
-    startProcessing(std::move(pcm_cb));
+    worker_ = std::thread([this] { workerLoop(); });
 }
 
 void SSBProcessor::setPulseConfig(const AudioPulseDetector::Config& c) {
@@ -249,8 +264,17 @@ void SSBProcessor::workerLoop() {
         }
         std::vector<int16_t> pcm;
         sdrb_pulse_result pr{};
-        // processSSB_opt (:103) + pulseDetector_.process(pcm) (:109) in one GPU call
-        sdrbSsbProcessWithPulse(std::move(job.iq), job.sampleRate, true, pcm, mode, have_cfg ? &new_cfg : nullptr, &pr);
+        // processSSB_opt (:103) + pulseDetector_.process(pcm) (:109) in one GPU call.  The reference's worker cannot
+        // fail; here a failed call (no memory, a CUDA error) drops the block and is recorded instead of ending the
+        // process through an exception that nothing on this thread would catch.
+        try {
+            sdrbSsbProcessWithPulse(std::move(job.iq), job.sampleRate, true, pcm, mode, have_cfg ? &new_cfg : nullptr, &pr);
+        } catch (const std::exception& e) {
+            std::lock_guard<std::mutex> lock(mu_);
+            last_error_ = e.what();
+            failed_++;
+            continue;
+        }
         if (on_pcm_ && !pcm.empty()) on_pcm_(pcm);                                      // :105-107
         if (on_pulse_) on_pulse_(pr.audioLastSnr, pr.audioLiveEtat);                    // :110-113
     }

@@ -17,6 +17,7 @@
 #pragma once
 #include <complex>
 #include <cstdint>
+#include <string>
 #include <vector>
 
 #include "../../include/sdr_b200.h"
@@ -68,6 +69,10 @@ public:
     const sdrb_pulse_result& lastPulse() const { return pulse_; }
     // additive: CUDA device of the context created by the first process() (default 0)
     void setDevice(int device) { device_ = device; }
+    // process() never throws (the reference's is void and runs on the bridge's processing thread): a failed call
+    // keeps the previous outputs and is recorded here
+    const std::string& lastError() const { return last_error_; }
+    unsigned long failedCalls() const { return failed_calls_; }
 
 private:
     void ensureContext(int n);
@@ -78,5 +83,7 @@ private:
     sdrb_ctx* ctx_ = nullptr;
     sdrb_frame_result last_{};
     sdrb_pulse_result pulse_{};
+    std::string last_error_;
+    unsigned long failed_calls_ = 0;
     std::vector<float> spectrum_;
 };

@@ -16,6 +16,7 @@
 #include <deque>
 #include <functional>
 #include <mutex>
+#include <string>
 #include <thread>
 #include <vector>
 
@@ -45,6 +46,11 @@ public:
     // additive
     void setSoundModeSource(std::function<int()> src);       // default: mode 1 ("normal")
     uint64_t droppedBlocks() const { return dropped_.load(); }
+    uint64_t failedBlocks() const { return failed_.load(); }   // blocks whose GPU call failed (dropped, worker kept alive)
+    std::string lastError() {
+        std::lock_guard<std::mutex> lock(mu_);
+        return last_error_;
+    }
 
 private:
     void workerLoop();
@@ -59,4 +65,6 @@ private:
     std::thread worker_;
     std::atomic<bool> running_{false};
     std::atomic<uint64_t> dropped_{0};
+    std::atomic<uint64_t> failed_{0};
+    std::string last_error_;
 };
