@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define SDRB_ABI_VERSION 1
+#define SDRB_ABI_VERSION 2
 
 typedef enum {
     SDRB_OK = 0,

@@ -53,6 +53,7 @@ struct StateBlobHeader {
     uint32_t magic, version;
     int32_t n_streams, rfMode;
     uint64_t ssb_samples;     // NCO phase origin of the extended SSB chain
+    uint32_t rfFs, pad;
 };
 constexpr int kMaxChunks = 32;
 constexpr uint32_t kBlobMagic = 0x53445242u;  // "SDRB"
@@ -67,6 +68,7 @@ struct sdrb_ctx {
     sdrb_config cfg = {};
     int n_streams = 0, max_blocks = 0;
     int rfMode = -1;            // latched by the first SSB call (static rfFilter, ssb_demod_opt.cpp:261-263)
+    uint32_t rfFs = 0;          // sample rate latched with it (iir2InitLowpass runs once, with the first call's rate)
     int effMode = 1;            // last sound mode in 0..2: any other value leaves the reference's file statics as the
                                 // previous call set them (ssb_demod_opt.cpp:17-26,230-255); they start as mode 1
     int fftPath = 0;
@@ -316,8 +318,8 @@ extern "C" int sdrb_plan_config(const sdrb_config* cfg, sdrb_plan* out) {
     out->freqPerBin = g.freqPerBin; out->nyquist = g.nyquist;
     SsbParams P;
     float taps[256] = {};
-    design_ssb(cfg->sampleRate, cfg->samplesPerReading, cfg->soundMode, cfg->soundMode, cfg->upperSideband,
-               cfg->ssbTrueSideband != 0, P, taps);
+    design_ssb(cfg->sampleRate, cfg->samplesPerReading, cfg->soundMode, cfg->sampleRate, cfg->soundMode,
+               cfg->upperSideband, cfg->ssbTrueSideband != 0, P, taps);
     out->decim = P.decim; out->nTaps = P.nTaps; out->pcmPerBlock = P.m;
     out->fftPath = fft_path_for(cfg->samplesPerReading);
     const BiquadCoef* cs[3] = {&P.rf, &P.hp, &P.bp};
@@ -345,8 +347,8 @@ static int upload_ssb(sdrb_ctx* ctx) {
     if (ctx->cfg.soundMode >= 0 && ctx->cfg.soundMode <= 2) ctx->effMode = ctx->cfg.soundMode;
     const int rf = ctx->rfMode >= 0 ? ctx->rfMode : ctx->effMode;
     const bool tsb = ctx->cfg.ssbTrueSideband != 0;
-    design_ssb(ctx->cfg.sampleRate, ctx->cfg.samplesPerReading, rf, ctx->effMode, ctx->cfg.upperSideband, tsb,
-               ctx->ssb, ctx->taps255);
+    design_ssb(ctx->cfg.sampleRate, ctx->cfg.samplesPerReading, rf, ctx->rfFs, ctx->effMode, ctx->cfg.upperSideband,
+               tsb, ctx->ssb, ctx->taps255);
     // NCO increments of the channel bank (extension; oracle/sdr_oracle_ext.c): channel c is tuned to
     // offset + c * spacing; with true sideband the first mix goes to the sideband centre (+/- B/2)
     // and the second mix brings it back, B = the low-pass bandwidth latched with the first block.
@@ -437,6 +439,7 @@ static int reset_state(sdrb_ctx* ctx) {
     CK(cudaMemcpy(ctx->d_fft_state, fs.data(), fs.size() * sizeof(FftStreamState), cudaMemcpyHostToDevice));
     CK(cudaMemset(ctx->d_ssb_state, 0, (size_t)ctx->n_streams * ctx->channels * sizeof(SsbStreamState)));
     ctx->rfMode = -1;
+    ctx->rfFs = 0;
     ctx->ssb_samples = 0;
     ctx->last_blocks = 0;
     ctx->last_stages = 0;
@@ -504,6 +507,7 @@ int sdrb_replan(sdrb_ctx* ctx, const sdrb_config* cfg, int max_blocks) {
     CK(cudaMemcpy(fs.data(), ctx->d_fft_state, fs.size() * sizeof(FftStreamState), cudaMemcpyDeviceToHost));
     CK(cudaMemcpy(ss.data(), ctx->d_ssb_state, ss.size() * sizeof(SsbStreamState), cudaMemcpyDeviceToHost));
     const int rfMode = ctx->rfMode;
+    const uint32_t rfFs = ctx->rfFs;
     const unsigned long long ssb_samples = ctx->ssb_samples;
     // the audio detectors do not depend on the geometry (they run at the nominal 48 kHz): detach them from the
     // context so that sdrb_configure neither frees nor resets them
@@ -524,6 +528,7 @@ int sdrb_replan(sdrb_ctx* ctx, const sdrb_config* cfg, int max_blocks) {
     CK(cudaMemcpy(ctx->d_fft_state, fs.data(), fs.size() * sizeof(FftStreamState), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(ctx->d_ssb_state, ss.data(), ss.size() * sizeof(SsbStreamState), cudaMemcpyHostToDevice));
     ctx->rfMode = rfMode;
+    ctx->rfFs = rfFs;
     ctx->ssb_samples = ssb_samples;
     return upload_ssb(ctx);
 }
@@ -650,6 +655,7 @@ static int validate_process(sdrb_ctx* ctx, const void* iq, int n_blocks, unsigne
         if (ctx->rfMode < 0) {  // first SSB block latches the RF low-pass design
             if (ctx->cfg.soundMode >= 0 && ctx->cfg.soundMode <= 2) ctx->effMode = ctx->cfg.soundMode;
             ctx->rfMode = ctx->effMode;
+            ctx->rfFs = ctx->cfg.sampleRate;
             if ((rc = upload_ssb(ctx)) != SDRB_OK) return rc;
         }
         if ((rc = ensure_ssb_buffers(ctx)) != SDRB_OK) return rc;
@@ -1097,7 +1103,7 @@ int sdrb_save_state(sdrb_ctx* ctx, void* host_blob, size_t bytes) {
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(ctx->stream));
     unsigned char* p = static_cast<unsigned char*>(host_blob);
-    StateBlobHeader h = {kBlobMagic, SDRB_ABI_VERSION, ctx->n_streams, ctx->rfMode, ctx->ssb_samples};
+    StateBlobHeader h = {kBlobMagic, SDRB_ABI_VERSION, ctx->n_streams, ctx->rfMode, ctx->ssb_samples, ctx->rfFs, 0u};
     memcpy(p, &h, sizeof h);
     p += sizeof h;
     CK(cudaMemcpy(p, ctx->d_fft_state, (size_t)ctx->n_streams * sizeof(FftStreamState), cudaMemcpyDeviceToHost));
@@ -1123,6 +1129,7 @@ int sdrb_load_state(sdrb_ctx* ctx, const void* host_blob, size_t bytes) {
     CK(cudaMemcpy(ctx->d_ssb_state, p, (size_t)ctx->n_streams * ctx->channels * sizeof(SsbStreamState),
                   cudaMemcpyHostToDevice));
     ctx->rfMode = h.rfMode;
+    ctx->rfFs = h.rfFs;
     ctx->ssb_samples = h.ssb_samples;
     return upload_ssb(ctx);
 }

@@ -119,10 +119,11 @@ inline SsbModeParams ssb_mode(int mode) {
     return {0.35f, 0.006f, 0.5f, 3200.0f, 0.9f, 0.55f};
 }
 
-// rfMode = the mode of the FIRST block (the reference's static rfFilter is initialised once, :261-263).
+// rfMode / rfFs = the mode and the sample rate of the FIRST block (the reference's static rfFilter is initialised
+// once, with that call's sampleRate and parameters, :261-263).
 // trueSideband (extension): the low-pass is designed at B/2 for the Weaver sideband filter.
-inline void design_ssb(uint32_t fs, int n, int rfMode, int mode, int upper, bool trueSideband, SsbParams& P,
-                       float* taps255) {
+inline void design_ssb(uint32_t fs, int n, int rfMode, uint32_t rfFs, int mode, int upper, bool trueSideband,
+                       SsbParams& P, float* taps255) {
     const SsbModeParams mp = ssb_mode(mode), rp = ssb_mode(rfMode);
     P.n = n;
     P.decim = std::max(1, static_cast<int>(fs / 48000.0f));
@@ -136,7 +137,7 @@ inline void design_ssb(uint32_t fs, int n, int rfMode, int mode, int upper, bool
     P.agcSlow = 0.00035f;
     P.gain = mp.gain;
     P.transientCoeff = mp.transientCoeff;
-    P.rf = design_rf_lowpass(static_cast<float>(fs), trueSideband ? rp.lowpassBd * 0.5f : rp.lowpassBd, rp.lowpassQ);
+    P.rf = design_rf_lowpass(static_cast<float>(rfFs ? rfFs : fs), trueSideband ? rp.lowpassBd * 0.5f : rp.lowpassBd, rp.lowpassQ);
     P.hp = design_highpass(48000.0f, 1200.0f, 0.7f);
     P.bp = design_bandpass(48000.0f, 2400.0f, 0.6f);
 }

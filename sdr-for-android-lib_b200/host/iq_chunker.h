@@ -11,9 +11,18 @@
 //   IqChunker<T>      one stream: push(ptr, count) / pop(block, timeout)
 //   IqFileSource<T>   replay of a raw IQ capture file in MTU-sized reads (stands in for readStream; the box
 //                     has no dongle), optional looping
+//   IqTcpSource       rtl_tcp client (third_party/rtl-sdr/src/rtl_tcp.c: 12-byte "RTL0" greeting, then raw u8
+//                     I,Q pairs; 5-byte big-endian commands back): a live network source in place of readStream
 //   StreamBatcher<T>  S chunkers -> one [S][B][N] batch for sdrb_process_host once every stream holds B blocks
 #pragma once
+#include <arpa/inet.h>
+#include <netinet/in.h>
+#include <netinet/tcp.h>
+#include <sys/socket.h>
+#include <unistd.h>
+
 #include <algorithm>
+#include <cstring>
 #include <chrono>
 #include <condition_variable>
 #include <cstdint>
@@ -118,6 +127,84 @@ private:
     std::FILE* f_ = nullptr;
     size_t mtu_;
     bool loop_;
+};
+
+// rtl_tcp client.  Wire format of the server in the reference tree (third_party/rtl-sdr/src/rtl_tcp.c): on connect
+// it sends dongle_info_t = { char magic[4] = "RTL0"; uint32 tuner_type; uint32 tuner_gain_count; } in network byte
+// order (:79-83, :618-629), then the dongle's raw samples, unsigned 8-bit I,Q pairs, as they arrive; the client
+// may send struct command { uint8 cmd; uint32 param; } packed, param big-endian (:281-284): 0x01 centre frequency,
+// 0x02 sample rate, 0x03 gain mode, 0x04 gain (:316-331).  read() has the shape of IqFileSource::read, so the same
+// loop feeds an IqChunker<uint16_t> (one uint16_t = one u8 I,Q pair, the SDRB_CU8 sample).
+class IqTcpSource {
+public:
+    IqTcpSource(const std::string& host_ipv4, uint16_t port, size_t mtu) : mtu_(mtu) {
+        fd_ = ::socket(AF_INET, SOCK_STREAM, 0);
+        if (fd_ < 0) return;
+        sockaddr_in a{};
+        a.sin_family = AF_INET;
+        a.sin_port = htons(port);
+        if (::inet_pton(AF_INET, host_ipv4.c_str(), &a.sin_addr) != 1 ||
+            ::connect(fd_, reinterpret_cast<sockaddr*>(&a), sizeof a) != 0) { close(); return; }
+        int one = 1;
+        ::setsockopt(fd_, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);
+        unsigned char hello[12];
+        if (!readAll(hello, sizeof hello) || std::memcmp(hello, "RTL0", 4) != 0) { close(); return; }
+        uint32_t be;
+        std::memcpy(&be, hello + 4, 4); tuner_type_ = ntohl(be);
+        std::memcpy(&be, hello + 8, 4); gain_count_ = ntohl(be);
+    }
+    ~IqTcpSource() { close(); }
+    IqTcpSource(const IqTcpSource&) = delete;
+    IqTcpSource& operator=(const IqTcpSource&) = delete;
+    bool ok() const { return fd_ >= 0; }
+    uint32_t tunerType() const { return tuner_type_; }
+    uint32_t tunerGainCount() const { return gain_count_; }
+
+    bool setCenterFrequency(uint32_t hz) { return command(0x01, hz); }
+    bool setSampleRate(uint32_t hz) { return command(0x02, hz); }
+    bool setGainMode(uint32_t manual) { return command(0x03, manual); }
+    bool setGain(uint32_t tenth_db) { return command(0x04, tenth_db); }
+
+    // At most min(mtu, samples_per_reading) whole I,Q pairs per call, whatever the segment boundaries were (an odd
+    // byte is kept for the next call).  0 = the server closed the connection.
+    size_t read(uint16_t* out, size_t samples_per_reading) {
+        if (fd_ < 0) return 0;
+        const size_t want = std::min(mtu_, samples_per_reading) * 2;   // bytes
+        unsigned char* dst = reinterpret_cast<unsigned char*>(out);
+        size_t have = 0;
+        if (has_odd_) { dst[0] = odd_; have = 1; has_odd_ = false; }
+        while (have < 2) {                                // block until one whole pair is there
+            const ssize_t r = ::recv(fd_, dst + have, want - have, 0);
+            if (r <= 0) return 0;
+            have += static_cast<size_t>(r);
+        }
+        if (have & 1) { odd_ = dst[have - 1]; has_odd_ = true; have--; }
+        return have / 2;
+    }
+
+private:
+    bool readAll(unsigned char* p, size_t n) {
+        while (n) {
+            const ssize_t r = ::recv(fd_, p, n, 0);
+            if (r <= 0) return false;
+            p += r; n -= static_cast<size_t>(r);
+        }
+        return true;
+    }
+    bool command(unsigned char cmd, uint32_t param) {
+        if (fd_ < 0) return false;
+        unsigned char b[5];
+        const uint32_t be = htonl(param);
+        b[0] = cmd;
+        std::memcpy(b + 1, &be, 4);
+        return ::send(fd_, b, sizeof b, MSG_NOSIGNAL) == (ssize_t)sizeof b;
+    }
+    void close() { if (fd_ >= 0) { ::close(fd_); fd_ = -1; } }
+    int fd_ = -1;
+    size_t mtu_;
+    uint32_t tuner_type_ = 0, gain_count_ = 0;
+    unsigned char odd_ = 0;
+    bool has_odd_ = false;
 };
 
 // S independent streams feeding one batched GPU call: tryAssemble() fills `batch` with [S][B][N] samples and

@@ -85,6 +85,54 @@ int main(int argc, char** argv) {
         CHECK(!bat.tryAssemble(batch));
         remove(path);
     }
+    {   // rtl_tcp client against a loopback server speaking the wire format of third_party/rtl-sdr/src/rtl_tcp.c
+        const int ls = socket(AF_INET, SOCK_STREAM, 0);
+        CHECK(ls >= 0);
+        sockaddr_in a{};
+        a.sin_family = AF_INET;
+        a.sin_addr.s_addr = htonl(INADDR_LOOPBACK);
+        a.sin_port = 0;
+        CHECK(bind(ls, (sockaddr*)&a, sizeof a) == 0 && listen(ls, 1) == 0);
+        socklen_t al = sizeof a;
+        CHECK(getsockname(ls, (sockaddr*)&a, &al) == 0);
+        const uint16_t port = ntohs(a.sin_port);
+        const size_t n = 512, blocks = 5;
+        std::vector<unsigned char> wire(2 * n * blocks + 2 * 77);
+        for (size_t i = 0; i < wire.size(); i++) wire[i] = (unsigned char)(i * 13 + 5);
+        unsigned char cmd[10] = {0};
+        std::thread server([&] {
+            const int c = accept(ls, nullptr, nullptr);
+            unsigned char hello[12] = {'R', 'T', 'L', '0', 0, 0, 0, 5, 0, 0, 0, 29};   // R820T, 29 gains
+            send(c, hello, sizeof hello, 0);
+            size_t got = 0;
+            while (got < sizeof cmd) { ssize_t r = recv(c, cmd + got, sizeof cmd - got, 0); if (r <= 0) break; got += (size_t)r; }
+            const size_t seg[] = {1, 3, 1001, 2, 4095, 7};   // odd segment sizes: pairs straddle segments
+            size_t pos = 0, k = 0;
+            while (pos < wire.size()) {
+                const size_t w = std::min(seg[k++ % 6], wire.size() - pos);
+                send(c, wire.data() + pos, w, 0);
+                pos += w;
+            }
+            close(c);
+        });
+        IqTcpSource src("127.0.0.1", port, 300);
+        CHECK(src.ok() && src.tunerType() == 5 && src.tunerGainCount() == 29);
+        CHECK(src.setCenterFrequency(430000000u) && src.setSampleRate(2000000u));
+        IqChunker<uint16_t> ch(n);
+        std::vector<uint16_t> rd(n);
+        size_t got, total = 0;
+        while ((got = src.read(rd.data(), n)) > 0) { CHECK(got <= 300); ch.push(rd.data(), got); total += got; }
+        server.join();
+        close(ls);
+        CHECK(total == wire.size() / 2 && ch.queued() == blocks && ch.pendingSamples() == 77);
+        CHECK(cmd[0] == 0x01 && cmd[1] == 0x19 && cmd[2] == 0xA1 && cmd[3] == 0x47 && cmd[4] == 0x80);   // 430 000 000 big-endian
+        CHECK(cmd[5] == 0x02 && cmd[6] == 0x00 && cmd[7] == 0x1E && cmd[8] == 0x84 && cmd[9] == 0x80);   // 2 000 000
+        std::vector<uint16_t> blk;
+        for (size_t b = 0; b < blocks; b++) {
+            CHECK(ch.pop(blk, 0));
+            CHECK(std::memcmp(blk.data(), wire.data() + 2 * n * b, 2 * n) == 0);   // I at the low byte, Q at the high byte
+        }
+    }
     printf("chunker OK\n");
     return 0;
 }

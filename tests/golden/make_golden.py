@@ -54,6 +54,8 @@ def gen_fft(case):
     sp = np.stack(spectra)
     out["power_every16"] = sp[:, ::16].copy()
     out["power_center"] = sp[:, n // 2 - 128:n // 2 + 128].copy()
+    if name == "fft_u8_16k":
+        out["power_full"] = sp.copy()   # two whole FFTW spectra: the GPU-vs-FFTW error per bin class is measured on them
     out["meta"] = np.array([fmt, fs, n, focus, stream, blocks], dtype=np.int64)
     np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
 

@@ -20,7 +20,7 @@ def test_every_declared_symbol_is_exported(sdrb):
     for name in sorted(declared):
         assert hasattr(sdrb.lib, name), f"{name} declared in include/sdr_b200.h but not exported"
     assert declared == set(sdrb.binding.EXPORTS), declared ^ set(sdrb.binding.EXPORTS)
-    assert sdrb.lib.sdrb_abi_version() == 1
+    assert sdrb.lib.sdrb_abi_version() == 2
     assert [sdrb.format_bytes(f) for f in (0, 1, 2, 3, 4)] == [2, 4, 8, 4, 0]
 
 

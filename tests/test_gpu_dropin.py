@@ -53,3 +53,30 @@ def test_dropin_front_end(sdrb, tmp_path, n, fs, B, focus, mode):
         assert np.abs(pcm.astype(np.int32) - exp.astype(np.int32)).max(initial=0) <= 1, b
     same = np.frombuffer(blob, dtype=np.int32, count=1, offset=off)[0]
     assert same == 1, "SSBProcessor (queue + worker) PCM differs from direct processSSB_opt calls"
+
+
+def test_ragged_reads_through_the_batcher_equal_a_direct_call(sdrb, gpu_ctx, tmp_path):
+    """host/iq_chunker.h in front of sdrb_process_host on the GPU: per-stream ragged reads ->
+    exact blocks -> [S][B][N] batches -> one pipelined host-to-host call per batch, two batches so that the carried
+    state crosses a batch boundary.  Records, spectra and PCM must equal a direct sdrb_process on the same samples."""
+    exe = os.path.join(ROOT, "sdr-for-android-lib_b200", "batcher_check.bin")
+    assert os.path.exists(exe), "batcher_check.bin missing: run __graft_entry__.build()"
+    S, B, n, batches, fs = 5, 3, 16384, 2, 2_000_000
+    out = tmp_path / "batcher.bin"
+    subprocess.run([exe, str(out), str(S), str(B), str(n), str(batches), str(fs)], check=True, timeout=300)
+    blob = out.read_bytes()
+    hdr = np.frombuffer(blob, dtype=np.int32, count=4)
+    m = int(hdr[3])
+    assert tuple(hdr[:3]) == (S, B, n) and m > 0
+    gpu_ctx.configure(sdrb.Config(FC, fs, n, 5, inputFormat=sdrb.CU8), S, B)
+    off = 16
+    for k in range(batches):
+        rec = np.frombuffer(blob, dtype=sdrb.RESULT_DTYPE, count=S * B, offset=off).reshape(S, B); off += rec.nbytes
+        power = np.frombuffer(blob, dtype=np.float32, count=S * B * n, offset=off).reshape(S, B, n); off += power.nbytes
+        pcm = np.frombuffer(blob, dtype=np.int16, count=S * B * m, offset=off).reshape(S, B, m); off += pcm.nbytes
+        iq = np.ascontiguousarray(sdrb.synth_host(sdrb.CU8, fs, 0, S, k * B * n, B * n).reshape(S, B, n, 2))
+        gpu_ctx.process(iq, B, sdrb.STAGE_FFT | sdrb.STAGE_SSB)
+        assert np.array_equal(gpu_ctx.results(), rec), k
+        assert np.array_equal(gpu_ctx.power_all(), power), k
+        assert np.array_equal(gpu_ctx.pcm(), pcm), k
+    assert off == len(blob)

@@ -326,3 +326,107 @@ def test_power_spectrum_parity_1m(sdrb, gpu_ctx, fmt):
             got = gpu_ctx.power(s, b)
             assert np.all(np.abs(got - ref) <= power_tolerance(ref)), (s, b, float(np.abs(got - ref).max()))
             check_results(res[s, b], orc.evaluate(got), 0, ("1M", s, b))
+
+
+def test_ssb_one_reading_per_call_is_one_kernel_and_exact(sdrb, gpu_ctx):
+    """One reading per stream per call: the whole of processSSB_opt is ONE kernel (no state pass, audio chain on the
+    lane); the carried filter states go from call to call.  PCM against the oracle, call after call, and against the
+    same readings handed over in one multi-reading call (state pass + fused pass + audio pass)."""
+    n, fs, S, B = 16384, 2_000_000, 37, 6
+    for fmt, mode in ((0, 1), (1, 0), (2, 2)):
+        cfg = sdrb.Config(FC, fs, n, 5, soundMode=mode, inputFormat=fmt)
+        iq = make_iq(sdrb, fmt, fs, 100, S, B, n)
+        gpu_ctx.configure(cfg, S, B)
+        gpu_ctx.process(iq, B, sdrb.STAGE_SSB)
+        pcm_multi = gpu_ctx.pcm().copy()
+        gpu_ctx.reset_state()
+        orc = [ol.OracleSsb() for _ in range(S)]
+        for b in range(B):
+            l0 = gpu_ctx.launch_count
+            gpu_ctx.process(np.ascontiguousarray(iq[:, b:b + 1]), 1, sdrb.STAGE_SSB)
+            assert gpu_ctx.launch_count - l0 == 1, "one reading per stream must be a single kernel"
+            pcm = gpu_ctx.pcm()
+            assert np.array_equal(pcm[:, 0], pcm_multi[:, b]), (fmt, b)
+            for s in (0, 17, 36):
+                exp = orc[s].process(ol.to_cf32(iq[s, b], fmt), fs, 1, mode)
+                assert np.abs(pcm[s, 0].astype(int) - exp.astype(int)).max() <= 1
+                assert (pcm[s, 0] == exp).mean() >= 0.999
+
+
+def test_ssb_fused_pass_equals_split_pass(sdrb, gpu_ctx, monkeypatch):
+    """The fused AGC + decimator pass (rotated tap table, accumulators on the lane) against the split pair
+    (post-AGC samples through a scratch, one thread per output): bit-identical PCM, several decimation factors."""
+    for fmt, n, fs in ((0, 16384, 2_000_000), (0, 16384, 2_500_000), (0, 16384, 3_200_000), (1, 65536, 30_720_000),
+                       (2, 16384, 1_600_000), (1, 16384, 1_024_000), (0, 16384, 1_536_000)):
+        S, B = 33, 3
+        cfg = sdrb.Config(FC, fs, n, 5, inputFormat=fmt)
+        iq = make_iq(sdrb, fmt, fs, 7, S, B, n)
+        out = []
+        for fused in ("1", "0"):
+            monkeypatch.setenv("SDRB_SSB_FUSED", fused)
+            gpu_ctx.configure(cfg, S, B)
+            gpu_ctx.process(iq, B, sdrb.STAGE_SSB)
+            out.append(gpu_ctx.pcm().copy())
+        assert out[0].size and np.array_equal(out[0], out[1]), (fmt, n, fs)
+    monkeypatch.delenv("SDRB_SSB_FUSED")
+
+
+def test_fft_and_ssb_side_by_side_equal_one_after_the_other(sdrb, gpu_ctx, monkeypatch):
+    """FFT chain and SSB chain on two CUDA streams (the default) against both on one stream: same records, same
+    spectra, same PCM."""
+    n, fs, S, B = 16384, 2_000_000, 300, 2
+    cfg = sdrb.Config(FC, fs, n, 5, inputFormat=0)
+    iq = make_iq(sdrb, 0, fs, 0, S, B, n)
+    out = []
+    for fork in ("1", "0"):
+        monkeypatch.setenv("SDRB_SSB_FORK", fork)
+        ctx = sdrb.Context(0)            # the switch is read when the context is created
+        ctx.configure(cfg, S, B)
+        ctx.process(iq, B, sdrb.STAGE_FFT | sdrb.STAGE_SSB)
+        out.append((ctx.results().copy(), ctx.pcm().copy(), ctx.power_all().copy()))
+        ctx.close()
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])
+    assert np.array_equal(out[0][2], out[1][2])
+
+
+def test_stream_shards_equal_the_whole(sdrb, gpu_ctx):
+    """SURVEY.md section 4 layer 4 (same results at 1 / 2 / 4 / 8 GPUs): the records, spectra and PCM of global stream
+    s are the same whether s is processed in one context holding every stream or in the shard context of its rank
+    (bench.py's sharding, two shard contexts standing in for two ranks on this one GPU)."""
+    n, fs, S, B, world = 16384, 2_000_000, 10, 3, 2
+    cfg = sdrb.Config(FC, fs, n, 5, inputFormat=0)
+    both = sdrb.STAGE_FFT | sdrb.STAGE_SSB
+    iq = make_iq(sdrb, 0, fs, 0, S, B, n)
+    gpu_ctx.configure(cfg, S, B)
+    gpu_ctx.process(iq, B, both)
+    res, pcm, pw = gpu_ctx.results().copy(), gpu_ctx.pcm().copy(), gpu_ctx.power_all().copy()
+    for rank in range(world):
+        first, count = sdrb.shard_streams(S, world, rank)
+        shard = sdrb.Context(0)
+        shard.configure(cfg, count, B)
+        mine = make_iq(sdrb, 0, fs, first, count, B, n)          # a rank generates / receives only its own streams
+        shard.process(mine, B, both)
+        assert np.array_equal(shard.results(), res[first:first + count]), rank
+        assert np.array_equal(shard.pcm(), pcm[first:first + count]), rank
+        assert np.array_equal(shard.power_all(), pw[first:first + count]), rank
+        shard.close()
+
+
+def test_replan_keeps_every_carried_state(sdrb, gpu_ctx):
+    """sdrb_replan: a new sample rate for the same streams; the SSB filter states (function statics in the
+    reference) and the FFT tracking state go on: the continuation equals the oracle's, which is never reset."""
+    n, S = 16384, 3
+    orc = [ol.OracleSsb() for _ in range(S)]
+    gpu_ctx.configure(sdrb.Config(FC, 2_000_000, n, 5, inputFormat=2), S, 2)
+    for step, fs in enumerate((2_000_000, 2_400_000, 2_000_000)):
+        cfg = sdrb.Config(FC, fs, n, 5, inputFormat=2)
+        if step:
+            gpu_ctx.replan(cfg, 2)
+        iq = make_iq(sdrb, 2, fs, 50, S, 2, n, first_block=2 * step)
+        gpu_ctx.process(iq, 2, sdrb.STAGE_SSB)
+        pcm = gpu_ctx.pcm()
+        for s in range(S):
+            for b in range(2):
+                exp = orc[s].process(ol.to_cf32(iq[s, b], 2), fs, 1, 1)
+                assert exp.size == pcm.shape[2]
+                assert np.abs(pcm[s, b].astype(int) - exp.astype(int)).max() <= 1, (step, s, b)
