@@ -505,36 +505,39 @@ def run_ours(args):
         h_rec_t = torch.empty((Se * B * sdrb.RESULT_DTYPE.itemsize,), dtype=torch.uint8).pin_memory() if has_fft else None
         h_pcm = torch.empty((max(1, Se * ch * B * m),), dtype=torch.int16).pin_memory() if m else None
 
-        def e2e_step(power=True):
-            # one C-ABI call: H2D of the IQ, all kernels, D2H of every payload, chunk-pipelined over CUDA streams
-            ectx.process_host(h_iq, B, stages, results=h_rec_t, power=h_pow if power else None, pcm=h_pcm)
+        h_pow16 = torch.empty((Se, B, n), dtype=torch.float16).pin_memory() if has_fft else None
 
-        e2e_step()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.e2e_steps):
-            e2e_step()
-        barrier()
-        t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_val = world * Se * B * n * args.e2e_steps / float(t.item()) / 1e6
-        # the same without hauling the spectra back (records + PCM only), for context
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.e2e_steps):
-            e2e_step(power=False)
-        barrier()
-        t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_small = world * Se * B * n * args.e2e_steps / float(t.item()) / 1e6
+        def e2e_step(power=True, half=False):
+            # one C-ABI call: H2D of the IQ, all kernels, D2H of every payload, chunk-pipelined over CUDA streams
+            if half:
+                ectx.process_host(h_iq, B, stages, results=h_rec_t, power=h_pow16, pcm=h_pcm, power_format=sdrb.POWER_DB_F16)
+            else:
+                ectx.process_host(h_iq, B, stages, results=h_rec_t, power=h_pow if power else None, pcm=h_pcm)
+
+        def e2e_time(**kw):
+            e2e_step(**kw)
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.e2e_steps):
+                e2e_step(**kw)
+            barrier()
+            t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return world * Se * B * n * args.e2e_steps / float(t.item()) / 1e6
+
+        e2e_val = e2e_time()
+        e2e_small = e2e_time(power=False)          # records + PCM only, for context
+        e2e_half = e2e_time(half=True) if has_fft else None   # opt-in payload: half-precision dB view of the spectra
         d2h = (Se * B * n * 4 + Se * B * sdrb.RESULT_DTYPE.itemsize if has_fft else 0) + Se * ch * B * m * 2
         e2e = {"value": e2e_val, "unit": "MS/s", "h2d_bytes_per_step": Se * B * n * bi, "d2h_bytes_per_step": d2h,
-               "streams_per_call": Se, "without_spectra_value": e2e_small,
+               "streams_per_call": Se, "without_spectra_value": e2e_small, "db_f16_view_value": e2e_half,
                "d2h_gbs_per_gpu": d2h * 1e-9 / (Se * B * n / (e2e_val / world * 1e6)),
-               "note": "one sdrb_process_host call per step: pinned host IQ in; records, spectra and PCM out; "
-                       "chunk-pipelined over 3 CUDA streams (H2D, kernels, D2H)"}
+               "host_ceiling": "profiles/r02_host_path.json: one GPU alone moves 48-50 GB/s each way with both directions "
+                               "busy; eight GPUs together 94 GB/s out (11.8 GB/s per GPU)",
+               "note": "one sdrb_process_host call per step: pinned host IQ in; records, float32 linear spectra and PCM out; "
+                       "chunk-pipelined over 3 CUDA streams (H2D, kernels, D2H).  db_f16_view_value: the same call with "
+                       "the opt-in half-precision dB view instead of the float32 spectra (sdrb_process_host_ex)"}
         if has_fft:
             h_rec = h_rec_t.numpy().view(sdrb.RESULT_DTYPE).reshape(Se, B)
             peak_rec = sdrb.strongest_peak(h_rec, first_stream, dist if world > 1 else None)

@@ -214,6 +214,22 @@ int  sdrb_power_device(sdrb_ctx* ctx, const float** dev_ptr);
 int  sdrb_get_power(sdrb_ctx* ctx, int stream, int block, float* host_out);
 /* All spectra of the last call, [n_streams][n_blocks][N] floats, into host memory (pinned or pageable). */
 int  sdrb_get_power_all(sdrb_ctx* ctx, float* host_out, size_t capacity_floats);
+/* dB view of the spectrum (extra output; the callback payload stays the linear spectrum above):
+ * 10*log10f(p/refPower + 1e-20f) with refPower = 1, the expression evaluateSignalStrength applies to the bins it
+ * looks at (src/dsp/fft_process.cpp:142,149; src/dsp/fft_process.h:74-75), for every bin.  Within 1e-3 dB of
+ * 10*log10f of the linear output. */
+enum sdrb_power_format {
+    SDRB_POWER_LINEAR_F32 = 0,   /* float32 linear power: the reference's ([F)V payload, the default everywhere */
+    SDRB_POWER_DB_F32 = 1,       /* float32 dB */
+    SDRB_POWER_DB_F16 = 2        /* IEEE half dB (0.0625 dB steps at 64..128 dB): half the device-to-host bytes */
+};
+int  sdrb_get_power_db(sdrb_ctx* ctx, int stream, int block, float* host_out);
+/* sdrb_process_host with the spectra delivered in `power_format` (power_out then holds float32 or half values,
+ * [n_streams][n_blocks][N]).  The host side of the call is bound by the device-to-host path (4 B per sample of
+ * linear spectra against 2 B of u8 IQ in: profiles/r02_host_path.json); the half-precision dB view is the opt-in
+ * payload that halves it for consumers that only draw the spectrum. */
+int  sdrb_process_host_ex(sdrb_ctx* ctx, const void* iq_host, int n_blocks, unsigned stages,
+                          sdrb_frame_result* results_out, void* power_out, int power_format, int16_t* pcm_out);
 /* int16 PCM = the ([S)V payload; layout [n_streams][n_blocks][pcm_per_block]
  * (x ssbChannels when the NCO bank is on: [stream][channel][block][m]). */
 int  sdrb_pcm_device(sdrb_ctx* ctx, const int16_t** dev_ptr);

@@ -36,6 +36,66 @@ static int is_pow2(int n) { return n > 0 && (n & (n - 1)) == 0; }
 
 /* Forward DFT in double precision, X[k] = sum x[n] exp(-2 pi i k n / N)
  * (fft_process.cpp:77-78: FFTW_FORWARD, unnormalised). */
+/* In-place radix-2 transform in double, sign -1 (m a power of two). */
+static void fft_pow2_double(double* re, double* im, int m) {
+    int bits = 0;
+    while ((1 << bits) < m) bits++;
+    for (int i = 0; i < m; i++) {
+        unsigned r = 0;
+        for (int b = 0; b < bits; b++) if (i & (1 << b)) r |= 1u << (bits - 1 - b);
+        if ((int)r > i) { double t = re[i]; re[i] = re[r]; re[r] = t; t = im[i]; im[i] = im[r]; im[r] = t; }
+    }
+    for (int len = 2; len <= m; len <<= 1) {
+        int half = len >> 1;
+        for (int j = 0; j < half; j++) {
+            double a = -2.0 * M_PI * (double)j / (double)len, wr = cos(a), wi = sin(a);
+            for (int base = 0; base < m; base += len) {
+                int u = base + j, v = u + half;
+                double tr = re[v] * wr - im[v] * wi, ti = re[v] * wi + im[v] * wr;
+                re[v] = re[u] - tr; im[v] = im[u] - ti;
+                re[u] += tr; im[u] += ti;
+            }
+        }
+    }
+}
+
+/* The DFT of any length in double (what fftwf_plan_dft_1d(sampCount, ...) computes, fft_process.cpp:77-79), for
+ * lengths too long for the O(n^2) sum: chirp-z identity n k = (n^2 + k^2 - (k - n)^2) / 2 over a power-of-two
+ * circular convolution.  Checker arithmetic only (double throughout). */
+static int dft_bluestein_double(const float* iq, int n, double* re, double* im) {
+    int m = 1;
+    while (m < 2 * n - 1) m <<= 1;
+    double* ar = (double*)calloc((size_t)m, sizeof(double));
+    double* ai = (double*)calloc((size_t)m, sizeof(double));
+    double* br = (double*)calloc((size_t)m, sizeof(double));
+    double* bi = (double*)calloc((size_t)m, sizeof(double));
+    double* cr = (double*)malloc(sizeof(double) * (size_t)n);
+    double* ci = (double*)malloc(sizeof(double) * (size_t)n);
+    if (!ar || !ai || !br || !bi || !cr || !ci) { free(ar); free(ai); free(br); free(bi); free(cr); free(ci); return -1; }
+    for (long long k = 0; k < n; k++) {
+        double a = -M_PI * (double)((k * k) % (2LL * n)) / (double)n;
+        cr[k] = cos(a); ci[k] = sin(a);
+        ar[k] = iq[2 * k] * cr[k] - iq[2 * k + 1] * ci[k];
+        ai[k] = iq[2 * k] * ci[k] + iq[2 * k + 1] * cr[k];
+        br[k] = cr[k]; bi[k] = -ci[k];
+        if (k) { br[m - k] = cr[k]; bi[m - k] = -ci[k]; }
+    }
+    fft_pow2_double(ar, ai, m);
+    fft_pow2_double(br, bi, m);
+    for (int i = 0; i < m; i++) {   /* conj(A * B): the next forward transform is then the inverse one */
+        double tr = ar[i] * br[i] - ai[i] * bi[i], ti = ar[i] * bi[i] + ai[i] * br[i];
+        ar[i] = tr; ai[i] = -ti;
+    }
+    fft_pow2_double(ar, ai, m);
+    for (int k = 0; k < n; k++) {
+        double vr = ar[k] / (double)m, vi = -ai[k] / (double)m;
+        re[k] = vr * cr[k] - vi * ci[k];
+        im[k] = vr * ci[k] + vi * cr[k];
+    }
+    free(ar); free(ai); free(br); free(bi); free(cr); free(ci);
+    return 0;
+}
+
 static int dft_double(const float* iq, int n, double* re, double* im) {
     if (is_pow2(n) && n >= 2) {
         int bits = 0;
@@ -72,7 +132,8 @@ static int dft_double(const float* iq, int n, double* re, double* im) {
         free(wi);
         return 0;
     }
-    if (n > 4096 || n < 1) return -2;
+    if (n < 1) return -2;
+    if (n > 4096) return dft_bluestein_double(iq, n, re, im);
     for (int k = 0; k < n; k++) {
         double sr = 0.0, si = 0.0;
         for (int j = 0; j < n; j++) {

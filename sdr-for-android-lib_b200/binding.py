@@ -8,6 +8,7 @@ import numpy as np
 CU8, CS16, CF32, RU16 = 0, 1, 2, 3
 STAGE_FFT, STAGE_SSB = 1, 2
 STAGE_SPECTRAL_PULSE, STAGE_AUDIO_PULSE = 4, 8
+POWER_LINEAR_F32, POWER_DB_F32, POWER_DB_F16 = 0, 1, 2
 _HERE = os.path.dirname(os.path.abspath(__file__))
 lib_path = os.environ.get("SDRB_LIB") or os.path.join(_HERE, "libsdr_b200.so")   # SDRB_LIB: A/B builds of the same ABI
 
@@ -94,6 +95,9 @@ EXPORTS = {
     "sdrb_process": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint]),
     "sdrb_sync": (C.c_int, [C.c_void_p]),
     "sdrb_process_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "sdrb_process_host_ex": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_void_p, C.c_void_p, C.c_int,
+                                       C.c_void_p]),
+    "sdrb_get_power_db": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "sdrb_get_results": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "sdrb_results_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "sdrb_audio_pulse_config_default": (None, [C.POINTER(AudioPulseConfig)]),
@@ -228,11 +232,20 @@ class Context:
         _check(lib.sdrb_process(self._h, C.c_void_p(addr), 1 if on_device else 0, n_blocks, stages), self._h)
         self.last_blocks = n_blocks
 
-    def process_host(self, iq, n_blocks, stages=STAGE_FFT | STAGE_SSB, results=None, power=None, pcm=None):
-        """Pipelined host-to-host call; outputs are preallocated numpy arrays / pinned tensors or None."""
+    def process_host(self, iq, n_blocks, stages=STAGE_FFT | STAGE_SSB, results=None, power=None, pcm=None,
+                     power_format=POWER_LINEAR_F32):
+        """Pipelined host-to-host call; outputs are preallocated numpy arrays / pinned tensors or None.
+        power_format: POWER_LINEAR_F32 (the reference's payload), POWER_DB_F32 or POWER_DB_F16 (dB view)."""
         ptr = lambda x: C.c_void_p(_ptr(x)[0]) if x is not None else C.c_void_p(0)
-        _check(lib.sdrb_process_host(self._h, ptr(iq), n_blocks, stages, ptr(results), ptr(power), ptr(pcm)), self._h)
+        _check(lib.sdrb_process_host_ex(self._h, ptr(iq), n_blocks, stages, ptr(results), ptr(power), power_format,
+                                        ptr(pcm)), self._h)
         self.last_blocks = n_blocks
+
+    def power_db(self, stream, block):
+        """dB view of one spectrum: 10*log10f(p + 1e-20f) (src/dsp/fft_process.cpp:149)."""
+        out = np.empty(self.cfg.samplesPerReading, dtype=np.float32)
+        _check(lib.sdrb_get_power_db(self._h, stream, block, out.ctypes.data_as(C.c_void_p)), self._h)
+        return out
 
     def sync(self):
         _check(lib.sdrb_sync(self._h), self._h)

@@ -86,6 +86,7 @@ struct sdrb_ctx {
     EstGeometry* d_geo = nullptr;
     void* d_in = nullptr;
     float* d_power = nullptr;
+    void* d_view = nullptr;     // dB view of the spectra (float or half), allocated with the first request for one
     FrameLocal* d_local = nullptr;
     sdrb_frame_result* d_results = nullptr;
     FftStreamState* d_fft_state = nullptr;
@@ -94,11 +95,15 @@ struct sdrb_ctx {
     float* d_a48 = nullptr;
     int16_t* d_pcm = nullptr;
     float* d_taps = nullptr;
+    float* d_taps_lin = nullptr;   // the 255 taps in linear order (any-length pass)
+    bool ssb_any = false;          // block bytes not a multiple of 64: the scalar any-length pass
     float* d_tapsE = nullptr;   // rotated tap table of the fused AGC + decimator pass (ssb.cu:k_ssb_main)
     int ssb_sp = 0;             // its accumulator count; 0 = the decimation factor is outside its range (split pair)
     cpx* d_tables16k = nullptr;   // 16K kernel tables (TP | T2)
     int* d_ticket = nullptr;      // transform counter of the 16K kernel when it shares the SMs with the SSB chain
     cpx* d_tw = nullptr;
+    cpx *d_chirp = nullptr, *d_bf = nullptr;   // Bluestein: chirp c[k], transform of the wrapped conjugate chirp
+    int blue_m = 0;
     cpx *d_sa = nullptr, *d_sb = nullptr;
     cpx* d_fb_tables = nullptr;   // four-step twiddle tables
     cpx* d_fbA = nullptr;         // four-step intermediate A' (fb_group frames)
@@ -174,9 +179,9 @@ static int fail(sdrb_ctx* c, int code, const char* fmt, ...) {
     } while (0)
 
 static void free_buffers(sdrb_ctx* c) {
-    void** ptrs[] = {(void**)&c->d_geo, &c->d_in, (void**)&c->d_power, (void**)&c->d_local, (void**)&c->d_results,
+    void** ptrs[] = {(void**)&c->d_geo, &c->d_in, (void**)&c->d_power, &c->d_view, (void**)&c->d_local, (void**)&c->d_results,
                      (void**)&c->d_fft_state, (void**)&c->d_ssb_state, &c->d_start,
-                     (void**)&c->d_a48, (void**)&c->d_pcm, (void**)&c->d_taps, (void**)&c->d_tapsE, (void**)&c->d_tw, (void**)&c->d_sa,
+                     (void**)&c->d_a48, (void**)&c->d_pcm, (void**)&c->d_taps, (void**)&c->d_taps_lin, (void**)&c->d_tapsE, (void**)&c->d_tw, (void**)&c->d_chirp, (void**)&c->d_bf, (void**)&c->d_sa,
                      (void**)&c->d_sb, (void**)&c->d_est_scratch, (void**)&c->d_inc1, (void**)&c->d_win,
                      (void**)&c->d_front, (void**)&c->d_fb_tables, (void**)&c->d_fbA,
                      (void**)&c->d_sp_state, (void**)&c->d_au_state, (void**)&c->d_sp_e, (void**)&c->d_sp_f,
@@ -303,7 +308,9 @@ static int check_config(sdrb_ctx* ctx, const sdrb_config* cfg) {
     return SDRB_OK;
 }
 
-static int fft_path_for(int n) { return n == F2_N ? 1 : (fft_big_supports(n) ? 2 : 0); }
+// 1: one-CTA 16K kernel, 2: multi-CTA four-step (64K, 1M), 0: multi-pass power of two, 3: any other length (Bluestein)
+static int fft_path_for(int n) { return n == F2_N ? 1 : (fft_big_supports(n) ? 2 : (is_pow2(n) && n >= 2 ? 0 : 3)); }
+constexpr int kMaxBluesteinN = 1 << 22;   // convolution length 2^23: 64 MiB per transform and scratch buffer
 
 extern "C" int sdrb_plan_config(const sdrb_config* cfg, sdrb_plan* out) {
     if (!out) return fail(nullptr, SDRB_ERR_ARG, "plan out is NULL");
@@ -367,11 +374,15 @@ static int upload_ssb(sdrb_ctx* ctx) {
     if (ctx->d_taps) { cudaFree(ctx->d_taps); ctx->d_taps = nullptr; }
     CK(cudaMalloc(&ctx->d_taps, t.size() * sizeof(float)));
     CK(cudaMemcpy(ctx->d_taps, t.data(), t.size() * sizeof(float), cudaMemcpyHostToDevice));
+    if (ctx->d_taps_lin) { cudaFree(ctx->d_taps_lin); ctx->d_taps_lin = nullptr; }
+    CK(cudaMalloc(&ctx->d_taps_lin, 256 * sizeof(float)));
+    CK(cudaMemcpy(ctx->d_taps_lin, ctx->taps255, 256 * sizeof(float), cudaMemcpyHostToDevice));
+    ctx->ssb_any = ((size_t)ctx->cfg.samplesPerReading * sdrb_format_bytes(ctx->cfg.inputFormat == SDRB_RU16 ? (int)SDRB_CF32 : ctx->cfg.inputFormat)) % 64 != 0;
     // fused AGC + decimator pass (reference-exact chain only): accumulator count and rotated tap table
     if (ctx->d_tapsE) { cudaFree(ctx->d_tapsE); ctx->d_tapsE = nullptr; }
     const int kfmt = ctx->cfg.inputFormat == SDRB_RU16 ? (int)FMT_CF32 : ctx->cfg.inputFormat;
     const char* fe = getenv("SDRB_SSB_FUSED");
-    ctx->ssb_sp = (ctx->ssb_ext || (fe && fe[0] == '0')) ? 0 : ssb_fused_slots(ctx->ssb, kfmt);
+    ctx->ssb_sp = (ctx->ssb_ext || ctx->ssb_any || (fe && fe[0] == '0')) ? 0 : ssb_fused_slots(ctx->ssb, kfmt);
     if (ctx->ssb_sp > 0) {
         const std::vector<float> te = ssb_fused_tap_table(ctx->taps255, ctx->ssb, ctx->ssb_sp);
         CK(cudaMalloc(&ctx->d_tapsE, te.size() * sizeof(float)));
@@ -584,6 +595,25 @@ static int ensure_fft_buffers(sdrb_ctx* ctx) {
         CK(cudaMalloc(&ctx->d_fbA, group * (size_t)n * sizeof(cpx)));
         if (ctx->front) CK(cudaMalloc(&ctx->d_front, group * (size_t)n * sizeof(cpx)));
     }
+    if (ctx->fftPath == 3 && !ctx->d_chirp) {
+        const int m = bluestein_m(n);
+        ctx->blue_m = m;
+        std::vector<cpx> chirp, bf, tw((size_t)m);
+        make_bluestein_tables(n, m, chirp, bf);
+        for (int k = 0; k < m; k++) tw[(size_t)k] = twiddle(k, m);
+        CK(cudaMalloc(&ctx->d_chirp, chirp.size() * sizeof(cpx)));
+        CK(cudaMemcpy(ctx->d_chirp, chirp.data(), chirp.size() * sizeof(cpx), cudaMemcpyHostToDevice));
+        CK(cudaMalloc(&ctx->d_bf, bf.size() * sizeof(cpx)));
+        CK(cudaMemcpy(ctx->d_bf, bf.data(), bf.size() * sizeof(cpx), cudaMemcpyHostToDevice));
+        CK(cudaMalloc(&ctx->d_tw, tw.size() * sizeof(cpx)));
+        CK(cudaMemcpy(ctx->d_tw, tw.data(), tw.size() * sizeof(cpx), cudaMemcpyHostToDevice));
+        size_t chunk = kGenericScratchBytes / ((size_t)m * sizeof(cpx));
+        if (chunk < 1) chunk = 1;
+        if (chunk > frames) chunk = frames;
+        CK(cudaMalloc(&ctx->d_sa, chunk * (size_t)m * sizeof(cpx)));
+        CK(cudaMalloc(&ctx->d_sb, chunk * (size_t)m * sizeof(cpx)));
+        if (ctx->front) CK(cudaMalloc(&ctx->d_front, chunk * (size_t)n * sizeof(cpx)));
+    }
     if (ctx->fftPath == 0 && ctx->front && !ctx->d_front) {
         size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
         if (chunk < 1) chunk = 1;
@@ -644,10 +674,10 @@ static int validate_process(sdrb_ctx* ctx, const void* iq, int n_blocks, unsigne
         return fail(ctx, SDRB_ERR_ARG, "SDRB_STAGE_AUDIO_PULSE consumes the PCM: add SDRB_STAGE_SSB");
     const int n = ctx->cfg.samplesPerReading;
     const size_t bps = sdrb_format_bytes(ctx->cfg.inputFormat);
-    if ((stages & SDRB_STAGE_FFT) && (!is_pow2(n) || n < 2 || n > (1 << 24)))
-        return fail(ctx, SDRB_ERR_UNSUPPORTED, "FFT length %d: only powers of two in [2, 2^24] are built", n);
-    if ((stages & SDRB_STAGE_SSB) && ((size_t)n * bps) % 64 != 0)
-        return fail(ctx, SDRB_ERR_UNSUPPORTED, "SSB block of %d samples: block bytes must be a multiple of 64", n);
+    if ((stages & SDRB_STAGE_FFT) && (is_pow2(n) ? n > (1 << 24) : n > kMaxBluesteinN))
+        return fail(ctx, SDRB_ERR_UNSUPPORTED, "FFT length %d: powers of two up to 2^24 and any other length up to 2^22 are built", n);
+    if ((stages & SDRB_STAGE_SSB) && ((size_t)n * bps) % 64 != 0 && ctx->ssb_ext)
+        return fail(ctx, SDRB_ERR_UNSUPPORTED, "extended SSB chain with a block of %d samples: block bytes must be a multiple of 64", n);
     int rc;
     CK(cudaSetDevice(ctx->device));
     if ((stages & SDRB_STAGE_FFT) && (rc = ensure_fft_buffers(ctx)) != SDRB_OK) return rc;
@@ -706,7 +736,12 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
     // the SSB chain on `ss` (the caller's stream, or the side stream when it runs beside the FFT chain)
     auto run_ssb = [&](cudaStream_t ss) -> int {
         const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 0;
-        if (!ctx->ssb_ext) {
+        if (!ctx->ssb_ext && ctx->ssb_any) {
+            CK(launch_ssb_any(fmt, d_iq, ctx->ssb, ctx->d_taps_lin, ctx->d_ssb_state + s0, ctx->d_agc + (size_t)s0 * n,
+                              ctx->d_pcm + f0s * m, ns, n_blocks, ss));
+            launches += 1;
+            trace_mark("ssb any-length", ss);
+        } else if (!ctx->ssb_ext) {
             CK(launch_ssb(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_tapsE, ctx->ssb_sp, static_cast<float2*>(ctx->d_start) + f0s,
                           ctx->d_ssb_state + s0, ctx->d_a48 + f0s * m, ctx->d_pcm + f0s * m,
                           ctx->d_agc ? ctx->d_agc + f0s * (size_t)n : nullptr, ns, n_blocks, ctx->sm_count, ss, &launches));
@@ -802,6 +837,22 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
                 }
                 CK(launch_fft_big(src_fmt, src, power + (size_t)f0 * n, ctx->d_fbA, ctx->d_fb_tables, n, nf, st));
                 fft_launches += 2;
+            }
+        } else if (ctx->fftPath == 3) {
+            size_t chunk = kGenericScratchBytes / ((size_t)ctx->blue_m * sizeof(cpx));
+            if (chunk < 1) chunk = 1;
+            for (size_t f0 = 0; f0 < (size_t)frames; f0 += chunk) {
+                const int nf = (int)((size_t)frames - f0 < chunk ? (size_t)frames - f0 : chunk);
+                const void* src = static_cast<const unsigned char*>(d_iq) + f0 * n * bps;
+                int src_fmt = fmt;
+                if (ctx->front) {
+                    CK(launch_fft_front(fmt, src, ctx->d_front, ctx->d_win, n, nf, ctx->front, st));
+                    fft_launches++;
+                    src = ctx->d_front;
+                    src_fmt = FMT_CF32;
+                }
+                CK(launch_fft_bluestein(src_fmt, src, power + f0 * n, ctx->d_sa, ctx->d_sb, ctx->d_chirp, ctx->d_bf,
+                                        ctx->d_tw, n, ctx->blue_m, nf, st, &fft_launches));
             }
         } else {
             size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
@@ -901,8 +952,24 @@ int sdrb_process(sdrb_ctx* ctx, const void* iq, int on_device, int n_blocks, uns
 // Any of results_out / power_out / pcm_out may be NULL (that payload then stays on the device).
 int sdrb_process_host(sdrb_ctx* ctx, const void* iq_host, int n_blocks, unsigned stages,
                       sdrb_frame_result* results_out, float* power_out, int16_t* pcm_out) {
+    return sdrb_process_host_ex(ctx, iq_host, n_blocks, stages, results_out, power_out, SDRB_POWER_LINEAR_F32, pcm_out);
+}
+
+static int ensure_view(sdrb_ctx* ctx) {
+    if (!ctx->d_view)
+        CK(cudaMalloc(&ctx->d_view, (size_t)ctx->n_streams * ctx->max_blocks * ctx->cfg.samplesPerReading * sizeof(float)));
+    return SDRB_OK;
+}
+
+int sdrb_process_host_ex(sdrb_ctx* ctx, const void* iq_host, int n_blocks, unsigned stages,
+                         sdrb_frame_result* results_out, void* power_out, int power_format, int16_t* pcm_out) {
     int rc = validate_process(ctx, iq_host, n_blocks, stages);
     if (rc != SDRB_OK) return rc;
+    if (power_format < SDRB_POWER_LINEAR_F32 || power_format > SDRB_POWER_DB_F16)
+        return fail(ctx, SDRB_ERR_ARG, "power_format %d is not a sdrb_power_format", power_format);
+    const bool view = power_out && power_format != SDRB_POWER_LINEAR_F32 && (stages & SDRB_STAGE_FFT);
+    if (view && (rc = ensure_view(ctx)) != SDRB_OK) return rc;
+    const size_t view_elem = power_format == SDRB_POWER_DB_F16 ? 2 : 4;
     const int n = ctx->cfg.samplesPerReading, S = ctx->n_streams;
     const size_t bps = sdrb_format_bytes(ctx->cfg.inputFormat);
     if (!ctx->d_in) CK(cudaMalloc(&ctx->d_in, (size_t)S * ctx->max_blocks * n * bps));
@@ -937,8 +1004,17 @@ int sdrb_process_host(sdrb_ctx* ctx, const void* iq_host, int n_blocks, unsigned
         if ((stages & SDRB_STAGE_FFT) && results_out)
             CK(cudaMemcpyAsync(results_out + f0, ctx->d_results + f0, nf * sizeof(sdrb_frame_result),
                                cudaMemcpyDeviceToHost, ctx->s_out));
-        if ((stages & SDRB_STAGE_FFT) && power_out)
-            CK(cudaMemcpyAsync(power_out + f0 * n, ctx->d_power + f0 * n, nf * n * sizeof(float),
+        if (view) {   // dB view of this chunk's spectra on the compute stream, behind its kernels
+            CK(launch_power_view(ctx->d_power + f0 * n, static_cast<unsigned char*>(ctx->d_view) + f0 * n * view_elem,
+                                 nf * n, power_format, st));
+            ctx->launches += 1;
+            CK(cudaEventRecord(ctx->ev_done[c], st));
+            CK(cudaStreamWaitEvent(ctx->s_out, ctx->ev_done[c], 0));
+            CK(cudaMemcpyAsync(static_cast<unsigned char*>(power_out) + f0 * n * view_elem,
+                               static_cast<unsigned char*>(ctx->d_view) + f0 * n * view_elem, nf * n * view_elem,
+                               cudaMemcpyDeviceToHost, ctx->s_out));
+        } else if ((stages & SDRB_STAGE_FFT) && power_out)
+            CK(cudaMemcpyAsync(static_cast<float*>(power_out) + f0 * n, ctx->d_power + f0 * n, nf * n * sizeof(float),
                                cudaMemcpyDeviceToHost, ctx->s_out));
         if ((stages & SDRB_STAGE_SSB) && pcm_out && m)
             CK(cudaMemcpyAsync(pcm_out + f0 * m * ctx->channels, ctx->d_pcm + f0 * m * ctx->channels,
@@ -1053,6 +1129,22 @@ int sdrb_get_power(sdrb_ctx* ctx, int stream, int block, float* host_out) {
     CK(cudaSetDevice(ctx->device));
     CK(cudaMemcpyAsync(host_out, ctx->d_power + ((size_t)stream * ctx->last_blocks + block) * n, n * sizeof(float),
                        cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SDRB_OK;
+}
+
+int sdrb_get_power_db(sdrb_ctx* ctx, int stream, int block, float* host_out) {
+    if (!ctx || !ctx->configured || !ctx->d_power) return fail(ctx, SDRB_ERR_STATE, "no power spectrum yet");
+    if (stream < 0 || stream >= ctx->n_streams || block < 0 || block >= ctx->last_blocks || !host_out)
+        return fail(ctx, SDRB_ERR_ARG, "stream/block out of range");
+    const size_t n = ctx->cfg.samplesPerReading;
+    CK(cudaSetDevice(ctx->device));
+    int rc = ensure_view(ctx);
+    if (rc != SDRB_OK) return rc;
+    const size_t off = ((size_t)stream * ctx->last_blocks + block) * n;
+    CK(launch_power_view(ctx->d_power + off, static_cast<float*>(ctx->d_view) + off, n, SDRB_POWER_DB_F32, ctx->stream));
+    ctx->launches += 1;
+    CK(cudaMemcpyAsync(host_out, static_cast<float*>(ctx->d_view) + off, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return SDRB_OK;
 }

@@ -19,6 +19,8 @@
 #include <algorithm>
 #include <cstdlib>
 
+#include <cuda_fp16.h>
+
 #include "internal.h"
 
 namespace sdrb {
@@ -493,6 +495,48 @@ cudaError_t launch_tracker(const FrameLocal* d_local, const EstGeometry* d_geo, 
                            sdrb_frame_result* d_results, int n_streams, int n_blocks, cudaStream_t st) {
     if (n_streams <= 0 || n_blocks <= 0) return cudaSuccess;
     k_tracker<<<(n_streams + 127) / 128, 128, 0, st>>>(d_local, d_geo, d_state, d_results, n_streams, n_blocks);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- dB view of the spectrum
+// 10*log10f(p / refPower + 1e-20f), refPower = 1 (fft_process.cpp:142,149), for every bin: an extra output next to
+// the linear payload.  Streaming: 16-byte loads, 16- or 8-byte stores.
+template <bool HALF>
+__global__ void __launch_bounds__(256)
+k_power_view(const float4* __restrict__ p, void* __restrict__ out, size_t n4) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 v = p[i];
+        const float a = 10.0f * log10f(v.x + 1e-20f), b = 10.0f * log10f(v.y + 1e-20f);
+        const float c = 10.0f * log10f(v.z + 1e-20f), d = 10.0f * log10f(v.w + 1e-20f);
+        if (HALF) {
+            const __half2 lo = __floats2half2_rn(a, b), hi = __floats2half2_rn(c, d);
+            uint2 w;
+            w.x = *reinterpret_cast<const unsigned*>(&lo);
+            w.y = *reinterpret_cast<const unsigned*>(&hi);
+            static_cast<uint2*>(out)[i] = w;
+        } else {
+            static_cast<float4*>(out)[i] = make_float4(a, b, c, d);
+        }
+    }
+}
+__global__ void k_power_view_tail(const float* __restrict__ p, void* __restrict__ out, size_t from, size_t count, int half) {
+    const size_t i = from + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const float a = 10.0f * log10f(p[i] + 1e-20f);
+    if (half) static_cast<__half*>(out)[i] = __float2half_rn(a);
+    else static_cast<float*>(out)[i] = a;
+}
+
+cudaError_t launch_power_view(const float* power, void* out, size_t count, int fmt, cudaStream_t st) {
+    if (!count) return cudaSuccess;
+    if (fmt != 1 && fmt != 2) return cudaErrorInvalidValue;
+    const size_t n4 = count / 4;
+    if (n4) {
+        const int grid = (int)((n4 + 255) / 256 < 148 * 16 ? (n4 + 255) / 256 : 148 * 16);
+        if (fmt == 2) k_power_view<true><<<grid, 256, 0, st>>>(reinterpret_cast<const float4*>(power), out, n4);
+        else k_power_view<false><<<grid, 256, 0, st>>>(reinterpret_cast<const float4*>(power), out, n4);
+    }
+    if (count & 3) k_power_view_tail<<<1, 32, 0, st>>>(power, out, n4 * 4, count, fmt == 2);
     return cudaGetLastError();
 }
 

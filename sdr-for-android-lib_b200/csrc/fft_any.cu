@@ -215,4 +215,99 @@ cudaError_t launch_fft_generic(int fmt, const void* iq, float* power, cpx* scrat
     return cudaGetLastError();
 }
 
+
+// ---------------------------------------------------------------- any other length: Bluestein
+// fftwf_plan_dft_1d takes every length (src/dsp/fft_process.cpp:77) and BridgeConfig::setSamplesPerReading does not
+// restrict it (src/bridge-config.h:56).  For N that is not a power of two the transform is the chirp-z identity
+//   n k = (n^2 + k^2 - (k - n)^2) / 2   ->   X[k] = c[k] * sum_n (x[n] c[n]) * conj(c[k - n]),   c[n] = exp(-i pi n^2 / N)
+// i.e. a circular convolution of length M = 2^p >= 2N - 1, done with the power-of-two passes above:
+//   a = x * c, zero padded  ->  FFT_M  ->  * FFT_M(b) (host table, b[n] = b[M - n] = conj(c[n]) for n < N)
+//   ->  inverse FFT_M as conj(FFT_M(conj(.))) / M  ->  * c[k]  ->  |.|^2, halves swapped.
+// The swap is the reference's loop (src/dsp/fft_process.cpp:92-97): i runs to N/2 only, so an odd N leaves its last
+// output bin at the value resize() gave it, zero.  Chirp phases come from n^2 mod 2N in integers (host, double).
+template <int FMT>
+__global__ void __launch_bounds__(256)
+k_blue_pre(const typename Ingest2<FMT>::raw_t* __restrict__ in, const cpx* __restrict__ chirp, cpx* __restrict__ a,
+           int n, int m) {
+    const size_t frame = blockIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    cpx v = mk(0.f, 0.f);
+    if (i < n) v = cmul(Ingest2<FMT>::cvt(in[frame * (size_t)n + i]), chirp[i]);
+    a[frame * (size_t)m + i] = v;
+}
+// a <- conj(a * bf): the conjugate turns the following forward transform into the inverse one
+__global__ void __launch_bounds__(256)
+k_blue_mul(cpx* __restrict__ a, const cpx* __restrict__ bf, int m) {
+    const size_t frame = blockIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const cpx v = cmul(a[frame * (size_t)m + i], bf[i]);
+    a[frame * (size_t)m + i] = mk(v.x, -v.y);
+}
+__global__ void __launch_bounds__(256)
+k_blue_post(const cpx* __restrict__ a, const cpx* __restrict__ chirp, float* __restrict__ power, int n, int m, float inv_m) {
+    const size_t frame = blockIdx.y;
+    const int o = blockIdx.x * blockDim.x + threadIdx.x;   // output (shifted) bin
+    if (o >= n) return;
+    const int half = n >> 1;
+    float p = 0.0f;                                         // odd n: the last bin is never written by the reference
+    if (o < 2 * half) {
+        const int k = o < half ? o + half : o - half;
+        const cpx r = a[frame * (size_t)m + k];
+        const cpx x = cmul(mk(r.x * inv_m, -r.y * inv_m), chirp[k]);
+        p = __fadd_rn(__fmul_rn(x.x, x.x), __fmul_rn(x.y, x.y));   // re*re + im*im, :85
+    }
+    power[frame * (size_t)n + o] = p;
+}
+
+int bluestein_m(int n) {
+    int m = 1;
+    while (m < 2 * n - 1) m <<= 1;
+    return m;
+}
+
+// power-of-two cpx -> cpx transform of every frame: `buf` in, result in the returned buffer (buf or other)
+static cpx* blue_fft(cpx* buf, cpx* other, const cpx* tw, int m, int n_frames, cudaStream_t st, int* launches) {
+    int bits = 0;
+    while ((1 << bits) < m) bits++;
+    int left = bits, Ns = 1;
+    cpx *cur = buf, *nxt = other;
+    while (left > 0) {
+        const int rb = left >= 4 ? 4 : left;
+        launch_pass_r<-1>(1 << rb, false, cur, nxt, tw, m, Ns, 1.0f, n_frames, st);
+        if (launches) (*launches)++;
+        cpx* t = cur; cur = nxt; nxt = t;
+        Ns <<= rb;
+        left -= rb;
+    }
+    return cur;
+}
+
+// chirp: [n] c[k]; bf: [m] FFT_M of the wrapped conjugate chirp; tw_m: [m] W_m^k; sa, sb: [n_frames][m] each
+cudaError_t launch_fft_bluestein(int fmt, const void* iq, float* power, cpx* sa, cpx* sb, const cpx* chirp,
+                                 const cpx* bf, const cpx* tw_m, int n, int m, int n_frames, cudaStream_t st,
+                                 int* launches) {
+    if (n_frames <= 0) return cudaSuccess;
+    const size_t in_bytes = fmt == FMT_CU8 ? 2 : (fmt == FMT_CS16 ? 4 : 8);
+    for (int f0 = 0; f0 < n_frames; f0 += 65535) {   // gridDim.y limit
+        const int nf = n_frames - f0 < 65535 ? n_frames - f0 : 65535;
+        const void* src = static_cast<const unsigned char*>(iq) + (size_t)f0 * n * in_bytes;
+        dim3 gm((unsigned)((m + 255) / 256), (unsigned)nf), gn((unsigned)((n + 255) / 256), (unsigned)nf);
+        switch (fmt) {
+            case FMT_CU8: k_blue_pre<FMT_CU8><<<gm, 256, 0, st>>>(static_cast<const uint16_t*>(src), chirp, sa, n, m); break;
+            case FMT_CS16: k_blue_pre<FMT_CS16><<<gm, 256, 0, st>>>(static_cast<const uint32_t*>(src), chirp, sa, n, m); break;
+            case FMT_CF32: k_blue_pre<FMT_CF32><<<gm, 256, 0, st>>>(static_cast<const cpx*>(src), chirp, sa, n, m); break;
+            default: return cudaErrorInvalidValue;
+        }
+        cpx* a = blue_fft(sa, sb, tw_m, m, nf, st, launches);
+        cpx* o = a == sa ? sb : sa;
+        k_blue_mul<<<gm, 256, 0, st>>>(a, bf, m);
+        a = blue_fft(a, o, tw_m, m, nf, st, launches);
+        k_blue_post<<<gn, 256, 0, st>>>(a, chirp, power + (size_t)f0 * n, n, m, 1.0f / (float)m);
+        if (launches) (*launches) += 3;
+    }
+    return cudaGetLastError();
+}
+
 }  // namespace sdrb

@@ -1,5 +1,6 @@
 // fft_tables.h — host-side twiddle table generation (double precision, rounded once).
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <vector>
 
@@ -43,6 +44,50 @@ inline std::vector<cpx> make_fb_tables() {
     for (int j = 0; j < RadixReg<R>::kLog2; j++)
         for (int n2 = 0; n2 < G::L; n2++) TB[j * G::L + n2] = twiddle(((long long)n2 * R) << j, N);
     return t;
+}
+
+// Bluestein tables for length n, convolution length m (a power of two >= 2n - 1): chirp c[k] = exp(-i pi k^2 / n)
+// with k^2 reduced mod 2n in integers, and bf = FFT_m of b, b[j] = b[m - j] = conj(c[j]) for j < n, in double.
+inline void make_bluestein_tables(int n, int m, std::vector<cpx>& chirp, std::vector<cpx>& bf) {
+    const double pi = 3.14159265358979323846264338327950288;
+    std::vector<double> cr((size_t)n), ci((size_t)n);
+    chirp.resize((size_t)n);
+    for (long long k = 0; k < n; k++) {
+        const long long q = (k * k) % (2LL * n);
+        const double a = -pi * (double)q / (double)n;
+        cr[(size_t)k] = std::cos(a);
+        ci[(size_t)k] = std::sin(a);
+        chirp[(size_t)k] = mk((float)cr[(size_t)k], (float)ci[(size_t)k]);
+    }
+    std::vector<double> re((size_t)m, 0.0), im((size_t)m, 0.0);
+    for (int j = 0; j < n; j++) {
+        re[(size_t)j] = cr[(size_t)j];
+        im[(size_t)j] = -ci[(size_t)j];
+        if (j) { re[(size_t)(m - j)] = cr[(size_t)j]; im[(size_t)(m - j)] = -ci[(size_t)j]; }
+    }
+    // in-place iterative radix-2 FFT in double (bit reversal + butterflies)
+    int bits = 0;
+    while ((1 << bits) < m) bits++;
+    for (int i = 0; i < m; i++) {
+        unsigned r = 0;
+        for (int b = 0; b < bits; b++) if (i & (1 << b)) r |= 1u << (bits - 1 - b);
+        if ((int)r > i) { std::swap(re[(size_t)i], re[r]); std::swap(im[(size_t)i], im[r]); }
+    }
+    for (int len = 2; len <= m; len <<= 1) {
+        const int half = len >> 1;
+        for (int j = 0; j < half; j++) {
+            const double a = -2.0 * pi * (double)j / (double)len;
+            const double wr = std::cos(a), wi = std::sin(a);
+            for (int base = 0; base < m; base += len) {
+                const size_t u = (size_t)(base + j), v = u + (size_t)half;
+                const double tr = re[v] * wr - im[v] * wi, ti = re[v] * wi + im[v] * wr;
+                re[v] = re[u] - tr; im[v] = im[u] - ti;
+                re[u] += tr; im[u] += ti;
+            }
+        }
+    }
+    bf.resize((size_t)m);
+    for (int i = 0; i < m; i++) bf[(size_t)i] = mk((float)re[(size_t)i], (float)im[(size_t)i]);
 }
 
 }  // namespace sdrb

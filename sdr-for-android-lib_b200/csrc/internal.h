@@ -129,6 +129,11 @@ cudaError_t fft16k2_prepare(const cpx* host_tables);   // make_f2_tables() layou
 cudaError_t launch_fft_generic(int fmt, const void* iq, float* power, cpx* scratch_a, cpx* scratch_b,
                                const cpx* twiddles, int n, int n_frames, cudaStream_t st, int* launches);
 int fft_generic_passes(int n);
+// any other length (Bluestein over the power-of-two passes): M = bluestein_m(n) >= 2n - 1
+int bluestein_m(int n);
+cudaError_t launch_fft_bluestein(int fmt, const void* iq, float* power, cpx* sa, cpx* sb, const cpx* chirp,
+                                 const cpx* bf, const cpx* tw_m, int n, int m, int n_frames, cudaStream_t st,
+                                 int* launches);
 // extension front end (window / block-mean removal) for the multi-pass paths: raw IQ -> cf32
 cudaError_t launch_fft_front(int fmt, const void* iq, cpx* out, const float* win, int n, int n_frames, int front,
                              cudaStream_t st);
@@ -147,6 +152,8 @@ cudaError_t estimator_prepare();
 size_t estimator_scratch_floats(const EstGeometry& g, int n_frames);
 cudaError_t launch_tracker(const FrameLocal* d_local, const EstGeometry* d_geo, FftStreamState* d_state,
                            sdrb_frame_result* d_results, int n_streams, int n_blocks, cudaStream_t st);
+// estimator.cu : dB view of linear power, out = float (fmt 1) or __half (fmt 2); 10*log10f(p + 1e-20f)
+cudaError_t launch_power_view(const float* power, void* out, size_t count, int fmt, cudaStream_t st);
 // ssb.cu.  d_taps is the [decim][ssb_smax] slot-major tap table (split decimator, extended chain);
 // d_tapsE the rotated table of the fused pass (ssb_fused_tap_table), sp = ssb_fused_slots (0: split pair).
 int ssb_smax(const SsbParams& P);
@@ -157,6 +164,9 @@ cudaError_t ssb_prepare();
 cudaError_t launch_ssb(int fmt, const void* iq, const SsbParams& P, const float* d_taps, const float* d_tapsE, int sp,
                        float2* d_start, SsbStreamState* d_state, float* d_a48, int16_t* d_pcm, float* d_agc,
                        int n_streams, int n_blocks, int sm_count, cudaStream_t st, int* launches);
+// any block length (bytes not a multiple of 64): one thread per stream, scalar loads; scratch [n_streams][P.n] floats
+cudaError_t launch_ssb_any(int fmt, const void* iq, const SsbParams& P, const float* taps_lin, SsbStreamState* d_state,
+                           float* scratch, int16_t* d_pcm, int n_streams, int n_blocks, cudaStream_t st);
 cudaError_t launch_ssb_audio(const float* d_a48, const SsbParams& P, SsbStreamState* d_state, int16_t* d_pcm,
                              int n_streams, int n_blocks, cudaStream_t st);
 // ssb_ext.cu : NCO channel bank + Weaver sideband selection (extension stages)

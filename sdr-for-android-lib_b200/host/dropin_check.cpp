@@ -84,6 +84,11 @@ int main(int argc, char** argv) {
         // the spectral detector saw every frame's best-1 kHz sigma
         same = same && fft.lastPulse().spectralSnrSigma == fft.getBest1kHzSnrSigma() && fft.lastPulse().spectralLiveEtat >= 0;
         for (int b = 0; same && b < B; b++) same = queued[b] == direct[b];
+        if (fft.failedCalls() || ssb.failedBlocks()) {   // the front end records failures instead of throwing
+            fprintf(stderr, "dropin_check: %lu failed FFT calls (%s), %lu failed SSB blocks (%s)\n", fft.failedCalls(),
+                    fft.lastError().c_str(), (unsigned long)ssb.failedBlocks(), ssb.lastError().c_str());
+            same = 0;
+        }
         put(f, &same, sizeof same);
     } catch (const std::exception& e) {
         fprintf(stderr, "dropin_check: %s\n", e.what());

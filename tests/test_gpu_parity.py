@@ -266,18 +266,55 @@ def test_error_behaviour(sdrb, gpu_ctx):
     cfg = sdrb.Config(FC, 2_000_000, 12000, 5, inputFormat=2)
     gpu_ctx.configure(cfg, 1, 1)
     iq = np.zeros((1, 1, 12000, 2), np.float32)
-    with pytest.raises(sdrb.SdrbError) as e:
-        gpu_ctx.process(iq, 1, sdrb.STAGE_FFT)
-    assert e.value.code == -3 and "power" in str(e.value)
     with pytest.raises(sdrb.SdrbError):
         gpu_ctx.process(iq, 2, sdrb.STAGE_SSB)          # more blocks than configured
     with pytest.raises(sdrb.SdrbError):
         gpu_ctx.configure(sdrb.Config(FC, 0, 1024, 5), 1, 1)
+    big = sdrb.Config(FC, 2_000_000, (1 << 22) + 2, 5, inputFormat=2)   # beyond the any-length transform's range
+    gpu_ctx.configure(big, 1, 1)
+    with pytest.raises(sdrb.SdrbError) as e:
+        gpu_ctx.process(np.zeros((1, 1, (1 << 22) + 2, 2), np.float32), 1, sdrb.STAGE_FFT)
+    assert e.value.code == -3
     fresh = sdrb.Context(0)
     with pytest.raises(sdrb.SdrbError) as e:
         fresh.process(iq, 1)
     assert e.value.code == -4
     fresh.close()
+
+
+@pytest.mark.parametrize("fmt,n,fs", [(2, 12000, 2_000_000), (0, 10000, 2_000_000), (1, 5000, 2_500_000),
+                                      (2, 12001, 2_000_000), (0, 4099, 1_000_000), (2, 1000, 250_000), (2, 3, 250_000),
+                                      (2, 1, 250_000)])
+def test_any_block_length(sdrb, gpu_ctx, fmt, n, fs):
+    """fftwf_plan_dft_1d takes every length (fft_process.cpp:77) and processSSB_opt every block size: lengths that
+    are not powers of two run the chirp-z transform over the power-of-two passes, SSB blocks whose bytes are not a
+    multiple of 64 the scalar pass.  Same checks as for the fast paths (an odd length leaves its last bin at zero,
+    as the reference's half-swap loop does); the float transform's error floor is that of the 2N-point convolution."""
+    S, B = 3, 3
+    cfg = sdrb.Config(FC, fs, n, 5, inputFormat=fmt)
+    plan = sdrb.plan_config(cfg)
+    iq = make_iq(sdrb, fmt, fs, 5, S, B, n)
+    gpu_ctx.configure(cfg, S, B)
+    gpu_ctx.process(iq, B, sdrb.STAGE_FFT | sdrb.STAGE_SSB)
+    res, pcm = gpu_ctx.results(), gpu_ctx.pcm()
+    assert pcm.shape == (S, B, plan.pcmPerBlock)
+    for s in range(S):
+        of, os_ = ol.OracleFft(FC, fs, n, 5), ol.OracleSsb()
+        for b in range(B):
+            f32 = ol.to_cf32(iq[s, b], fmt)
+            ref, got = ol.oracle_power(f32), gpu_ctx.power(s, b)
+            total = float(ref.astype(np.float64).sum())
+            tol = 1e-5 * ref + 3.0 * (2.0 * np.sqrt(ref) * 3e-7 * np.sqrt(total) + 1e-9 * total / max(n, 1))
+            assert np.all(np.abs(got - ref) <= tol), (s, b, float(np.abs(got - ref).max()))
+            if n & 1:
+                assert got[n - 1] == 0.0
+            if plan.focusLen > 0:
+                check_results(res[s, b], of.evaluate(got), 0, ("any-n", s, b))
+            exp = os_.process(f32, fs, 1, 1)
+            assert exp.size == pcm.shape[2]
+            if exp.size:
+                assert np.abs(pcm[s, b].astype(int) - exp.astype(int)).max() <= 1, (s, b)
+                assert (pcm[s, b] == exp).mean() >= 0.999
 
 
 def test_full_size_properties_c2(sdrb, gpu_ctx):
@@ -430,3 +467,32 @@ def test_replan_keeps_every_carried_state(sdrb, gpu_ctx):
                 exp = orc[s].process(ol.to_cf32(iq[s, b], 2), fs, 1, 1)
                 assert exp.size == pcm.shape[2]
                 assert np.abs(pcm[s, b].astype(int) - exp.astype(int)).max() <= 1, (step, s, b)
+
+
+def test_db_view_of_the_spectrum(sdrb, gpu_ctx):
+    """north_star: '|X|^2 to dB'.  The dB view (10*log10f(p + 1e-20f), fft_process.cpp:149) of every bin within 1e-3 dB
+    of the same expression on the linear output; the half-precision view of the host-to-host call within its own
+    quantisation (0.0625 dB at 64..128 dB); the linear payload is untouched by either."""
+    n, fs, S, B = 16384, 2_000_000, 6, 2
+    cfg = sdrb.Config(FC, fs, n, 5, inputFormat=0)
+    iq = make_iq(sdrb, 0, fs, 0, S, B, n)
+    gpu_ctx.configure(cfg, S, B)
+    gpu_ctx.process(iq, B, sdrb.STAGE_FFT)
+    lin = gpu_ctx.power_all().copy()
+    for s, b in ((0, 0), (5, 1)):
+        want = (np.float32(10.0) * np.log10(lin[s, b] + np.float32(1e-20))).astype(np.float32)
+        assert np.abs(gpu_ctx.power_db(s, b) - want).max() < 1e-3
+        ref = ol.oracle_power(ol.to_cf32(iq[s, b], 0))
+        strong = ref > 1e-4 * ref.max()
+        assert np.abs(gpu_ctx.power_db(s, b)[strong] - 10 * np.log10(ref[strong] + 1e-20)).max() < 1e-3
+    gpu_ctx.reset_state()
+    r = np.zeros((S, B), dtype=sdrb.RESULT_DTYPE)
+    h16 = np.zeros((S, B, n), dtype=np.float16)
+    gpu_ctx.process_host(iq, B, sdrb.STAGE_FFT, results=r, power=h16, power_format=sdrb.POWER_DB_F16)
+    want = 10.0 * np.log10(lin.astype(np.float64) + 1e-20)
+    assert np.abs(h16.astype(np.float64) - want).max() <= 0.0625 * 0.5 + 1e-3 + np.abs(want).max() * 2.0 ** -11
+    f32 = np.zeros((S, B, n), dtype=np.float32)
+    gpu_ctx.reset_state()
+    gpu_ctx.process_host(iq, B, sdrb.STAGE_FFT, results=r, power=f32, power_format=sdrb.POWER_DB_F32)
+    assert np.abs(f32.astype(np.float64) - want).max() < 1e-3
+    assert np.array_equal(gpu_ctx.power_all(), lin)
