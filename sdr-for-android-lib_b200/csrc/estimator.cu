@@ -26,7 +26,7 @@
 namespace sdrb {
 
 constexpr int EST_WARPS = 4;                 // frames per CTA in k_estimator (one warp each)
-constexpr int EST_SMEM_POOL_FLOATS = 2048;   // pooled bins staged in shared memory per warp; above: global scratch
+constexpr int EST_SMEM_POOL_FLOATS = 8192;   // pooled bins staged in shared memory per warp (32 KiB x 4 warps at most); above: global scratch
 constexpr int EST_MAX_BANDS = 11;
 
 __device__ __forceinline__ float db10(float p) {
