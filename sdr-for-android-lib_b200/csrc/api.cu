@@ -124,8 +124,8 @@ struct sdrb_ctx {
     AirspyStreamState* d_air_state = nullptr;
     float* d_air_T = nullptr;
     cpx* d_air_iq = nullptr;
+    float* d_ext_work = nullptr;   // extended chain: removeDC output X and mixed samples M (ssb_ext.cu)
     float* d_agc = nullptr;        // post-AGC samples [streams][blocks][N] between k_ssb_agc and k_ssb_fir
-    bool agc_tried = false;
     float* d_air_work = nullptr;   // per-chunk start / end values of the DC pass
     size_t air_work_per_stream = 0;
     int air_chunk = 0, air_warm = 0;
@@ -186,8 +186,7 @@ static void free_buffers(sdrb_ctx* c) {
                      (void**)&c->d_front, (void**)&c->d_fb_tables, (void**)&c->d_fbA,
                      (void**)&c->d_sp_state, (void**)&c->d_au_state, (void**)&c->d_sp_e, (void**)&c->d_sp_f,
                      (void**)&c->d_au_e, (void**)&c->d_pulse, (void**)&c->d_air_state, (void**)&c->d_air_T,
-                     (void**)&c->d_air_iq, (void**)&c->d_air_work, (void**)&c->d_agc};
-    c->agc_tried = false;
+                     (void**)&c->d_air_iq, (void**)&c->d_air_work, (void**)&c->d_agc, (void**)&c->d_ext_work};
     for (void** p : ptrs) {
         if (*p) cudaFree(*p);
         *p = nullptr;
@@ -641,19 +640,24 @@ static int ensure_ssb_buffers(sdrb_ctx* ctx) {
     const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 1;
     if (!ctx->d_a48) CK(cudaMalloc(&ctx->d_a48, frames * m * sizeof(float)));
     if (!ctx->d_pcm) CK(cudaMalloc(&ctx->d_pcm, frames * m * sizeof(int16_t)));
-    // scratch of the split AGC / decimator pair: one float per input sample (and per channel of an NCO bank).
-    // The reference-exact chain needs it only when the fused pass does not take the decimation factor (then it is
-    // required); the extended chain falls back to its own fused kernel without it (SDRB_SSB_SPLIT=0, or no memory).
-    if (!ctx->d_agc && !ctx->agc_tried && (ctx->ssb_ext || ctx->ssb_sp == 0)) {
-        ctx->agc_tried = true;
-        const char* e = getenv("SDRB_SSB_SPLIT");
-        if (!ctx->ssb_ext || !(e && e[0] == '0')) {
-            const size_t bytes = frames * (size_t)ctx->cfg.samplesPerReading * sizeof(float);   // frames includes the channels
-            if (cudaMalloc(&ctx->d_agc, bytes) != cudaSuccess) {
-                cudaGetLastError();
-                ctx->d_agc = nullptr;
-                if (!ctx->ssb_ext) return fail(ctx, SDRB_ERR_NOMEM, "no memory for the %zu-byte AGC scratch of the split SSB pass", bytes);
-            }
+    // scratch of the split AGC / decimator pair: one float per input sample (and per channel of an NCO bank).  The
+    // reference-exact chain needs it only when the fused pass does not take the decimation factor; the extended
+    // chain always, plus its pre-pass buffers (removeDC output and mixed samples).
+    if (!ctx->d_agc && (ctx->ssb_ext || ctx->ssb_sp == 0)) {
+        const size_t bytes = frames * (size_t)ctx->cfg.samplesPerReading * sizeof(float);   // frames includes the channels
+        if (cudaMalloc(&ctx->d_agc, bytes) != cudaSuccess) {
+            cudaGetLastError();
+            ctx->d_agc = nullptr;
+            return fail(ctx, SDRB_ERR_NOMEM, "no memory for the %zu-byte AGC scratch of the SSB chain", bytes);
+        }
+    }
+    if (ctx->ssb_ext && !ctx->d_ext_work) {
+        const size_t fl = ssb_ext_work_floats(ctx->cfg.samplesPerReading, ctx->n_streams, ctx->channels, ctx->max_blocks,
+                                              ctx->cfg.ssbTrueSideband != 0);
+        if (cudaMalloc(&ctx->d_ext_work, fl * sizeof(float)) != cudaSuccess) {
+            cudaGetLastError();
+            ctx->d_ext_work = nullptr;
+            return fail(ctx, SDRB_ERR_NOMEM, "no memory for the %zu-byte pre-pass buffers of the extended SSB chain", fl * sizeof(float));
         }
     }
     return SDRB_OK;
@@ -676,8 +680,9 @@ static int validate_process(sdrb_ctx* ctx, const void* iq, int n_blocks, unsigne
     const size_t bps = sdrb_format_bytes(ctx->cfg.inputFormat);
     if ((stages & SDRB_STAGE_FFT) && (is_pow2(n) ? n > (1 << 24) : n > kMaxBluesteinN))
         return fail(ctx, SDRB_ERR_UNSUPPORTED, "FFT length %d: powers of two up to 2^24 and any other length up to 2^22 are built", n);
-    if ((stages & SDRB_STAGE_SSB) && ((size_t)n * bps) % 64 != 0 && ctx->ssb_ext)
-        return fail(ctx, SDRB_ERR_UNSUPPORTED, "extended SSB chain with a block of %d samples: block bytes must be a multiple of 64", n);
+    if ((stages & SDRB_STAGE_SSB) && ctx->ssb_ext && n % 32 != 0)
+        return fail(ctx, SDRB_ERR_UNSUPPORTED, "extended SSB chain with a block of %d samples: the block length must be a "
+                                               "multiple of 32 samples", n);
     int rc;
     CK(cudaSetDevice(ctx->device));
     if ((stages & SDRB_STAGE_FFT) && (rc = ensure_fft_buffers(ctx)) != SDRB_OK) return rc;
@@ -750,8 +755,9 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
             CK(launch_ssb_ext(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_inc1, ctx->inc2, ctx->cfg.ssbTrueSideband != 0,
                               static_cast<float4*>(ctx->d_start) + f0s * C, ctx->d_ssb_state + (size_t)s0 * C,
                               ctx->d_a48 + f0s * C * m, ctx->d_pcm + f0s * C * m,
-                              ctx->d_agc ? ctx->d_agc + f0s * C * (size_t)n : nullptr, ns, ctx->channels, n_blocks,
-                              ctx->ssb_samples, ss, &launches));
+                              ctx->d_agc + f0s * C * (size_t)n,
+                              ctx->d_ext_work + ssb_ext_work_floats(n, s0, ctx->channels, n_blocks, ctx->cfg.ssbTrueSideband != 0),
+                              ns, ctx->channels, n_blocks, ctx->ssb_samples, ss, &launches));
         }
         return SDRB_OK;
     };

@@ -120,6 +120,39 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
     // co-tenants then simply takes fewer transforms instead of finishing last.
     unsigned parity = 0;
     int fn;
+    // Rotated loop (no front end): phase 3 of transform f and the load + DFT32 of the NEXT transform sit in one basic
+    // block, so the scheduler can put the exchange loads and global stores of phase 3 under the FP work of the next
+    // transform's phase 1 (measured on the B200, 37888 u8 transforms: 1.658 -> 1.640 ms per step, still 96 registers).
+    if constexpr (FRONT == 0) {
+        if (f >= n_frames) return;
+        cpx v[32];
+        if (kStaged) { mbar_wait(bar, parity); parity ^= 1u; f2_phase1_load<FMT>(t, stage, v); }
+        else f2_phase1_load<FMT>(t, in + (size_t)f * F2_N, v);
+        fft32(v);
+        for (;;) {
+            __syncthreads();  // E is free (previous phase 3 has read it) and the stage has been consumed
+            if (t == 0) {
+                const int nx = ticket ? (int)gridDim.x + atomicAdd(ticket, 1) : f + (int)gridDim.x;
+                s_next = nx;
+                if (kStaged && nx < n_frames) {
+                    mbar_expect_tx(bar, F2Smem<FMT>::kStageBytes);
+                    bulk_g2s(stage, in + (size_t)nx * F2_N, F2Smem<FMT>::kStageBytes, bar);
+                }
+            }
+            f2_phase1_twiddle_store(t, TP, v, E);
+            __syncthreads();
+            fn = s_next;
+            f2_phase2(t, E);
+            __syncthreads();
+            if (fn >= n_frames) break;
+            if (kStaged) { mbar_wait(bar, parity); parity ^= 1u; f2_phase1_load<FMT>(t, stage, v); }
+            else f2_phase1_load<FMT>(t, in + (size_t)fn * F2_N, v);
+            f2_phase3(t, E, F2DevTw(), out + (size_t)f * F2_N);
+            fft32(v);
+            f = fn;
+        }
+        f2_phase3(t, E, F2DevTw(), out + (size_t)f * F2_N);
+    } else {
     for (; f < n_frames; f = fn) {
         cpx v[32];
         if (kStaged) {
@@ -146,6 +179,7 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
         f2_phase2(t, E);
         __syncthreads();
         f2_phase3(t, E, F2DevTw(), out + (size_t)f * F2_N);
+    }
     }
 }
 

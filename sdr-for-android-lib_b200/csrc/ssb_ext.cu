@@ -11,12 +11,19 @@
 // oracle/sdr_oracle_ext.c:sdr_oracle_process_ssbx.  With every knob at identity the library
 // never comes here (ssb.cu is the reference-exact path).
 //
-// Parallel structure is the one of ssb.cu with (stream, channel) as the unit that carries state:
-//   k_ssbx_state : one lane per (stream, channel), blocks in order: removeDC + NCO + IIR2(I[,Q]),
-//                  records the exact filter state at every block start
-//   k_ssbx_main  : one lane per (stream, channel, block): full chain to ~48 kHz float audio
-//   k_ssb_audio  : (ssb.cu) one lane per (stream, channel): HP/BP, boost, PCM
-// PCM layout: [stream][channel][block][m].
+// Structure (round 2).  Only the IIR2 carries state from sample to sample across blocks; everything in front of it is
+// either per block (removeDC, shared by every channel of a stream) or closed-form per sample (the NCO phase is
+// inc * samples-since-reset), so it is hoisted out of the sequential lane:
+//   k_ssbx_dc    : one lane per (stream, block): removeDC (complex, a 2-operation chain) -> X [stream][block][n] cf32
+//   k_ssbx_mix   : one thread per 4 samples of a (stream, channel): NCO + first mix -> M [stream][channel][block][n]
+//                  (re only, or (re, im) pairs with true sideband)
+//   k_ssbx_state : one lane per CHAIN (the I filter of a (stream, channel), and its Q filter with true sideband),
+//                  blocks in order: IIR2 on M only (9 operations per sample, a 20-cycle chain) -- it was 64
+//                  instructions and 89 cycles per sample with DC, NCO and mix on the lane -- records the exact filter
+//                  state at every block start
+//   k_ssbx_agc   : one lane per (stream, channel, block): IIR2 from that state, second mix (true sideband), demod,
+//                  AGC in sweeps -> post-AGC samples; k_ssb_fir (ssb.cu) decimates; k_ssb_audio: HP/BP, boost, PCM
+// PCM layout: [stream][channel][block][m].  The block length must be a multiple of 32 samples.
 #include "internal.h"
 #include "nco.cuh"
 #include "ssb_common.cuh"
@@ -27,16 +34,22 @@ namespace sdrb {
 template <int NST>
 struct TileStreamX {
     const unsigned char* const* rowptr;   // this warp's 32 row pointers (shared memory)
-    unsigned char* tile;                  // this warp's two tiles
+    unsigned char* tile;                  // this warp's tiles
     int lane;
+    const unsigned char* rp[4];           // the four rows this lane copies, in registers (bind())
+    // Fetching the pointers from shared memory at every chunk put four dependent LDS.64 -> LDGSTS pairs (all through
+    // one register, so in series) in front of every chunk: ~300 cycles on the lone in-order warp of a state pass.
+    __device__ __forceinline__ void bind() {
+        const int sub = lane & 3, r0 = lane >> 2;
+#pragma unroll
+        for (int k = 0; k < 4; k++) rp[k] = rowptr[r0 + 8 * k] + sub * 16;
+    }
     __device__ __forceinline__ void issue(int chunk, int stage) {
         const int sub = lane & 3, r0 = lane >> 2;
-        unsigned char* t = tile + stage * SSB_TILE_BYTES;
+        unsigned char* t = tile + stage * SSB_TILE_BYTES + sub * 16;
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const int r = r0 + 8 * k;
-            cp_async16(t + r * SSB_ROW_PITCH + sub * 16, rowptr[r] + (size_t)chunk * SSB_ROW_BYTES + sub * 16);
-        }
+        for (int k = 0; k < 4; k++)
+            cp_async16(t + (r0 + 8 * k) * SSB_ROW_PITCH, rp[k] + (size_t)chunk * SSB_ROW_BYTES);
         cp_async_commit();
     }
     __device__ __forceinline__ const uint4* row(int stage) const {
@@ -57,280 +70,275 @@ struct TileStreamX {
     __device__ __forceinline__ const uint4* cur(int c) const { return row(c % NST); }
 };
 
-struct SsbxLane {
-    float dcr, dci;            // removeDC (complex), reset per block
-    float iz1, iz2, qz1, qz2;  // IIR2 previous outputs, I and Q
-    uint32_t ph1, ph2;         // NCO phases
-};
+constexpr int SSBX_WARPS = 4;
+// cp.async stages of the state pass.  One warp per CTA and per SM pulls 2 KB per chunk and spends only 160-320 cycles
+// of arithmetic on it (8 or 16 float samples per chain and chunk, against 32 for u8 input in ssb.cu): with eight stages
+// the 14 KB in flight per SM did not cover the DRAM round trip and the walk ran at ~336 cycles per chunk whatever the
+// chunk held (measured: 41 cycles per sample without, 62 with true sideband, against a 20-cycle chain).
+constexpr int SSBX_STATE_STAGES = 24;
 
-// removeDC + NCO 1 + IIR2 on I (and Q): one sample.  Returns yI, yQ.
-template <bool TSB>
-__device__ __forceinline__ void ssbx_front(SsbxLane& L, float I, float Q, const SsbParams& P, float oma,
-                                           uint32_t inc1, float& yi, float& yq) {
-    L.dcr = __fadd_rn(__fmul_rn(P.dcAlpha, L.dcr), __fmul_rn(oma, I));
-    L.dci = __fadd_rn(__fmul_rn(P.dcAlpha, L.dci), __fmul_rn(oma, Q));
-    const float xr = __fsub_rn(I, L.dcr), xi = __fsub_rn(Q, L.dci);
-    float c1, s1;
-    nco_cs(L.ph1, c1, s1);
-    L.ph1 += inc1;
-    const float mr = __fadd_rn(__fmul_rn(xr, c1), __fmul_rn(xi, s1));
-    float y = __fmul_rn(P.rf.a0, mr);
-    y = __fadd_rn(y, __fmul_rn(P.rf.a1, L.iz1));
-    y = __fadd_rn(y, __fmul_rn(P.rf.a2, L.iz2));
-    y = __fsub_rn(y, __fmul_rn(P.rf.b1, L.iz1));
-    y = __fsub_rn(y, __fmul_rn(P.rf.b2, L.iz2));
-    L.iz2 = L.iz1; L.iz1 = y;
-    yi = y;
-    yq = 0.0f;
-    if (TSB) {
-        const float mi = __fsub_rn(__fmul_rn(xi, c1), __fmul_rn(xr, s1));
-        float w = __fmul_rn(P.rf.a0, mi);
-        w = __fadd_rn(w, __fmul_rn(P.rf.a1, L.qz1));
-        w = __fadd_rn(w, __fmul_rn(P.rf.a2, L.qz2));
-        w = __fsub_rn(w, __fmul_rn(P.rf.b1, L.qz1));
-        w = __fsub_rn(w, __fmul_rn(P.rf.b2, L.qz2));
-        L.qz2 = L.qz1; L.qz1 = w;
-        yq = w;
-    }
+// A 16-byte shared-memory load that stays where it is written: left to the compiler, the loads of an iteration sink
+// to their first use and the single warp of a state-pass CTA then waits a shared-memory round trip every few samples
+// (measured: 36 cycles per sample against the chain's 20).
+__device__ __forceinline__ float4 lds128_now(const float4* p) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "r"((unsigned)__cvta_generic_to_shared(p)));
+    return v;
 }
 
-constexpr int SSBX_WARPS = 4;
+// iir2Process :75-84 (previous OUTPUTS as state), one sample
+__device__ __forceinline__ float ssbx_iir(const BiquadCoef& c, float x, float& z1, float& z2) {
+    float y = __fmul_rn(c.a0, x);
+    y = __fadd_rn(y, __fmul_rn(c.a1, z1));
+    y = __fadd_rn(y, __fmul_rn(c.a2, z2));
+    y = __fsub_rn(y, __fmul_rn(c.b1, z1));
+    y = __fsub_rn(y, __fmul_rn(c.b2, z2));
+    z2 = z1;
+    z1 = y;
+    return y;
+}
 
-// ---------------------------------------------------------------- pass 1
-template <int FMT, bool TSB>
-__global__ void __launch_bounds__(32)
-k_ssbx_state(const void* __restrict__ iq, const __grid_constant__ SsbParams P, const uint32_t* __restrict__ inc1_tab,
-             float4* __restrict__ start, SsbStreamState* __restrict__ state, int n_streams, int channels,
-             int n_blocks, unsigned long long base_samples) {
+// ---------------------------------------------------------------- pre-pass 1: removeDC per (stream, block)
+// removeDC (src/ssb/ssb_demod_opt.cpp:49-55) on the complex sample, restarted per block; lanes = frames.
+template <int FMT>
+__global__ void __launch_bounds__(SSBX_WARPS * 32)
+k_ssbx_dc(const void* __restrict__ iq, const __grid_constant__ SsbParams P, float2* __restrict__ X, int n_frames) {
     extern __shared__ __align__(16) unsigned char smem[];
-    __shared__ const unsigned char* rows[32];
-    const int lane = threadIdx.x;
-    const size_t nv = (size_t)n_streams * channels;
-    const size_t v0 = (size_t)blockIdx.x * 32;
-    const size_t v = v0 + lane;
-    const bool live = v < nv;
-    const size_t vc = live ? v : nv - 1;
-    const size_t block_bytes = (size_t)P.n * sizeof(typename Ingest<FMT>::raw_t);
-    rows[lane] = static_cast<const unsigned char*>(iq) + (vc / channels) * block_bytes * n_blocks;
-    __syncwarp();
-    TileStreamX<SSB_STAGES> ts = {rows, smem, lane};
-    const int chunks_per_block = (int)(block_bytes / SSB_ROW_BYTES);
-    const int nchunks = chunks_per_block * n_blocks;
+    constexpr int NS = 4 * SsbIngest<FMT>::kPerVec;
+    constexpr int OP = 2 * NS + 4;                    // output tile row pitch (floats)
+    __shared__ __align__(16) float s_out[SSBX_WARPS][32 * OP];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    TileStreamT<SSB_MAIN_STAGES> ts;
+    ts.lane = lane;
+    ts.base = static_cast<const unsigned char*>(iq);
+    ts.row_bytes = (size_t)P.n * sizeof(typename Ingest<FMT>::raw_t);
+    ts.first_row = ((size_t)blockIdx.x * SSBX_WARPS + warp) * 32;
+    ts.last_row = (size_t)n_frames - 1;
+    ts.tile = smem + warp * SSB_MAIN_STAGES * SSB_TILE_BYTES;
+    if (ts.first_row >= (size_t)n_frames) return;
+    const int nchunks = (int)(ts.row_bytes / SSB_ROW_BYTES);
     const float oma = __fsub_rn(1.0f, P.dcAlpha);
-    const uint32_t inc1 = inc1_tab[vc % channels];
-    SsbxLane L = {};
-    L.iz1 = state[vc].rf_z1; L.iz2 = state[vc].rf_z2; L.qz1 = state[vc].pad0; L.qz2 = state[vc].pad1;
-    L.ph1 = (uint32_t)((unsigned long long)inc1 * base_samples);
+    float dcr = 0.0f, dci = 0.0f;
+    float* tile = s_out[warp];
+    constexpr int LPR = 2 * NS / 4, RPI = 32 / LPR;   // lanes per output row, rows per store instruction
     ts.prologue(nchunks);
-    int cb = 0, b = 0;
     for (int c = 0; c < nchunks; c++) {
         ts.advance(c, nchunks);
         __syncwarp();
-        if (cb == 0) {
-            L.dcr = L.dci = 0.0f;
-            if (live) start[v * n_blocks + b] = make_float4(L.iz1, L.iz2, L.qz1, L.qz2);
-        }
         const uint4* row = ts.cur(c);
+        float4* mine = reinterpret_cast<float4*>(tile + lane * OP);
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
-            const uint4 d = row[q];
+        for (int v = 0; v < 4; v++) {
+            const uint4 d = row[v];
+            float o[2 * SsbIngest<FMT>::kPerVec];
 #pragma unroll
             for (int j = 0; j < SsbIngest<FMT>::kPerVec; j++) {
-                float I, Q, yi, yq;
+                float I, Q;
                 SsbIngest<FMT>::get(d, j, I, Q);
-                ssbx_front<TSB>(L, I, Q, P, oma, inc1, yi, yq);
+                dcr = __fadd_rn(__fmul_rn(P.dcAlpha, dcr), __fmul_rn(oma, I));
+                dci = __fadd_rn(__fmul_rn(P.dcAlpha, dci), __fmul_rn(oma, Q));
+                o[2 * j] = __fsub_rn(I, dcr);
+                o[2 * j + 1] = __fsub_rn(Q, dci);
+            }
+#pragma unroll
+            for (int k = 0; k < SsbIngest<FMT>::kPerVec / 2; k++)
+                mine[v * (SsbIngest<FMT>::kPerVec / 2) + k] = make_float4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < LPR; i++) {
+            const int r = i * RPI + lane / LPR, col = lane % LPR;
+            const size_t fr = ts.first_row + r;
+            if (fr <= ts.last_row)
+                *reinterpret_cast<float4*>(reinterpret_cast<float*>(X) + (fr * (size_t)P.n + (size_t)c * NS) * 2 + 4 * col) =
+                    *reinterpret_cast<const float4*>(tile + r * OP + 4 * col);
+        }
+        __syncwarp();
+    }
+}
+
+// ---------------------------------------------------------------- pre-pass 2: NCO + first mix, sample-parallel
+// m = (x_r + j x_i) * exp(-j theta): re = x_r c + x_i s, im = x_i c - x_r s, theta = inc1 * (samples since reset);
+// the expressions and their order are those of oracle/sdr_oracle_ext.c.  One thread = 4 consecutive samples of one
+// (stream, channel); span = n_blocks * n samples per stream in this call.
+template <bool TSB>
+__global__ void __launch_bounds__(256)
+k_ssbx_mix(const float2* __restrict__ X, const uint32_t* __restrict__ inc1_tab, float* __restrict__ M, int channels,
+           size_t span, size_t n_units, unsigned long long base_samples) {
+    const size_t q4 = span / 4;
+    const size_t total = n_units * q4;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const size_t v = idx / q4, k = (idx - v * q4) * 4;
+        const size_t s = v / channels;
+        const uint32_t inc1 = inc1_tab[v % channels];
+        uint32_t ph = (uint32_t)((unsigned long long)inc1 * (base_samples + k));
+        const float4* x4 = reinterpret_cast<const float4*>(X + s * span + k);
+        const float4 a = x4[0], b = x4[1];
+        const float xr[4] = {a.x, a.z, b.x, b.z}, xi[4] = {a.y, a.w, b.y, b.w};
+        float mr[4], mi[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            float c1, s1;
+            nco_cs(ph, c1, s1);
+            ph += inc1;
+            mr[j] = __fadd_rn(__fmul_rn(xr[j], c1), __fmul_rn(xi[j], s1));
+            if (TSB) mi[j] = __fsub_rn(__fmul_rn(xi[j], c1), __fmul_rn(xr[j], s1));
+        }
+        if (TSB) {
+            float4* o = reinterpret_cast<float4*>(M + (v * span + k) * 2);
+            o[0] = make_float4(mr[0], mi[0], mr[1], mi[1]);
+            o[1] = make_float4(mr[2], mi[2], mr[3], mi[3]);
+        } else {
+            *reinterpret_cast<float4*>(M + v * span + k) = make_float4(mr[0], mr[1], mr[2], mr[3]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------- pass 1: the carried IIR2 state, block by block
+// One lane per CHAIN: a (stream, channel) has one (I) or, with true sideband, two (I and Q: two lanes reading the same
+// row of pairs) -- a warp issues in order, so two chains in one lane would queue behind each other's dependent
+// operations.  The lane walks M[v][0 .. n_blocks * n) in order, one 64-byte chunk (16 or 8 samples of its chain) per
+// iteration, the chunk's four shared-memory loads ahead of the arithmetic.
+template <bool TSB>
+__global__ void __launch_bounds__(32)
+k_ssbx_state(const float* __restrict__ M, const __grid_constant__ SsbParams P, float4* __restrict__ start,
+             SsbStreamState* __restrict__ state, size_t n_units, int n_blocks) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ const unsigned char* rows[32];
+    constexpr int E = TSB ? 2 : 1;
+    const int lane = threadIdx.x;
+    const size_t n_chains = n_units * E;
+    const size_t ch = (size_t)blockIdx.x * 32 + lane;
+    const bool live = ch < n_chains;
+    const size_t chc = live ? ch : n_chains - 1;
+    const size_t v = chc / E;
+    const int comp = (int)(chc % E);
+    const size_t block_bytes = (size_t)P.n * E * sizeof(float);
+    rows[lane] = reinterpret_cast<const unsigned char*>(M) + v * block_bytes * n_blocks;
+    __syncwarp();
+    TileStreamX<SSBX_STATE_STAGES> ts = {rows, smem, lane};
+    ts.bind();
+    const int chunks_per_block = (int)(block_bytes / SSB_ROW_BYTES);
+    const int nchunks = chunks_per_block * n_blocks;
+    float z1 = comp ? state[v].pad0 : state[v].rf_z1, z2 = comp ? state[v].pad1 : state[v].rf_z2;
+    float2* start2 = reinterpret_cast<float2*>(start);   // float4 per (unit, block) = (I z1, I z2, Q z1, Q z2)
+    // software pipeline: the registers of chunk c + 1 are loaded while chunk c is in the chain (a load that is only
+    // used in the next iteration cannot sink to its first use, which is where ptxas puts the loads of a chunk otherwise)
+    ts.prologue(nchunks);
+    int cb = 0, b = 0;
+    float4 nx[4];
+    ts.advance(0, nchunks);
+    __syncwarp();
+    {
+        const float4* row = reinterpret_cast<const float4*>(ts.cur(0));
+#pragma unroll
+        for (int q = 0; q < 4; q++) nx[q] = lds128_now(row + q);
+    }
+    __syncwarp();
+    for (int c = 0; c < nchunks; c++) {
+        float4 d[4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) d[q] = nx[q];
+        if (c + 1 < nchunks) {
+            ts.advance(c + 1, nchunks);     // reuses the stage of chunk c, whose values are in registers already
+            __syncwarp();
+            const float4* row = reinterpret_cast<const float4*>(ts.cur(c + 1));
+#pragma unroll
+            for (int q = 0; q < 4; q++) nx[q] = lds128_now(row + q);
+        }
+        if (cb == 0 && live) {
+            start2[(v * n_blocks + b) * 2 + comp] = make_float2(z1, z2);
+            if (!TSB) start2[(v * n_blocks + b) * 2 + 1] = make_float2(0.0f, 0.0f);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            if (TSB) {
+                ssbx_iir(P.rf, comp ? d[q].y : d[q].x, z1, z2);
+                ssbx_iir(P.rf, comp ? d[q].w : d[q].z, z1, z2);
+            } else {
+                ssbx_iir(P.rf, d[q].x, z1, z2); ssbx_iir(P.rf, d[q].y, z1, z2);
+                ssbx_iir(P.rf, d[q].z, z1, z2); ssbx_iir(P.rf, d[q].w, z1, z2);
             }
         }
         __syncwarp();
         if (++cb == chunks_per_block) { cb = 0; b++; }
     }
-    if (live) { state[v].rf_z1 = L.iz1; state[v].rf_z2 = L.iz2; state[v].pad0 = L.qz1; state[v].pad1 = L.qz2; }
-}
-
-// ---------------------------------------------------------------- pass 2
-template <int FMT, int SMAX, bool TSB>
-__global__ void __launch_bounds__(SSBX_WARPS * 32)
-k_ssbx_main(const void* __restrict__ iq, const __grid_constant__ SsbParams P, const float* __restrict__ taps,
-            const uint32_t* __restrict__ inc1_tab, uint32_t inc2, const float4* __restrict__ start,
-            float* __restrict__ a48, int n_streams, int channels, int n_blocks, unsigned long long base_samples) {
-    extern __shared__ __align__(16) unsigned char smem[];
-    __shared__ const unsigned char* rows_all[SSBX_WARPS][32];
-    float* hT = reinterpret_cast<float*>(smem + SSBX_WARPS * SSB_MAIN_STAGES * SSB_TILE_BYTES);
-    for (int i = threadIdx.x; i < P.decim * SMAX; i += SSBX_WARPS * 32) hT[i] = taps[i];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const size_t nvf = (size_t)n_streams * channels * n_blocks;
-    const size_t vf0 = ((size_t)blockIdx.x * SSBX_WARPS + warp) * 32;
-    const size_t vf = vf0 + lane;
-    const bool live = vf < nvf;
-    const size_t vfc = live ? vf : nvf - 1;
-    const size_t v = vfc / n_blocks, b = vfc % n_blocks;
-    const size_t block_bytes = (size_t)P.n * sizeof(typename Ingest<FMT>::raw_t);
-    rows_all[warp][lane] = static_cast<const unsigned char*>(iq) + ((v / channels) * n_blocks + b) * block_bytes;
-    __syncthreads();
-    if (vf0 >= nvf) return;
-    TileStreamX<SSB_MAIN_STAGES> ts = {rows_all[warp], smem + warp * SSB_MAIN_STAGES * SSB_TILE_BYTES, lane};
-    const int nchunks = (int)(block_bytes / SSB_ROW_BYTES);
-    const float oma = __fsub_rn(1.0f, P.dcAlpha);
-    const uint32_t inc1 = inc1_tab[v % channels];
-    const unsigned long long k0 = base_samples + (unsigned long long)b * (unsigned long long)P.n;
-    const float4 s0 = start[vfc];
-    SsbxLane L = {};
-    L.iz1 = s0.x; L.iz2 = s0.y; L.qz1 = s0.z; L.qz2 = s0.w;
-    L.ph1 = (uint32_t)((unsigned long long)inc1 * k0);
-    L.ph2 = (uint32_t)((unsigned long long)inc2 * k0);
-    float gain = 1.0f;
-    const float omFast = __fsub_rn(1.0f, P.agcFast), omSlow = __fsub_rn(1.0f, P.agcSlow);
-    float acc[SMAX];
-#pragma unroll(SMAX <= 16 ? SMAX : 1)
-    for (int s = 0; s < SMAX; s++) acc[s] = 0.0f;
-    const int sLast = (P.nTaps - 1) / P.decim, rLast = (P.nTaps - 1) % P.decim;
-    int r = 0, q = 0;
-    float* out = a48 + vfc * (size_t)P.m;
-
-    ts.prologue(nchunks);
-    for (int c = 0; c < nchunks; c++) {
-        ts.advance(c, nchunks);
-        __syncwarp();
-        const uint4* row = ts.cur(c);
-#pragma unroll
-        for (int vv = 0; vv < 4; vv++) {
-            const uint4 d = row[vv];
-#pragma unroll
-            for (int j = 0; j < SsbIngest<FMT>::kPerVec; j++) {
-                float I, Q, yi, yq;
-                SsbIngest<FMT>::get(d, j, I, Q);
-                ssbx_front<TSB>(L, I, Q, P, oma, inc1, yi, yq);
-                float a;
-                if (TSB) {   // Weaver second mix: Re{(yI + j yQ) exp(+/- j theta2)}, doubled
-                    float c2, s2;
-                    nco_cs(L.ph2, c2, s2);
-                    L.ph2 += inc2;
-                    const float p = __fmul_rn(yi, c2), w = __fmul_rn(yq, s2);
-                    const float u = P.upper ? __fsub_rn(p, w) : __fadd_rn(p, w);
-                    a = __fadd_rn(u, u);
-                } else {
-                    a = P.upper ? __fadd_rn(yi, yi) : __fsub_rn(yi, yi);
-                }
-                const float mag = __fadd_rn(fabsf(a), 1e-8f);
-                const float desired = __fdiv_rn(P.agcTarget, __fadd_rn(__fsqrt_rn(mag), 1e-6f));
-                const bool fast = desired < gain;
-                gain = __fadd_rn(__fmul_rn(gain, fast ? omFast : omSlow),
-                                 __fmul_rn(desired, fast ? P.agcFast : P.agcSlow));
-                float x = __fmul_rn(a, gain);
-                x = x < -1.0f ? -1.0f : (1.0f < x ? 1.0f : x);
-                const float* h = hT + r * SMAX;
-#pragma unroll(SMAX <= 16 ? SMAX : 1)
-                for (int s = 0; s < SMAX; s++) acc[s] = __fadd_rn(acc[s], __fmul_rn(x, h[s]));
-                if (r == rLast) {
-                    const int jo = q - sLast;
-                    if (jo >= 0 && jo < P.m && live) out[jo] = acc[SMAX - 1];
-                }
-                if (++r == P.decim) {
-                    r = 0;
-                    q++;
-#pragma unroll(SMAX <= 16 ? SMAX : 1)
-                    for (int s = SMAX - 1; s > 0; s--) acc[s] = acc[s - 1];
-                    acc[0] = 0.0f;
-                }
-            }
-        }
-        __syncwarp();
+    if (live) {
+        if (comp) { state[v].pad0 = z1; state[v].pad1 = z2; }
+        else { state[v].rf_z1 = z1; state[v].rf_z2 = z2; }
     }
 }
 
-// ---------------------------------------------------------------- pass 2, split (see k_ssb_agc / k_ssb_fir in ssb.cu)
-// The main pass in sweeps over a 64-byte chunk, without the decimator: post-AGC samples go to xagc [vf][n].
-template <int FMT, bool TSB>
+// ---------------------------------------------------------------- pass 2: IIR2 from the recorded state, second mix, AGC
+// One lane per (stream, channel, block).  True sideband: Weaver second mix Re{(yI + j yQ) exp(+/- j theta2)}, doubled;
+// otherwise the reference's demodSSB on {y, y} (USB = y + y, LSB = y - y).  AGC in sweeps (ssb_common.cuh); the
+// post-AGC samples go to xagc [unit][block][n] through a shared-memory tile, k_ssb_fir (ssb.cu) decimates them.
+template <bool TSB, bool CHECK>
 __global__ void __launch_bounds__(SSBX_WARPS * 32)
-k_ssbx_agc(const void* __restrict__ iq, const __grid_constant__ SsbParams P, const uint32_t* __restrict__ inc1_tab,
-           uint32_t inc2, const float4* __restrict__ start, float* __restrict__ xagc, int n_streams, int channels,
-           int n_blocks, unsigned long long base_samples) {
+k_ssbx_agc(const float* __restrict__ M, const __grid_constant__ SsbParams P, uint32_t inc2,
+           const float4* __restrict__ start, float* __restrict__ xagc, size_t n_frames, int n_blocks,
+           unsigned long long base_samples) {
     extern __shared__ __align__(16) unsigned char smem[];
-    constexpr int NS = 4 * SsbIngest<FMT>::kPerVec;
+    constexpr int E = TSB ? 2 : 1, NS = 16 / E;       // samples per 64-byte chunk of M
     constexpr int OP = NS + 4;
     __shared__ const unsigned char* rows_all[SSBX_WARPS][32];
     __shared__ __align__(16) float s_out[SSBX_WARPS][32 * OP];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const size_t nvf = (size_t)n_streams * channels * n_blocks;
     const size_t vf0 = ((size_t)blockIdx.x * SSBX_WARPS + warp) * 32;
     const size_t vf = vf0 + lane;
-    const bool live = vf < nvf;
-    const size_t vfc = live ? vf : nvf - 1;
-    const size_t v = vfc / n_blocks, b = vfc % n_blocks;
-    const size_t block_bytes = (size_t)P.n * sizeof(typename Ingest<FMT>::raw_t);
-    rows_all[warp][lane] = static_cast<const unsigned char*>(iq) + ((v / channels) * n_blocks + b) * block_bytes;
+    const bool live = vf < n_frames;
+    const size_t vfc = live ? vf : n_frames - 1;
+    const size_t b = vfc % n_blocks;
+    const size_t block_bytes = (size_t)P.n * E * sizeof(float);
+    rows_all[warp][lane] = reinterpret_cast<const unsigned char*>(M) + vfc * block_bytes;
     __syncthreads();
-    if (vf0 >= nvf) return;
+    if (vf0 >= n_frames) return;
     TileStreamX<SSB_MAIN_STAGES> ts = {rows_all[warp], smem + warp * SSB_MAIN_STAGES * SSB_TILE_BYTES, lane};
+    ts.bind();
     const int nchunks = (int)(block_bytes / SSB_ROW_BYTES);
-    const float oma = __fsub_rn(1.0f, P.dcAlpha);
-    const uint32_t inc1 = inc1_tab[v % channels];
-    const unsigned long long k0 = base_samples + (unsigned long long)b * (unsigned long long)P.n;
     const float4 s0 = start[vfc];
-    SsbxLane L = {};
-    L.iz1 = s0.x; L.iz2 = s0.y; L.qz1 = s0.z; L.qz2 = s0.w;
-    L.ph1 = (uint32_t)((unsigned long long)inc1 * k0);
-    L.ph2 = (uint32_t)((unsigned long long)inc2 * k0);
+    float iz1 = s0.x, iz2 = s0.y, qz1 = s0.z, qz2 = s0.w;
+    uint32_t ph2 = (uint32_t)((unsigned long long)inc2 * (base_samples + (unsigned long long)b * (unsigned long long)P.n));
     float gain = 1.0f;
     const float omFast = __fsub_rn(1.0f, P.agcFast), omSlow = __fsub_rn(1.0f, P.agcSlow);
-    const bool tgt_ok = ssb_moderate(P.agcTarget);
     float* tile = s_out[warp];
     constexpr int LPR = NS / 4, RPI = 32 / LPR;
-
     ts.prologue(nchunks);
     for (int c = 0; c < nchunks; c++) {
         ts.advance(c, nchunks);
         __syncwarp();
-        const uint4* row = ts.cur(c);
-        float a[NS], des[NS];
+        const float4* row = reinterpret_cast<const float4*>(ts.cur(c));
+        float4 dd[4];
 #pragma unroll
-        for (int vv = 0; vv < 4; vv++) {
-            const uint4 d = row[vv];
+        for (int q = 0; q < 4; q++) dd[q] = lds128_now(row + q);
+        float a[NS];
 #pragma unroll
-            for (int j = 0; j < SsbIngest<FMT>::kPerVec; j++) {
-                float I, Q, yi, yq;
-                SsbIngest<FMT>::get(d, j, I, Q);
-                ssbx_front<TSB>(L, I, Q, P, oma, inc1, yi, yq);
-                float av;
-                if (TSB) {   // Weaver second mix: Re{(yI + j yQ) exp(+/- j theta2)}, doubled
+        for (int q = 0; q < 4; q++) {
+            const float4 d = dd[q];
+            if (TSB) {
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const float yi = ssbx_iir(P.rf, h ? d.z : d.x, iz1, iz2);
+                    const float yq = ssbx_iir(P.rf, h ? d.w : d.y, qz1, qz2);
                     float c2, s2;
-                    nco_cs(L.ph2, c2, s2);
-                    L.ph2 += inc2;
+                    nco_cs(ph2, c2, s2);
+                    ph2 += inc2;
                     const float p = __fmul_rn(yi, c2), w = __fmul_rn(yq, s2);
                     const float u = P.upper ? __fsub_rn(p, w) : __fadd_rn(p, w);
-                    av = __fadd_rn(u, u);
-                } else {
-                    av = P.upper ? __fadd_rn(yi, yi) : __fsub_rn(yi, yi);
+                    a[2 * q + h] = __fadd_rn(u, u);
                 }
-                a[vv * SsbIngest<FMT>::kPerVec + j] = av;
+            } else {
+                const float m4[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+                for (int h = 0; h < 4; h++) {
+                    const float y = ssbx_iir(P.rf, m4[h], iz1, iz2);
+                    a[4 * q + h] = P.upper ? __fadd_rn(y, y) : __fsub_rn(y, y);
+                }
             }
         }
-        bool ok = tgt_ok;
-#pragma unroll
-        for (int i = 0; i < NS; i++) {
-            const float mag = __fadd_rn(fabsf(a[i]), 1e-8f);
-            ok = ok && ssb_moderate(mag);
-            des[i] = ssb_div_rn(P.agcTarget, __fadd_rn(ssb_sqrt_rn(mag), 1e-6f));
-        }
-        if (!ok) {
-#pragma unroll 1
-            for (int i = 0; i < NS; i++) {
-                float ai = 0.0f;
-#pragma unroll
-                for (int k = 0; k < NS; k++) if (k == i) ai = a[k];
-                const float mag = __fadd_rn(fabsf(ai), 1e-8f);
-                const float dsr = __fdiv_rn(P.agcTarget, __fadd_rn(__fsqrt_rn(mag), 1e-6f));
-#pragma unroll
-                for (int k = 0; k < NS; k++) if (k == i) des[k] = dsr;
-            }
-        }
-#pragma unroll
-        for (int i = 0; i < NS; i++) {
-            const bool fast = des[i] < gain;
-            gain = __fadd_rn(__fmul_rn(gain, fast ? omFast : omSlow), __fmul_rn(des[i], fast ? P.agcFast : P.agcSlow));
-            const float x = __fmul_rn(a[i], gain);
-            a[i] = x < -1.0f ? -1.0f : (1.0f < x ? 1.0f : x);
-        }
+        ssb_agc_sweeps<NS, CHECK>(a, P, omFast, omSlow, gain);
         float4* mine = reinterpret_cast<float4*>(tile + lane * OP);
 #pragma unroll
         for (int k = 0; k < LPR; k++) mine[k] = make_float4(a[4 * k], a[4 * k + 1], a[4 * k + 2], a[4 * k + 3]);
@@ -339,7 +347,7 @@ k_ssbx_agc(const void* __restrict__ iq, const __grid_constant__ SsbParams P, con
         for (int i = 0; i < LPR; i++) {
             const int r = i * RPI + lane / LPR, col = lane % LPR;
             const size_t fr = vf0 + r;
-            if (fr < nvf)
+            if (fr < n_frames)
                 *reinterpret_cast<float4*>(xagc + fr * (size_t)P.n + (size_t)c * NS + 4 * col) =
                     *reinterpret_cast<const float4*>(tile + r * OP + 4 * col);
         }
@@ -348,67 +356,54 @@ k_ssbx_agc(const void* __restrict__ iq, const __grid_constant__ SsbParams P, con
 }
 
 // ---------------------------------------------------------------- launch
-template <int FMT, int SMAX, bool TSB>
-static cudaError_t launch_mainx_t(const void* iq, const SsbParams& P, const float* taps, const uint32_t* inc1,
-                                  uint32_t inc2, const float4* start, float* a48, int S, int C, int B,
-                                  unsigned long long base, cudaStream_t st) {
-    const size_t smem = (size_t)SSBX_WARPS * SSB_MAIN_STAGES * SSB_TILE_BYTES + (size_t)P.decim * SMAX * sizeof(float);
-    cudaError_t e = cudaFuncSetAttribute(k_ssbx_main<FMT, SMAX, TSB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    const size_t nvf = (size_t)S * C * B;
-    const int grid = (int)((nvf + SSBX_WARPS * 32 - 1) / (SSBX_WARPS * 32));
-    k_ssbx_main<FMT, SMAX, TSB><<<grid, SSBX_WARPS * 32, smem, st>>>(iq, P, taps, inc1, inc2, start, a48, S, C, B, base);
-    return cudaGetLastError();
-}
-
-template <int FMT, bool TSB>
-static cudaError_t launch_mainx_f(int smax, const void* iq, const SsbParams& P, const float* taps, const uint32_t* inc1,
-                                  uint32_t inc2, const float4* start, float* a48, int S, int C, int B,
-                                  unsigned long long base, cudaStream_t st) {
-    switch (smax) {
-        case 1: return launch_mainx_t<FMT, 1, TSB>(iq, P, taps, inc1, inc2, start, a48, S, C, B, base, st);
-        case 2: return launch_mainx_t<FMT, 2, TSB>(iq, P, taps, inc1, inc2, start, a48, S, C, B, base, st);
-        case 4: return launch_mainx_t<FMT, 4, TSB>(iq, P, taps, inc1, inc2, start, a48, S, C, B, base, st);
-        case 8: return launch_mainx_t<FMT, 8, TSB>(iq, P, taps, inc1, inc2, start, a48, S, C, B, base, st);
-        case 16: return launch_mainx_t<FMT, 16, TSB>(iq, P, taps, inc1, inc2, start, a48, S, C, B, base, st);
-        default: return launch_mainx_t<FMT, 256, TSB>(iq, P, taps, inc1, inc2, start, a48, S, C, B, base, st);
-    }
+// Scratch (all in `d_work`, floats): X = S * B * n * 2, then M = S * C * B * n * (1 or 2); d_agc = S * C * B * n.
+size_t ssb_ext_work_floats(int n, int S, int C, int B, int true_sideband) {
+    return (size_t)S * B * n * 2 + (size_t)S * C * B * n * (true_sideband ? 2 : 1);
 }
 
 template <int FMT, bool TSB>
 static cudaError_t launch_ssbx_f(const void* iq, const SsbParams& P, const float* d_taps, const uint32_t* d_inc1,
                                  uint32_t inc2, float4* d_start, SsbStreamState* d_state, float* d_a48, float* d_agc,
-                                 int S, int C, int B, unsigned long long base, cudaStream_t st) {
-    const size_t nv = (size_t)S * C;
-    k_ssbx_state<FMT, TSB><<<(unsigned)((nv + 31) / 32), 32, SSB_STAGES * SSB_TILE_BYTES, st>>>(iq, P, d_inc1, d_start, d_state,
-                                                                                      S, C, B, base);
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
-    const size_t nvf = nv * B;
-    if (d_agc && nvf < (1ull << 31)) {
-        const int grid = (int)((nvf + SSBX_WARPS * 32 - 1) / (SSBX_WARPS * 32));
-        const size_t asmem = (size_t)SSBX_WARPS * SSB_MAIN_STAGES * SSB_TILE_BYTES;
-        if ((e = cudaFuncSetAttribute(k_ssbx_agc<FMT, TSB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asmem)) != cudaSuccess)
-            return e;
-        k_ssbx_agc<FMT, TSB><<<grid, SSBX_WARPS * 32, asmem, st>>>(
-            iq, P, d_inc1, inc2, d_start, d_agc, S, C, B, base);
-        if ((e = cudaGetLastError()) != cudaSuccess) return e;
-        return launch_ssb_fir(d_agc, d_taps, d_a48, P, (int)nvf, st);
-    }
-    return launch_mainx_f<FMT, TSB>(ssb_smax(P), iq, P, d_taps, d_inc1, inc2, d_start, d_a48, S, C, B, base, st);
+                                 float* d_work, int S, int C, int B, unsigned long long base, cudaStream_t st) {
+    const size_t nv = (size_t)S * C, nvf = nv * B, span = (size_t)B * P.n;
+    float2* X = reinterpret_cast<float2*>(d_work);
+    float* M = d_work + (size_t)S * span * 2;
+    cudaError_t e;
+    const size_t tsmem = (size_t)SSBX_WARPS * SSB_MAIN_STAGES * SSB_TILE_BYTES;
+    if ((e = cudaFuncSetAttribute(k_ssbx_dc<FMT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem)) != cudaSuccess) return e;
+    const int frames = S * B;
+    k_ssbx_dc<FMT><<<(frames + SSBX_WARPS * 32 - 1) / (SSBX_WARPS * 32), SSBX_WARPS * 32, tsmem, st>>>(iq, P, X, frames);
+    const size_t threads = nv * (span / 4);
+    const unsigned mgrid = (unsigned)(threads / 256 + 1 < 148u * 32u ? threads / 256 + 1 : 148u * 32u);
+    k_ssbx_mix<TSB><<<mgrid, 256, 0, st>>>(X, d_inc1, M, C, span, nv, base);
+    const size_t chains = nv * (TSB ? 2 : 1);
+    const size_t ssmem = (size_t)SSBX_STATE_STAGES * SSB_TILE_BYTES;
+    if ((e = cudaFuncSetAttribute(k_ssbx_state<TSB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssmem)) != cudaSuccess) return e;
+    k_ssbx_state<TSB><<<(unsigned)((chains + 31) / 32), 32, ssmem, st>>>(M, P, d_start, d_state, nv, B);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (P.m <= 0) return cudaSuccess;
+    constexpr bool CHECK = FMT == FMT_CF32;
+    if ((e = cudaFuncSetAttribute(k_ssbx_agc<TSB, CHECK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem)) != cudaSuccess) return e;
+    const unsigned agrid = (unsigned)((nvf + SSBX_WARPS * 32 - 1) / (SSBX_WARPS * 32));
+    k_ssbx_agc<TSB, CHECK><<<agrid, SSBX_WARPS * 32, tsmem, st>>>(M, P, inc2, d_start, d_agc, nvf, B, base);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    return launch_ssb_fir(d_agc, d_taps, d_a48, P, (int)nvf, st);
 }
 
+// d_agc: [S * C * B][n] floats, d_work: ssb_ext_work_floats() floats -- both required
 cudaError_t launch_ssb_ext(int fmt, const void* iq, const SsbParams& P, const float* d_taps, const uint32_t* d_inc1,
                            uint32_t inc2, int true_sideband, float4* d_start, SsbStreamState* d_state, float* d_a48,
-                           int16_t* d_pcm, float* d_agc, int n_streams, int channels, int n_blocks,
+                           int16_t* d_pcm, float* d_agc, float* d_work, int n_streams, int channels, int n_blocks,
                            unsigned long long base_samples, cudaStream_t st, int* launches) {
     if (n_streams <= 0 || channels <= 0 || n_blocks <= 0) return cudaSuccess;
+    if (!d_agc || !d_work) return cudaErrorMemoryAllocation;
+    if ((size_t)n_streams * channels * n_blocks >= (1ull << 31)) return cudaErrorInvalidValue;
     cudaError_t e;
 #define SDRB_X(F)                                                                                                      \
-    (true_sideband ? launch_ssbx_f<F, true>(iq, P, d_taps, d_inc1, inc2, d_start, d_state, d_a48, d_agc, n_streams, channels, \
-                                            n_blocks, base_samples, st)                                                \
-                   : launch_ssbx_f<F, false>(iq, P, d_taps, d_inc1, inc2, d_start, d_state, d_a48, d_agc, n_streams, channels, \
-                                             n_blocks, base_samples, st))
+    (true_sideband ? launch_ssbx_f<F, true>(iq, P, d_taps, d_inc1, inc2, d_start, d_state, d_a48, d_agc, d_work, n_streams, \
+                                            channels, n_blocks, base_samples, st)                                      \
+                   : launch_ssbx_f<F, false>(iq, P, d_taps, d_inc1, inc2, d_start, d_state, d_a48, d_agc, d_work, n_streams, \
+                                             channels, n_blocks, base_samples, st))
     switch (fmt) {
         case FMT_CU8: e = SDRB_X(FMT_CU8); break;
         case FMT_CS16: e = SDRB_X(FMT_CS16); break;
@@ -417,7 +412,7 @@ cudaError_t launch_ssb_ext(int fmt, const void* iq, const SsbParams& P, const fl
     }
 #undef SDRB_X
     if (e != cudaSuccess) return e;
-    if (launches) *launches += (d_agc && P.m > 0) ? 3 : 2;
+    if (launches) *launches += P.m > 0 ? 5 : 3;
     if (P.m > 0) {
         e = launch_ssb_audio(d_a48, P, d_state, d_pcm, n_streams * channels, n_blocks, st);
         if (launches) (*launches)++;
