@@ -258,6 +258,34 @@ int  sdrb_airspy_redone_chunks(sdrb_ctx* ctx, uint64_t* out);
  * to readStream as CF32.  Synchronises. */
 int  sdrb_get_airspy_iq(sdrb_ctx* ctx, float* host_out, size_t capacity_floats);
 
+/* ---- allocation-free estimator ------------------------------------------ */
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The frame-local part of
+ * evaluateSignalStrength -- what sdrb_process(SDRB_STAGE_FFT) computes per reading before the per-stream tracker --
+ * over n_frames caller-owned DEVICE spectra d_power[n_frames][samples_per_reading] (linear, fft-shifted, e.g. from
+ * sdrb_power_device), into caller-owned DEVICE records d_out[n_frames], on `cuda_stream` (NULL = the default stream)
+ * of `device`.  Needs no context and calls no cudaMalloc / cudaFree: the scratch the kernels need lives in a static
+ * device array of about 0.9 MB that every GPU loading the library holds until exit.
+ * Limits: n_frames <= SDRB_NOALLOC_MAX_FRAMES, and a focus range whose pooled noise bins fit the estimator's
+ * shared-memory pool (8192 bins per frame; the defaults pool 328) -- beyond either the call fails with
+ * SDRB_ERR_ARG / SDRB_ERR_UNSUPPORTED and a message in sdrb_last_error(NULL).
+ * Every call shares the array: calls that overlap on the GPU (two streams, two threads) race; serialise them.
+ * Asynchronous: d_out is valid once the stream has reached the end of the call's work. */
+#define SDRB_NOALLOC_MAX_FRAMES 4096
+typedef struct sdrb_frame_estimate {
+    float absPeakDb, signalPowerDb;
+    float meanSnrDb, meanSnrSigma;
+    float perBinMean, peakAboveNoiseMeanDb;
+    float maxBinSnrDb, maxBinSnrSigma;
+    float best1kHzSnrDb, best1kHzSnrSigma;
+    int32_t best1kStart;   /* first bin of the best 1 kHz window, -1 when there is none */
+    int32_t peakBin;       /* arg-max bin of the focus band (spectrum index), -1 when the focus band is empty */
+    int32_t valid;         /* at least two reference windows: the SNR fields are meaningful */
+    int32_t reserved;
+} sdrb_frame_estimate;
+int  sdrb_estimate_noalloc(int device, uint32_t sample_rate, int samples_per_reading, int focus_khz,
+                           const float* d_power, int n_frames, sdrb_frame_estimate* d_out, void* cuda_stream);
+
 /* ---- per-stream state (checkpoint / resume) ----------------------------- */
 /* Opaque blob: three biquad states, tracking memory, detection ring, frame counter.  The pulse detectors'
  * histories and the Airspy converter state are NOT part of the blob: they restart with sdrb_configure /

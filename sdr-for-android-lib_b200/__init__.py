@@ -8,7 +8,7 @@ raises if the library has not been built.
 from .binding import (  # noqa: F401
     Config, FrameResult, Plan, Context, SdrbError, lib, lib_path, plan_config, synth_host,
     CU8, CS16, CF32, RU16, STAGE_FFT, STAGE_SSB, STAGE_SPECTRAL_PULSE, STAGE_AUDIO_PULSE, format_bytes, format_dtype,
-    POWER_LINEAR_F32, POWER_DB_F32, POWER_DB_F16,
+    POWER_LINEAR_F32, POWER_DB_F32, POWER_DB_F16, FrameEstimate, ESTIMATE_DTYPE, NOALLOC_MAX_FRAMES, estimate_noalloc,
     RESULT_DTYPE, PULSE_DTYPE, PulseResult, AudioPulseConfig, audio_pulse_config_default,
 )
 from .sharding import shard_streams, gather_records, strongest_peak  # noqa: F401

@@ -68,6 +68,24 @@ class PulseResult(C.Structure):
 PULSE_DTYPE = np.dtype(PulseResult)
 
 
+class FrameEstimate(C.Structure):
+    """sdrb_frame_estimate: the frame-local estimator record of sdrb_estimate_noalloc."""
+    _fields_ = [(k, C.c_float) for k in ("absPeakDb", "signalPowerDb", "meanSnrDb", "meanSnrSigma", "perBinMean",
+                                         "peakAboveNoiseMeanDb", "maxBinSnrDb", "maxBinSnrSigma", "best1kHzSnrDb",
+                                         "best1kHzSnrSigma")] + \
+               [(k, C.c_int32) for k in ("best1kStart", "peakBin", "valid", "reserved")]
+
+
+ESTIMATE_DTYPE = np.dtype(FrameEstimate)
+NOALLOC_MAX_FRAMES = 4096
+
+
+def estimate_noalloc(device, sample_rate, n, focus_khz, d_power_ptr, n_frames, d_out_ptr, stream_ptr=0):
+    """sdrb_estimate_noalloc: device pointers in, nothing allocated; raises SdrbError on a rejected call."""
+    _check(lib.sdrb_estimate_noalloc(device, sample_rate, n, focus_khz, C.c_void_p(d_power_ptr), n_frames,
+                                     C.c_void_p(d_out_ptr), C.c_void_p(stream_ptr)))
+
+
 class Plan(C.Structure):
     _fields_ = [("n", C.c_int32), ("focusLo", C.c_int32), ("focusHi", C.c_int32), ("focusLen", C.c_int32),
                 ("winBins1k", C.c_int32), ("nWin", C.c_int32), ("nBottom", C.c_int32),
@@ -111,6 +129,7 @@ EXPORTS = {
     "sdrb_get_power_all": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "sdrb_pcm_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "sdrb_get_pcm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    "sdrb_estimate_noalloc": (C.c_int, [C.c_int, C.c_uint32, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "sdrb_state_bytes": (C.c_size_t, [C.c_void_p]),
     "sdrb_save_state": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "sdrb_load_state": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),

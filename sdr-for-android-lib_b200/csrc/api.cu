@@ -161,6 +161,8 @@ struct sdrb_ctx {
     int host_chunks = 8;        // SDRB_HOST_CHUNKS: pipeline depth of sdrb_process_host
 };
 
+namespace sdrb { void set_global_error(const char* text) { g_create_error = text ? text : ""; } }
+
 static int fail(sdrb_ctx* c, int code, const char* fmt, ...) {
     char buf[512];
     va_list ap;

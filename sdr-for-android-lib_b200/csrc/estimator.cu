@@ -541,3 +541,85 @@ cudaError_t launch_power_view(const float* power, void* out, size_t count, int f
 }
 
 }  // namespace sdrb
+
+// ---------------------------------------------------------------- allocation-free estimator (sdrb_estimate_noalloc)
+// No counterpart in the reference: added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The frame-local part of
+// evaluateSignalStrength (k_band_scan + k_estimator above, unchanged) over caller-owned device spectra, with the
+// scratch those kernels need -- the bin geometry and the per-frame band statistics that pass from one kernel to the
+// other -- in a file-scope device array instead of a cudaMalloc'ed buffer.  Every GPU that loads the library holds the
+// array (about 0.9 MB) until exit.  Every call shares it: nothing in it has to start at zero (the geometry and every
+// band statistic a call reads are written by that call first), but two calls that overlap on the GPU race on it.
+#include <cstdio>
+#include <mutex>
+
+#include "host_design.h"
+
+namespace {
+constexpr size_t kNoAllocGeoBytes = 1024;   // EstGeometry at offset 0, band statistics behind it
+constexpr size_t kNoAllocBandBytes = (size_t)SDRB_NOALLOC_MAX_FRAMES * sdrb::EST_MAX_BANDS * sizeof(sdrb::BandStat);
+static_assert(sizeof(sdrb::EstGeometry) <= kNoAllocGeoBytes, "geometry does not fit its slot");
+static_assert(sizeof(sdrb_frame_estimate) == sizeof(sdrb::FrameLocal), "sdrb_frame_estimate mirrors FrameLocal");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocGeoBytes + kNoAllocBandBytes];
+
+// the geometry arrives as a kernel parameter and is written by device code, which can name the array directly:
+// no host-to-device copy from pageable memory, nothing allocated
+__global__ void k_noalloc_put_geometry(const __grid_constant__ sdrb::EstGeometry g) {
+    const int* src = reinterpret_cast<const int*>(&g);
+    int* dst = reinterpret_cast<int*>(g_noalloc_scratch);
+    for (int i = threadIdx.x; i < (int)(sizeof(sdrb::EstGeometry) / 4); i += blockDim.x) dst[i] = src[i];
+}
+
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address every kernel is given
+// comes from cudaGetSymbolAddress, once per device, with that device current.
+constexpr int kNoAllocMaxDevices = 64;
+unsigned char* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+std::mutex g_noalloc_mu;
+}  // namespace
+
+extern "C" int sdrb_estimate_noalloc(int device, uint32_t sample_rate, int samples_per_reading, int focus_khz,
+                                     const float* d_power, int n_frames, sdrb_frame_estimate* d_out, void* cuda_stream) {
+    using namespace sdrb;
+    char msg[256];
+    auto bad = [&](int code, const char* text) { set_global_error(text); return code; };
+    if (device < 0 || device >= kNoAllocMaxDevices) return bad(SDRB_ERR_ARG, "sdrb_estimate_noalloc: device out of range [0, 64)");
+    if (!d_power || !d_out) return bad(SDRB_ERR_ARG, "sdrb_estimate_noalloc: d_power / d_out is NULL");
+    if (sample_rate == 0 || samples_per_reading < 1) return bad(SDRB_ERR_ARG, "sdrb_estimate_noalloc: sample_rate and samples_per_reading must be positive");
+    if (n_frames < 1 || n_frames > SDRB_NOALLOC_MAX_FRAMES) {
+        snprintf(msg, sizeof msg, "sdrb_estimate_noalloc: n_frames %d outside [1, %d] (SDRB_NOALLOC_MAX_FRAMES: the static scratch "
+                                  "holds that many frames; split the batch or use sdrb_process)", n_frames, SDRB_NOALLOC_MAX_FRAMES);
+        return bad(SDRB_ERR_ARG, msg);
+    }
+    EstGeometry g;
+    design_geometry(sample_rate, samples_per_reading, focus_khz, g);
+    if (pooled_cap_of(g) > EST_SMEM_POOL_FLOATS) {
+        snprintf(msg, sizeof msg, "sdrb_estimate_noalloc: focus range %d kHz pools %d bins per frame; above %d the estimator needs a "
+                                  "per-frame global scratch that the static array does not hold (use sdrb_process)",
+                 focus_khz, pooled_cap_of(g), EST_SMEM_POOL_FLOATS);
+        return bad(SDRB_ERR_UNSUPPORTED, msg);
+    }
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return bad(SDRB_ERR_CUDA, cudaGetErrorString(e));
+    unsigned char* base;
+    {
+        std::lock_guard<std::mutex> lock(g_noalloc_mu);
+        if (!g_noalloc_ptr[device]) {   // set-up, once per device, with that device current
+            unsigned char* ptr = nullptr;
+            if ((e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch)) != cudaSuccess || !ptr ||
+                (e = estimator_prepare()) != cudaSuccess) {
+                snprintf(msg, sizeof msg, "sdrb_estimate_noalloc: set-up on device %d failed: %s", device, cudaGetErrorString(e));
+                return bad(SDRB_ERR_CUDA, msg);
+            }
+            g_noalloc_ptr[device] = ptr;
+        }
+        base = g_noalloc_ptr[device];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    k_noalloc_put_geometry<<<1, 64, 0, st>>>(g);
+    if ((e = cudaGetLastError()) == cudaSuccess)
+        e = launch_estimator(d_power, reinterpret_cast<const EstGeometry*>(base), g, reinterpret_cast<FrameLocal*>(d_out),
+                             reinterpret_cast<float*>(base + kNoAllocGeoBytes), 0, SDRB_NOALLOC_MAX_FRAMES, n_frames, st);
+    if (e != cudaSuccess) return bad(SDRB_ERR_CUDA, cudaGetErrorString(e));
+    return SDRB_OK;
+}
+

@@ -114,6 +114,9 @@ struct TraceSink {
 extern thread_local TraceSink* g_trace;
 inline void trace_mark(const char* name, cudaStream_t st) { if (g_trace) g_trace->mark(name, st); }
 
+// text for sdrb_last_error(NULL) from entry points that have no context (api.cu)
+void set_global_error(const char* text);
+
 // ---------------------------------------------------------------- launchers
 // airspy.cu : raw 12-bit real samples (uint16, 2 per complex output) -> cf32 [streams][n_real/2]
 cudaError_t launch_airspy_front(const uint16_t* d_raw, AirspyStreamState* d_state, float* d_T, cpx* d_iq, float* d_work,
