@@ -128,7 +128,7 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
         cpx v[32];
         if (kStaged) { mbar_wait(bar, parity); parity ^= 1u; f2_phase1_load<FMT>(t, stage, v); }
         else f2_phase1_load<FMT>(t, in + (size_t)f * F2_N, v);
-        fft32(v);
+        fft_dit<5>(v);
         for (;;) {
             __syncthreads();  // E is free (previous phase 3 has read it) and the stage has been consumed
             if (t == 0) {
@@ -148,7 +148,7 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
             if (kStaged) { mbar_wait(bar, parity); parity ^= 1u; f2_phase1_load<FMT>(t, stage, v); }
             else f2_phase1_load<FMT>(t, in + (size_t)fn * F2_N, v);
             f2_phase3(t, E, F2DevTw(), out + (size_t)f * F2_N);
-            fft32(v);
+            fft_dit<5>(v);
             f = fn;
         }
         f2_phase3(t, E, F2DevTw(), out + (size_t)f * F2_N);
@@ -163,7 +163,7 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
             f2_phase1_load<FMT>(t, in + (size_t)f * F2_N, v);
         }
         if (FRONT) f2_front<FRONT>(t, v, win, red);
-        fft32(v);
+        fft_dit<5>(v);
         __syncthreads();  // E is free (previous phase 3 has read it) and the stage has been consumed
         if (t == 0) {
             const int nx = ticket ? (int)gridDim.x + atomicAdd(ticket, 1) : f + (int)gridDim.x;

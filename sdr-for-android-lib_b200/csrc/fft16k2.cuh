@@ -13,11 +13,14 @@
 // W_N^(t 2^j) by a product tree (depth <= 4), which costs fewer shared-memory wavefronts and no
 // more FP32 work than a two-table product.
 //
+// The register codelets are the decimation-in-time, FMA-form ones of fft_dit.cuh (fft_dit<5>, fft_dit<4>); the
+// decimation-in-frequency fft32 below stays for the four-step kernels (fft_big.cuh).
 // The phase functions are __host__ __device__ so the CPU simulator can run them thread by thread.
 #pragma once
 #include <stdint.h>
 
 #include "fft_core.cuh"
+#include "fft_dit.cuh"
 
 namespace sdrb {
 
@@ -113,14 +116,14 @@ struct Ingest2<FMT_CF32> {
 
 SDRB_HD int f2_slot(int plane, int row, int c) { return plane * F2_PITCH + row * 16 + c; }
 
-// ---- phase 1: load + convert, then DFT32 over a and twiddle.  v[slot32(ka)] holds the result.
+// ---- phase 1: load + convert, then DFT32 over a and twiddle.  v[dit_slot<5>(ka)] holds the result.
 template <int FMT>
 SDRB_HD void f2_phase1_load(int t, const typename Ingest2<FMT>::raw_t* in, cpx* v) {
 #pragma unroll
     for (int a = 0; a < 32; a++) v[a] = Ingest2<FMT>::cvt(in[512 * a + t]);
 }
 SDRB_HD void f2_phase1_compute(int t, const cpx* TP, cpx* v) {
-    fft32(v);
+    fft_dit<5>(v);
     // W_N^(t ka) from W_N^(t 2^j): w[k] = w[k with lowest set bit cleared] * P[ctz k]
     cpx P[5];
 #pragma unroll
@@ -131,7 +134,7 @@ SDRB_HD void f2_phase1_compute(int t, const cpx* TP, cpx* v) {
         const int low = k & (-k);
         const int j = low == 1 ? 0 : (low == 2 ? 1 : (low == 4 ? 2 : (low == 8 ? 3 : 4)));
         w[k] = (k == low) ? P[j] : cmul(w[k - low], P[j]);
-        v[slot32(k)] = cmul(v[slot32(k)], w[k]);
+        v[dit_slot<5>(k)] = cmul(v[dit_slot<5>(k)], w[k]);
     }
 }
 // The same twiddle pass with the exchange store folded in: each value is stored as soon as it is final, so the
@@ -147,7 +150,7 @@ SDRB_HD void f2_phase1_twiddle_store(int t, const cpx* TP, cpx* v, cpx* E) {
         const int low = k & (-k);
         const int j = low == 1 ? 0 : (low == 2 ? 1 : (low == 4 ? 2 : (low == 8 ? 3 : 4)));
         w[k] = (k == low) ? P[j] : cmul(w[k - low], P[j]);
-        E[k * F2_PITCH + t] = cmul(v[slot32(k)], w[k]);
+        E[k * F2_PITCH + t] = cmul(v[dit_slot<5>(k)], w[k]);
     }
 }
 template <int FMT>
@@ -157,7 +160,7 @@ SDRB_HD void f2_phase1(int t, const typename Ingest2<FMT>::raw_t* in, const cpx*
 }
 SDRB_HD void f2_phase1_store(int t, cpx* E, const cpx* v) {
 #pragma unroll
-    for (int k = 0; k < 32; k++) E[k * F2_PITCH + t] = v[slot32(k)];
+    for (int k = 0; k < 32; k++) E[k * F2_PITCH + t] = v[dit_slot<5>(k)];
 }
 
 // ---- phase 2: DFT32 over b for (ka, c), in place (its twiddle W_512^(c kb) is applied by phase 3 on load)
@@ -167,9 +170,9 @@ SDRB_HD void f2_phase2(int t, cpx* E) {
     cpx v[32];
 #pragma unroll
     for (int b = 0; b < 32; b++) v[b] = base[b * 16];
-    fft32(v);
+    fft_dit<5>(v);
 #pragma unroll
-    for (int k = 0; k < 32; k++) base[k * 16] = v[slot32(k)];
+    for (int k = 0; k < 32; k++) base[k * 16] = v[dit_slot<5>(k)];
 }
 
 // ---- phase 3: twiddle W_512^(c kb) on load (kb is uniform over a warp: the device functor reads the
@@ -186,11 +189,11 @@ SDRB_HD void f2_phase3(int t, const cpx* E, TW tw, float* __restrict__ out) {
         v[0] = base[0];
 #pragma unroll
         for (int c = 1; c < 16; c++) v[c] = cmul(base[c], tw(kb, c));
-        fft16(v);
+        fft_dit<4>(v);
         const int k0 = ka + 32 * kb;
 #pragma unroll
         for (int kc = 0; kc < 16; kc++) {
-            const cpx x = v[rev16(kc)];
+            const cpx x = v[dit_slot<4>(kc)];
             // re*re + im*im (src/dsp/fft_process.cpp:85); bin k lands at (k + N/2) mod N (:92-97)
             out[(k0 + 1024 * kc + 8192) & 16383] = x.x * x.x + x.y * x.y;
         }

@@ -67,7 +67,7 @@ int main() {
         for (int t = 0; t < F2_THREADS; t++) {
             cpx v[32];
             f2_phase1_load<FMT_CU8>(t, raw.data(), v);   // the kernel's sequence: load, DFT32, twiddle + store
-            fft32(v);
+            fft_dit<5>(v);
             f2_phase1_twiddle_store(t, TP, v, E2.data());
         }
         for (int t = 0; t < F2_THREADS; t++) f2_phase2(t, E2.data());
