@@ -47,7 +47,11 @@ struct EventTrace : sdrb::TraceSink {
 };
 
 constexpr size_t kGenericScratchBytes = 256u << 20;  // per ping-pong buffer of the generic FFT
-constexpr size_t kFourStepL2Bytes = 96u << 20;       // four-step intermediate kept within the 126 MB L2
+// Four-step intermediate per launch pair.  Round 1 kept it within 96 MB "so that it stays in L2"; ncu showed it did not
+// (kernel B read 97 MB per group from DRAM, 16 % L2 hits) and a sweep on the B200 is monotonic in the other direction:
+// 24 MB 0.99 ms, 96 MB 0.665 ms, 384 MB 0.603 ms, whole batch 0.600 ms (256 x 8 x 65536 cs16); 1M points 0.608 -> 0.491 ms.
+// Fewer, longer launches win (tails and launch gaps), so the cap is only there to bound the scratch.  SDRB_FB_L2_MB overrides.
+constexpr size_t kFourStepL2Bytes = 1024u << 20;
 
 struct StateBlobHeader {
     uint32_t magic, version;
@@ -588,7 +592,9 @@ static int ensure_fft_buffers(sdrb_ctx* ctx) {
         const std::vector<cpx> tb = n == 65536 ? make_fb_tables<16>() : make_fb_tables<32>();
         CK(cudaMalloc(&ctx->d_fb_tables, tb.size() * sizeof(cpx)));
         CK(cudaMemcpy(ctx->d_fb_tables, tb.data(), tb.size() * sizeof(cpx), cudaMemcpyHostToDevice));
-        size_t group = kFourStepL2Bytes / ((size_t)n * sizeof(cpx));
+        size_t l2_bytes = kFourStepL2Bytes;
+        if (const char* e = getenv("SDRB_FB_L2_MB")) { const long mb = atol(e); if (mb > 0) l2_bytes = (size_t)mb << 20; }
+        size_t group = l2_bytes / ((size_t)n * sizeof(cpx));
         if (group < 1) group = 1;
         if (group > frames) group = frames;
         if (group < frames) group = (size_t)fft_big_best_group(n, (int)group);

@@ -75,7 +75,7 @@ constexpr int SSBX_WARPS = 4;
 // of arithmetic on it (8 or 16 float samples per chain and chunk, against 32 for u8 input in ssb.cu): with eight stages
 // the 14 KB in flight per SM did not cover the DRAM round trip and the walk ran at ~336 cycles per chunk whatever the
 // chunk held (measured: 41 cycles per sample without, 62 with true sideband, against a 20-cycle chain).
-constexpr int SSBX_STATE_STAGES = 24;
+constexpr int SSBX_STATE_STAGES = 32;   // a power of two: the stage index is a mask, not a division (80 KiB)
 
 // A 16-byte shared-memory load that stays where it is written: left to the compiler, the loads of an iteration sink
 // to their first use and the single warp of a state-pass CTA then waits a shared-memory round trip every few samples
@@ -223,11 +223,13 @@ k_ssbx_state(const float* __restrict__ M, const __grid_constant__ SsbParams P, f
     const int chunks_per_block = (int)(block_bytes / SSB_ROW_BYTES);
     const int nchunks = chunks_per_block * n_blocks;
     float z1 = comp ? state[v].pad0 : state[v].rf_z1, z2 = comp ? state[v].pad1 : state[v].rf_z2;
-    float2* start2 = reinterpret_cast<float2*>(start);   // float4 per (unit, block) = (I z1, I z2, Q z1, Q z2)
+    // float4 per (unit, block) = (I z1, I z2, Q z1, Q z2); the pointer walks along: fetching `start` from the constant
+    // bank and forming the address under a predicate cost ~40 cycles in every chunk (ncu), stored or not
+    float2* sp = reinterpret_cast<float2*>(start) + (v * n_blocks) * 2 + comp;
     // software pipeline: the registers of chunk c + 1 are loaded while chunk c is in the chain (a load that is only
     // used in the next iteration cannot sink to its first use, which is where ptxas puts the loads of a chunk otherwise)
     ts.prologue(nchunks);
-    int cb = 0, b = 0;
+    int cb = 0;
     float4 nx[4];
     ts.advance(0, nchunks);
     __syncwarp();
@@ -248,9 +250,12 @@ k_ssbx_state(const float* __restrict__ M, const __grid_constant__ SsbParams P, f
 #pragma unroll
             for (int q = 0; q < 4; q++) nx[q] = lds128_now(row + q);
         }
-        if (cb == 0 && live) {
-            start2[(v * n_blocks + b) * 2 + comp] = make_float2(z1, z2);
-            if (!TSB) start2[(v * n_blocks + b) * 2 + 1] = make_float2(0.0f, 0.0f);
+        if (cb == 0) {            // warp-uniform: a branch, taken once per block
+            if (live) {
+                sp[0] = make_float2(z1, z2);
+                if (!TSB) sp[1] = make_float2(0.0f, 0.0f);
+            }
+            sp += 2;
         }
 #pragma unroll
         for (int q = 0; q < 4; q++) {
@@ -263,7 +268,7 @@ k_ssbx_state(const float* __restrict__ M, const __grid_constant__ SsbParams P, f
             }
         }
         __syncwarp();
-        if (++cb == chunks_per_block) { cb = 0; b++; }
+        if (++cb == chunks_per_block) cb = 0;
     }
     if (live) {
         if (comp) { state[v].pad0 = z1; state[v].pad1 = z2; }

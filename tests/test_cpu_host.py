@@ -169,3 +169,36 @@ def test_bridge_chunker_and_replay(tmp_path):
                     "-o", exe, os.path.join(ROOT, "tests", "cpp", "chunker_test.cpp")], check=True)
     r = subprocess.run([exe, str(tmp_path / "cap.iq")], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and "chunker OK" in r.stdout, r.stdout + r.stderr
+
+
+def test_bench_numpy_source_equals_the_library_generator(sdrb):
+    """bench_synth.py (numpy) feeds the CPU legs of bench.py so that they never map the product library; it must be the
+    same integer generator as sdrb_synth_host (csrc/synth.cuh), byte for byte, for every wire format."""
+    import bench_synth as bs
+    for fmt in (sdrb.CU8, sdrb.CS16, sdrb.CF32):
+        for fs, stream, first in ((2_000_000, 0, 0), (30_720_000, 5, 3_400_000), (2_500_000, 70_000, 5_000_000_000)):
+            a = sdrb.synth_host(fmt, fs, stream, 1, first, 4000)[0]
+            b = bs.synth(fmt, fs, stream, first, 4000)
+            assert a.dtype == b.dtype and np.array_equal(a, b), (fmt, fs, stream, first)
+    raw = bs.synth(sdrb.CU8, 2_000_000, 1, 0, 64)
+    assert np.array_equal(bs.to_cf32(raw, sdrb.CU8), ol.to_cf32(raw, sdrb.CU8))
+
+
+def test_reference_arm_never_loads_the_product(tmp_path):
+    """`bench.py --impl reference` times the reference's CPU code only: it must run with the product library out of
+    reach (SDRB_LIB pointing nowhere makes any import of the package raise) and print the contract's JSON line with
+    the same `config` keys as our arm."""
+    import json
+    import subprocess
+    import sys
+    env = dict(os.environ, SDRB_LIB=str(tmp_path / "absent.so"))
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    assert d["impl"] == "reference" and d["unit"] == "MS/s" and d["value"] > 0 and d["gpu_launches"] == 0
+    assert "ssb" in d["config"]["stages"] and "fft" in d["config"]["stages"]
+    assert d["cpu_baseline"]["kind"] in ("reference", "port") and d["cpu_baseline"]["cores"] >= 1
+    import bench
+    ours = bench.config_dict(dict(bench.WORKLOADS["default"], name="default"), 1)
+    assert set(ours) == set(d["config"]) and ours == d["config"]
