@@ -90,6 +90,22 @@ int main(int argc, char** argv) {
             same = 0;
         }
         put(f, &same, sizeof same);
+        // pass 3: `static size_t sampCount = iq.size(); iq.resize(sampCount);` (src/ssb/ssb_demod_opt.cpp:225-227): the
+        // first call's block length is frozen; a shorter block is zero-extended, a longer one cut.  Blocks 0, 1, 2 with
+        // n, n / 2 and (when there is one more block to take from) 2 n samples, and a sound mode outside 0..2 on the
+        // last call (the file statics then keep the previous mode's parameters, :230-255)
+        if (B >= 4) {
+            sdrbSsbReset();
+            std::vector<int16_t> q0, q1, q2;
+            processSSB_opt(std::vector<std::complex<float>>(iq, iq + n), fs, true, q0, pulse, mode);
+            processSSB_opt(std::vector<std::complex<float>>(iq + (size_t)n, iq + (size_t)n + n / 2), fs, true, q1, pulse, mode);
+            processSSB_opt(std::vector<std::complex<float>>(iq + (size_t)2 * n, iq + (size_t)4 * n), fs, true, q2, pulse, 7);
+            const int32_t sizes[3] = {(int32_t)q0.size(), (int32_t)q1.size(), (int32_t)q2.size()};
+            put(f, sizes, sizeof sizes);
+            put(f, q0.data(), q0.size() * sizeof(int16_t));
+            put(f, q1.data(), q1.size() * sizeof(int16_t));
+            put(f, q2.data(), q2.size() * sizeof(int16_t));
+        }
     } catch (const std::exception& e) {
         fprintf(stderr, "dropin_check: %s\n", e.what());
         fclose(f);

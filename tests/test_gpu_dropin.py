@@ -53,6 +53,19 @@ def test_dropin_front_end(sdrb, tmp_path, n, fs, B, focus, mode):
         assert np.abs(pcm.astype(np.int32) - exp.astype(np.int32)).max(initial=0) <= 1, b
     same = np.frombuffer(blob, dtype=np.int32, count=1, offset=off)[0]
     assert same == 1, "SSBProcessor (queue + worker) PCM differs from direct processSSB_opt calls"
+    off += 4
+    # pass 3: the first call freezes the block length (ssb_demod_opt.cpp:225-227): a half block is zero-extended, a
+    # double block cut; the last call passes sound mode 7, which leaves the previous mode's parameters in place
+    sizes = np.frombuffer(blob, dtype=np.int32, count=3, offset=off); off += 12
+    assert tuple(sizes) == (m, m, m)
+    fresh = ol.OracleSsb()
+    feeds = ((iq[0], mode), (iq[1][:n // 2], mode), (np.concatenate([iq[2], iq[3]]), 7))
+    for k, (block, md) in enumerate(feeds):
+        got = np.frombuffer(blob, dtype=np.int16, count=m, offset=off); off += 2 * m
+        exp = fresh.process(block, fs, 1, md)        # the oracle latches the first length itself (sdr_oracle.c)
+        assert len(exp) == m and np.abs(got.astype(np.int32) - exp.astype(np.int32)).max(initial=0) <= 1, k
+        assert (got == exp).mean() >= 0.999
+    assert off == len(blob)
 
 
 def test_ragged_reads_through_the_batcher_equal_a_direct_call(sdrb, gpu_ctx, tmp_path):
