@@ -40,7 +40,8 @@ FMT_NAME = {CU8: "cu8", CS16: "cs16", CF32: "cf32", RU16: "ru16"}
 FMT_BYTES = {CU8: 2, CS16: 4, CF32: 8, RU16: 4}
 METRIC = "IQ MS/s through FFT+peak+SSB at 1/2/4/8 B200, % HBM roofline, vs host CPU"
 
-# name -> workload.  S = streams per GPU, B = readings per stream per step.
+# name -> workload.  S = streams per GPU, B = readings per stream per step.  The C3 shapes take 32 readings per call
+# (68 ms of signal): with 256 streams the per-(stream, block) passes of the SSB chain only have S x B lanes to fill the GPU.
 WORKLOADS = {
     "default": dict(
         what="65536 independent RTL-SDR u8 streams per GPU, one reading of each per step (the reference's own call shape, one "
@@ -55,13 +56,13 @@ WORKLOADS = {
                S=1, B=64, n=16384, fs=2_000_000, fmt=CU8, stages=F_FFT | F_SSB, extra={}),
     "c3": dict(what="256 LimeSDR-style cs16 streams, 30.72 MS/s, 65536-pt FFT + true-LSB demod (BASELINE configs[2]; "
                     "extension stage: the reference's LSB output is all zeros)",
-               S=256, B=8, n=65536, fs=30_720_000, fmt=CS16, stages=F_FFT | F_SSB,
+               S=256, B=32, n=65536, fs=30_720_000, fmt=CS16, stages=F_FFT | F_SSB,
                extra={"upperSideband": 0, "ssbTrueSideband": 1}),
     "c3ref": dict(what="256 cs16 streams, 30.72 MS/s, 65536-pt FFT + USB demod in reference mode (configs[2] without the "
                        "extension stage)",
-                  S=256, B=8, n=65536, fs=30_720_000, fmt=CS16, stages=F_FFT | F_SSB, extra={}),
+                  S=256, B=32, n=65536, fs=30_720_000, fmt=CS16, stages=F_FFT | F_SSB, extra={}),
     "c3fft": dict(what="256 cs16 streams, 65536-pt FFT + peak + strength only",
-                  S=256, B=8, n=65536, fs=30_720_000, fmt=CS16, stages=F_FFT, extra={}),
+                  S=256, B=32, n=65536, fs=30_720_000, fmt=CS16, stages=F_FFT, extra={}),
     "c4": dict(what="wideband cf32 61.44 MS/s, 256 SSB channels per stream on a 25 kHz raster, SSB only (BASELINE "
                     "configs[3]; extension stage, no reference code)",
                S=8, B=32, n=16384, fs=61_440_000, fmt=CF32, stages=F_SSB,

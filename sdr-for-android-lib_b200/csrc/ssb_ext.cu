@@ -24,6 +24,8 @@
 //   k_ssbx_agc   : one lane per (stream, channel, block): IIR2 from that state, second mix (true sideband), demod,
 //                  AGC in sweeps -> post-AGC samples; k_ssb_fir (ssb.cu) decimates; k_ssb_audio: HP/BP, boost, PCM
 // PCM layout: [stream][channel][block][m].  The block length must be a multiple of 32 samples.
+#include <cstdlib>
+
 #include "internal.h"
 #include "nco.cuh"
 #include "ssb_common.cuh"
@@ -86,6 +88,13 @@ __device__ __forceinline__ float4 lds128_now(const float4* p) {
                  : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
                  : "r"((unsigned)__cvta_generic_to_shared(p)));
     return v;
+}
+
+__device__ __forceinline__ void named_bar_sync_x(int id, int count) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+__device__ __forceinline__ void named_bar_arrive_x(int id, int count) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
 }
 
 // iir2Process :75-84 (previous OUTPUTS as state), one sample
@@ -276,6 +285,110 @@ k_ssbx_state(const float* __restrict__ M, const __grid_constant__ SsbParams P, f
     }
 }
 
+// ---------------------------------------------------------------- pass 1 as a producer / chain warp pair
+// The same walk with the roles of ssb.cu's k_ssb_state: warp 0 only moves data (cp.async from M into a ring of G groups
+// of K chunks), warp 1 only runs the chains (a group's K x 64 bytes per lane into registers, then 9 operations per
+// sample).  ncu on the one-warp version above: the chain itself at its 20 cycles per sample, plus ~17 cycles per
+// sample of copy issue, waits and loop overhead that a lone in-order warp cannot hide.  Named barriers hand the ring
+// slots over (full: ids 1..G, empty: ids 1+G..2G; bar.arrive by the side that hands over, bar.sync by the side that
+// waits).  Used when the chunk count is a multiple of K.
+constexpr int SSBX_RING_G = 4;      // ring slots (groups)
+constexpr int SSBX_RING_D = 2;      // groups the producer keeps in flight behind the one it is issuing
+
+template <bool TSB, int K>
+__global__ void __launch_bounds__(64)
+k_ssbx_state2(const float* __restrict__ M, const __grid_constant__ SsbParams P, float4* __restrict__ start,
+              SsbStreamState* __restrict__ state, size_t n_units, int n_blocks) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    constexpr int E = TSB ? 2 : 1, G = SSBX_RING_G, D = SSBX_RING_D;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t n_chains = n_units * E;
+    const size_t ch0 = (size_t)blockIdx.x * 32;
+    const size_t block_bytes = (size_t)P.n * E * sizeof(float);
+    const int chunks_per_block = (int)(block_bytes / SSB_ROW_BYTES);
+    const int ngroups = chunks_per_block * n_blocks / K;
+    if (warp == 0) {
+        // ---- producer: rows r0 + 8 j of the tile belong to chains ch0 + r0 + 8 j
+        const int sub = lane & 3, r0 = lane >> 2;
+        const unsigned char* rp[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            size_t ch = ch0 + r0 + 8 * j;
+            if (ch >= n_chains) ch = n_chains - 1;
+            rp[j] = reinterpret_cast<const unsigned char*>(M) + (ch / E) * block_bytes * n_blocks + sub * 16;
+        }
+        for (int gi = 0; gi < ngroups + D; gi++) {
+            if (gi < ngroups) {
+                const int slot = gi & (G - 1);
+                if (gi >= G) named_bar_sync_x(1 + G + slot, 64);            // the chain warp has emptied the slot
+                unsigned char* t = smem + (size_t)slot * K * SSB_TILE_BYTES + sub * 16;
+#pragma unroll
+                for (int k = 0; k < K; k++)
+#pragma unroll
+                    for (int j = 0; j < 4; j++)
+                        cp_async16(t + k * SSB_TILE_BYTES + (r0 + 8 * j) * SSB_ROW_PITCH,
+                                   rp[j] + ((size_t)gi * K + k) * SSB_ROW_BYTES);
+            }
+            cp_async_commit();                                              // one commit group per gi, empty past the end
+            if (gi >= D) {
+                cp_async_wait<D>();                                         // group gi - D has landed
+                __syncwarp();
+                __threadfence_block();
+                named_bar_arrive_x(1 + ((gi - D) & (G - 1)), 64);           // slot full
+            }
+        }
+    } else {
+        // ---- chain
+        const size_t ch = ch0 + lane;
+        const bool live = ch < n_chains;
+        const size_t chc = live ? ch : n_chains - 1;
+        const size_t v = chc / E;
+        const int comp = (int)(chc % E);
+        float z1 = comp ? state[v].pad0 : state[v].rf_z1, z2 = comp ? state[v].pad1 : state[v].rf_z2;
+        float2* sp = reinterpret_cast<float2*>(start) + (v * n_blocks) * 2 + comp;
+        int cb = 0;
+        for (int gi = 0; gi < ngroups; gi++) {
+            const int slot = gi & (G - 1);
+            named_bar_sync_x(1 + slot, 64);                                 // slot full
+            const unsigned char* t = smem + (size_t)slot * K * SSB_TILE_BYTES + lane * SSB_ROW_PITCH;
+            float4 d[K][4];
+#pragma unroll
+            for (int k = 0; k < K; k++)
+#pragma unroll
+                for (int q = 0; q < 4; q++) d[k][q] = lds128_now(reinterpret_cast<const float4*>(t + k * SSB_TILE_BYTES) + q);
+            if (gi + G < ngroups) {
+                __threadfence_block();                                      // the loads are done before the slot is handed back
+                named_bar_arrive_x(1 + G + slot, 64);
+            }
+#pragma unroll
+            for (int k = 0; k < K; k++) {
+                if (cb == 0) {
+                    if (live) {
+                        sp[0] = make_float2(z1, z2);
+                        if (!TSB) sp[1] = make_float2(0.0f, 0.0f);
+                    }
+                    sp += 2;
+                }
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    if (TSB) {
+                        ssbx_iir(P.rf, comp ? d[k][q].y : d[k][q].x, z1, z2);
+                        ssbx_iir(P.rf, comp ? d[k][q].w : d[k][q].z, z1, z2);
+                    } else {
+                        ssbx_iir(P.rf, d[k][q].x, z1, z2); ssbx_iir(P.rf, d[k][q].y, z1, z2);
+                        ssbx_iir(P.rf, d[k][q].z, z1, z2); ssbx_iir(P.rf, d[k][q].w, z1, z2);
+                    }
+                }
+                if (++cb == chunks_per_block) cb = 0;
+            }
+        }
+        if (live) {
+            if (comp) { state[v].pad0 = z1; state[v].pad1 = z2; }
+            else { state[v].rf_z1 = z1; state[v].rf_z2 = z2; }
+        }
+    }
+}
+
 // ---------------------------------------------------------------- pass 2: IIR2 from the recorded state, second mix, AGC
 // One lane per (stream, channel, block).  True sideband: Weaver second mix Re{(yI + j yQ) exp(+/- j theta2)}, doubled;
 // otherwise the reference's demodSSB on {y, y} (USB = y + y, LSB = y - y).  AGC in sweeps (ssb_common.cuh); the
@@ -382,9 +495,17 @@ static cudaError_t launch_ssbx_f(const void* iq, const SsbParams& P, const float
     const unsigned mgrid = (unsigned)(threads / 256 + 1 < 148u * 32u ? threads / 256 + 1 : 148u * 32u);
     k_ssbx_mix<TSB><<<mgrid, 256, 0, st>>>(X, d_inc1, M, C, span, nv, base);
     const size_t chains = nv * (TSB ? 2 : 1);
-    const size_t ssmem = (size_t)SSBX_STATE_STAGES * SSB_TILE_BYTES;
-    if ((e = cudaFuncSetAttribute(k_ssbx_state<TSB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssmem)) != cudaSuccess) return e;
-    k_ssbx_state<TSB><<<(unsigned)((chains + 31) / 32), 32, ssmem, st>>>(M, P, d_start, d_state, nv, B);
+    const long long nchunks = (long long)((size_t)P.n * (TSB ? 2 : 1) * sizeof(float) / SSB_ROW_BYTES) * B;
+    static const bool one_warp = getenv("SDRB_SSBX_STATE") && getenv("SDRB_SSBX_STATE")[0] == '1';
+    if (nchunks % 4 == 0 && !one_warp) {
+        constexpr int K = 4;
+        k_ssbx_state2<TSB, K><<<(unsigned)((chains + 31) / 32), 64, (size_t)SSBX_RING_G * K * SSB_TILE_BYTES, st>>>(
+            M, P, d_start, d_state, nv, B);
+    } else {
+        const size_t ssmem = (size_t)SSBX_STATE_STAGES * SSB_TILE_BYTES;
+        if ((e = cudaFuncSetAttribute(k_ssbx_state<TSB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssmem)) != cudaSuccess) return e;
+        k_ssbx_state<TSB><<<(unsigned)((chains + 31) / 32), 32, ssmem, st>>>(M, P, d_start, d_state, nv, B);
+    }
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     if (P.m <= 0) return cudaSuccess;
     constexpr bool CHECK = FMT == FMT_CF32;
