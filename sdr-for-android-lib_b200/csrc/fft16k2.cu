@@ -185,7 +185,12 @@ k_fft16k2(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict
 
 template <int FMT, int FRONT>
 static cudaError_t prep_one() {
-    return cudaFuncSetAttribute(k_fft16k2<FMT, FRONT>, cudaFuncAttributeMaxDynamicSharedMemorySize, F2Smem<FMT>::kBytes);
+    cudaError_t e = cudaFuncSetAttribute(k_fft16k2<FMT, FRONT>, cudaFuncAttributeMaxDynamicSharedMemorySize, F2Smem<FMT>::kBytes);
+    if (e != cudaSuccess) return e;
+    // all of the SM's L1 / shared memory as shared memory: what this CTA leaves free (~46 KB for u8) is then there for a
+    // co-resident CTA of the SSB pass instead of sitting in an L1 this kernel does not use
+    return cudaFuncSetAttribute(k_fft16k2<FMT, FRONT>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                (int)cudaSharedmemCarveoutMaxShared);
 }
 template <int FMT>
 static cudaError_t prep_fmt() {
