@@ -4,26 +4,30 @@
 // [fs/4 shift, 47-tap half-band fir_interleaved_24 :287-326 on the even samples, delay_interleaved :391-414
 // on the odd samples].  Checker: oracle/sdr_oracle_airspy.c, pinned against the reference's own file.
 //
-// Three kernels:
-//   k_airspy_dc   one thread per (stream, CHUNK of 16384 real samples).  The DC tracker
-//                 avg += 0.01f * (x - avg) is a rounded float recurrence: its bits are only reproduced by
-//                 walking the samples in order (three dependent operations per sample), which with one thread
-//                 per stream leaves the GPU empty (256 streams x 1 M samples: 36 ms).  The recurrence forgets
-//                 its start, though: two runs over the same samples from different starts come within an ulp
-//                 after ~1700 samples (0.99 per sample) and then land on the SAME float (measured: 1650-2150
-//                 samples on noisy ADC data) - and from then on they are the same run.  So every chunk but a
-//                 stream's first starts from a GUESS (avg = 0, 4096 samples before the chunk start) and walks
-//                 its warm-up + its own samples; the chunk also records the avg it started its own samples
-//                 from and the avg it ended with.
-//   k_airspy_fix  one thread per stream: chunk c is exact if the avg it started from is bit-identical to the
-//                 avg chunk c-1 ended with (chunk 0 starts from the carried state, so by induction every chunk
-//                 that passes is the sequential run).  A chunk that fails (it does on noise-free constant
-//                 input, where the recurrence stalls inside a ~100-ulp dead band) is walked again from the
-//                 right value, in order, and counted.  Worst case = the old one-thread-per-stream cost;
-//                 the result is bit-exact in every case.  Also carries avg and the 48-sample tail.
-//   k_airspy_fir  fully parallel: one thread per complex output, tile of translated samples staged in shared
-//                 memory; twelve un-fused multiply-adds in the reference's left-to-right order (I), a 12-sample
-//                 delay (Q).  The 48 translated samples before the call come from the carried state.
+// Two kernels (round 2: the half-band FIR moved INTO the walk; the translated scratch, its 8 B written and 8 B
+// re-read per complex sample, and the third kernel are gone):
+//   k_airspy_front  one lane per (stream, CHUNK of real samples).  The DC tracker avg += 0.01f * (x - avg) is a
+//                 rounded float recurrence: its bits are only reproduced by walking the samples in order (three
+//                 dependent operations per sample), which with one thread per stream leaves the GPU empty
+//                 (256 streams x 1 M samples: 36 ms).  The recurrence forgets its start, though: two runs over
+//                 the same samples from different starts come within an ulp after ~1700 samples (0.99 per
+//                 sample) and then land on the SAME float (measured: 1650-2150 samples on noisy ADC data) - and
+//                 from then on they are the same run.  So every chunk but a stream's first starts from a GUESS
+//                 (avg = 0, 4096 samples before the chunk start) and walks its run-in + its own samples.  The
+//                 lane keeps the last 24 even / 12 odd translated samples in registers and, for its own samples,
+//                 turns every piece of 32 translated samples into 16 complex outputs on the spot: twelve
+//                 un-fused products summed in the reference's left-to-right order (I), the 12-sample delay (Q).
+//                 The dependent chain of the walk leaves most issue slots of a lane empty; the FIR fills them.
+//                 A chunk records the avg it held 48 samples BEFORE its own first sample and 48 samples before
+//                 its end.
+//   k_airspy_fix  one thread per stream: chunk c is exact if the avg it held 48 samples before its start is
+//                 bit-identical to the one chunk c-1 held at the same sample (then both lanes walked the same 48
+//                 samples from the same value: same FIR history, same avg at the boundary; chunk 0 starts from
+//                 the carried state, so by induction every chunk that passes is the sequential run).  A chunk
+//                 that fails (it does on noise-free constant input, where the recurrence stalls inside a
+//                 ~100-ulp dead band) is walked again from the right value, in order, and counted.  Worst case =
+//                 one thread per stream; the result is bit-exact in every case.  Also carries avg and the
+//                 48-sample tail into the next call.
 // Output is cf32 [streams][blocks][N], which the CF32 FFT / SSB kernels consume unchanged.
 #include <cstdlib>
 
@@ -31,12 +35,9 @@
 
 namespace sdrb {
 
-__constant__ float c_hb[12] = {   // even taps 0..22 of HB_KERNEL_FLOAT (filters.h:30-52); taps 24..46 mirror them
-    -0.000998606272947510f, 0.001695637278417295f, -0.003054430179754289f, 0.005055504379767936f,
-    -0.007901319195893647f, 0.011873357051047719f, -0.017411159379930066f, 0.025304817427568772f,
-    -0.037225225204559217f, 0.057533286997004301f, -0.102327462004259350f, 0.317034472508947400f};
-
 namespace {
+
+constexpr unsigned AIR_NO_CHECK = 0x7fc00001u;   // "no avg recorded 48 samples before my start": never equals an avg
 
 __device__ __forceinline__ float air_step(unsigned raw, float& avg, int phase) {
     // (raw - 2048) * (1 / 2048) (airspy.c:316, SAMPLE_SCALE :58-62) without the int -> float conversion: the word
@@ -49,260 +50,304 @@ __device__ __forceinline__ float air_step(unsigned raw, float& avg, int phase) {
     return phase == 0 ? -x : phase == 1 ? -0.5f * x : phase == 2 ? x : 0.5f * x;
 }
 
-// n samples (a multiple of 8) from `in` (16-byte aligned), in order; translated samples to `out` when WRITE.
-// The recurrence is latency-bound on its own (three dependent operations per sample); the loads must not add
-// to that chain, so eight 16-byte loads (64 samples) are in flight ahead of the arithmetic.
-template <bool WRITE>
-__device__ __forceinline__ void air_walk(const uint4* __restrict__ in, float4* __restrict__ out, long long n8, float& avg) {
-    constexpr int PF = 8;
-    uint4 w[PF];
-#pragma unroll
-    for (int k = 0; k < PF; k++) w[k] = k < n8 ? __ldg(in + k) : make_uint4(0, 0, 0, 0);
-    for (long long i = 0; i < n8; i += PF) {
-#pragma unroll
-        for (int k = 0; k < PF; k++) {
-            if (i + k >= n8) break;
-            const uint4 c = w[k];
-            if (i + k + PF < n8) w[k] = __ldg(in + i + k + PF);
-            float4 a, b;
-            a.x = air_step(c.x & 0xffffu, avg, 0); a.y = air_step(c.x >> 16, avg, 1);
-            a.z = air_step(c.y & 0xffffu, avg, 2); a.w = air_step(c.y >> 16, avg, 3);
-            b.x = air_step(c.z & 0xffffu, avg, 0); b.y = air_step(c.z >> 16, avg, 1);
-            b.z = air_step(c.w & 0xffffu, avg, 2); b.w = air_step(c.w >> 16, avg, 3);
-            if (WRITE) {
-                out[2 * (i + k)] = a;
-                out[2 * (i + k) + 1] = b;
-            }
-        }
-    }
+// eight samples (one 16-byte word; the first is a multiple of 4 into the stream) -> t[0..7]
+__device__ __forceinline__ void air_walk8(const uint4 v, float& avg, float* t) {
+    t[0] = air_step(v.x & 0xffffu, avg, 0); t[1] = air_step(v.x >> 16, avg, 1);
+    t[2] = air_step(v.y & 0xffffu, avg, 2); t[3] = air_step(v.y >> 16, avg, 3);
+    t[4] = air_step(v.z & 0xffffu, avg, 0); t[5] = air_step(v.z >> 16, avg, 1);
+    t[6] = air_step(v.w & 0xffffu, avg, 2); t[7] = air_step(v.w >> 16, avg, 3);
 }
 
-// T is [n_streams][AIRSPY_TAIL + n_real]: the carried tail, then this call's translated samples.
-// from[s][c] = the avg chunk c started its own samples with, upto[s][c] = the avg it ended with.
-//
-// A lane walks one chunk, so the 32 lanes of a warp sit 32 KiB (input) / 64 KiB (output) apart: direct 16-byte
-// loads and stores would touch 32 different lines per instruction.  Instead the warp moves PIECES of 32 samples
-// per row: 64 bytes of every row come in with cp.async (4 lanes x 16 B per row, four pieces in flight), a lane walks
-// its own row from shared memory, leaves its 32 translated samples in an output tile, and the warp writes the
-// tile out 4 rows x 128 contiguous bytes per instruction.  Row pitches (80 B in, 144 B out) keep the 16-byte
-// accesses of a quarter-warp on distinct banks.
-constexpr int AIRDC_WARPS = 2;
-constexpr int AIRDC_IN_PITCH = 80, AIRDC_OUT_PITCH = 144;
-constexpr int AIRDC_IN_TILE = 32 * AIRDC_IN_PITCH, AIRDC_OUT_TILE = 32 * AIRDC_OUT_PITCH;
-constexpr int AIRDC_STAGES = 4;   // pieces in flight per warp: a 32-sample piece is shorter than a memory round trip
-struct __align__(8) AirRow {
-    const uint16_t* in;   // first sample the lane walks (run-in included)
-    float* out;           // where the chunk's own first translated sample goes
-    int total, w;         // samples walked, of which run-in (not written); both multiples of 8, w of 32
+// The FIR history of a lane: with j0 the first complex output of the coming piece, e[i] = even translated sample
+// j0 - 24 + i (sample 2 (j0 - 24 + i) of the stream), o[i] = odd translated sample j0 - 12 + i.
+struct AirHist {
+    float e[24], o[12];
 };
 
-__global__ void __launch_bounds__(AIRDC_WARPS * 32)
-k_airspy_dc(const uint16_t* __restrict__ raw, const AirspyStreamState* __restrict__ state, float* __restrict__ T,
-            float* __restrict__ from, float* __restrict__ upto, int n_streams, long long n_real, int n_chunks,
-            int chunk, int warm) {
+// One piece: 32 translated samples t[] (even E[j0 + i] = t[2 i], odd O[j0 + i] = t[2 i + 1]) -> 16 complex outputs
+// out[2 m], out[2 m + 1].  Output j = { sum_k h[k] * (E[j - k] + E[j - 23 + k]), O[j - 12] }: fir_interleaved_24
+// (iqconverter_float.c:287-326: twelve products, each of a tap with the SUM of its two mirrored samples, added
+// left to right) and delay_interleaved (:391-414).  All indices are literals after unrolling, the taps immediates.
+__device__ __forceinline__ void air_fir16(const AirHist& hs, const float* t, float* out) {
+    constexpr float h[12] = {   // even taps 0..22 of HB_KERNEL_FLOAT (filters.h:30-52); taps 24..46 mirror them
+        -0.000998606272947510f, 0.001695637278417295f, -0.003054430179754289f, 0.005055504379767936f,
+        -0.007901319195893647f, 0.011873357051047719f, -0.017411159379930066f, 0.025304817427568772f,
+        -0.037225225204559217f, 0.057533286997004301f, -0.102327462004259350f, 0.317034472508947400f};
+    float ee[40];
+#pragma unroll
+    for (int i = 0; i < 24; i++) ee[i] = hs.e[i];
+#pragma unroll
+    for (int i = 0; i < 16; i++) ee[24 + i] = t[2 * i];
+#pragma unroll
+    for (int m = 0; m < 16; m++) {
+        float acc = __fmul_rn(h[0], __fadd_rn(ee[24 + m], ee[1 + m]));
+#pragma unroll
+        for (int k = 1; k < 12; k++) acc = __fadd_rn(acc, __fmul_rn(h[k], __fadd_rn(ee[24 + m - k], ee[1 + m + k])));
+        out[2 * m] = acc;
+        out[2 * m + 1] = m < 12 ? hs.o[m] : t[2 * (m - 12) + 1];
+    }
+}
+// the history 16 outputs later
+__device__ __forceinline__ void air_shift(AirHist& hs, const float* t) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) hs.e[i] = hs.e[16 + i];
+#pragma unroll
+    for (int i = 0; i < 16; i++) hs.e[8 + i] = t[2 * i];
+#pragma unroll
+    for (int i = 0; i < 12; i++) hs.o[i] = t[2 * (4 + i) + 1];
+}
+// from the 48 translated samples before an output (oldest first): a carried tail, or a walk of 48 samples
+__device__ __forceinline__ void air_hist_from(AirHist& hs, const float* t48) {
+#pragma unroll
+    for (int i = 0; i < 24; i++) hs.e[i] = t48[2 * i];
+#pragma unroll
+    for (int i = 0; i < 12; i++) hs.o[i] = t48[2 * (12 + i) + 1];
+}
+
+// The 32 lanes of a warp walk the SAME chunk of 32 different streams, so everything about the walk but the data is
+// warp-uniform (run-in, length, piece count, the marks) and every address is affine in the row.  Lanes sit a whole
+// stream apart in the input and in the output: direct 16-byte loads and stores would touch 32 different lines per
+// instruction.  Instead the warp moves pieces per row: 128 bytes (one line, two pieces of 32 samples) of every row
+// come in with cp.async (8 lanes x 16 B per row, three loads in flight), a lane walks its own row from shared memory
+// and leaves the 16 complex outputs (128 bytes) of every piece in an output tile, which the warp writes out 4 rows x
+// 128 contiguous bytes per instruction.  The row pitch (144 B in and out) keeps the 16-byte accesses of a
+// quarter-warp on distinct banks.
+// Lanes past the last stream shadow it (reads only).
+constexpr int AIRDC_WARPS = 2;
+#ifndef AIRDC_SUPER
+#define AIRDC_SUPER 2
+#endif
+constexpr int AIRDC_SUP = AIRDC_SUPER;                        // 32-sample pieces per load: 2 = whole 128-byte lines
+constexpr int AIRDC_IN_PITCH = 64 * AIRDC_SUP + 16, AIRDC_OUT_PITCH = 144;
+constexpr int AIRDC_IN_TILE = 32 * AIRDC_IN_PITCH, AIRDC_OUT_TILE = 32 * AIRDC_OUT_PITCH;
+constexpr int AIRDC_STAGES = AIRDC_SUP == 1 ? 4 : 3;          // loads in flight per warp
+constexpr int AIRDC_LPR = 4 * AIRDC_SUP;                      // lanes (16 bytes each) along a row of a load
+
+// chunk c of a stream = real samples [c * chunk, (c + 1) * chunk), the last one through the end of the call
+// (so every chunk but a lone one is at least `chunk` >= 64 samples long).
+// from48[s][c] = the avg the lane held 48 samples before its own first sample (AIR_NO_CHECK if its run-in is
+// shorter than that), upto48[s][c] = the avg it held 48 samples before its end.
+#ifndef AIRDC_MINB
+#define AIRDC_MINB 6   // 6 CTAs per SM: what the shared memory allows
+#endif
+__global__ void __launch_bounds__(AIRDC_WARPS * 32, AIRDC_MINB)
+k_airspy_front(const uint16_t* __restrict__ raw, const AirspyStreamState* __restrict__ state, float* __restrict__ iq,
+               float* __restrict__ from48, float* __restrict__ upto48, int n_streams, long long n_real, int n_chunks,
+               int chunk, int warm) {
     __shared__ __align__(16) unsigned char s_in[AIRDC_WARPS][AIRDC_STAGES * AIRDC_IN_TILE];
     __shared__ __align__(16) unsigned char s_out[AIRDC_WARPS][AIRDC_OUT_TILE];
-    __shared__ AirRow s_rows[AIRDC_WARPS][32];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const long long lanes = (long long)n_streams * n_chunks;
-    const long long id0 = ((long long)blockIdx.x * AIRDC_WARPS + warp) * 32;
-    if (id0 >= lanes) return;
-    const bool live = id0 + lane < lanes;
-    const long long id = live ? id0 + lane : id0;   // idle lanes shadow lane 0's row (reads only)
-    const int s = (int)(id / n_chunks), c = (int)(id - (long long)s * n_chunks);
-    float* t = T + (size_t)s * (AIRSPY_TAIL + n_real);
-    const uint16_t* x = raw + (size_t)s * n_real;
+    // read once: under register pressure the compiler otherwise re-reads the thread id
+    // (S2R, tens of cycles on the short scoreboard) inside the piece loop for every lane-derived address
+    const unsigned tid = __shfl_sync(0xffffffffu, threadIdx.x, threadIdx.x & 31);   // (a shuffle is not re-derived)
+    const int lane = tid & 31, warp = tid >> 5;
+    const int groups = (n_streams + 31) >> 5;
+    const long long task = (long long)blockIdx.x * AIRDC_WARPS + warp;     // (stream group, chunk), chunk fastest
+    if (task >= (long long)groups * n_chunks) return;
+    const int g = (int)(task / n_chunks), c = (int)(task - (long long)g * n_chunks);
+    const int rows_live = min(32, n_streams - 32 * g);
+    const int s = 32 * g + min(lane, rows_live - 1);
+    // ---- warp-uniform geometry
     const long long pos = (long long)c * chunk;
-    const int len = (int)(n_real - pos < chunk ? n_real - pos : chunk);
+    const int len = (int)(c == n_chunks - 1 ? n_real - pos : chunk);
     const int w = c == 0 ? 0 : (int)(pos < warm ? pos : warm);
-    // a run-in that reaches back to the call's first sample starts from the carried avg: not a guess
-    float avg = (live && pos <= warm) ? state[s].avg : 0.0f;
-    if (c == 0 && live) {
-#pragma unroll 4
-        for (int k = 0; k < AIRSPY_TAIL; k++) t[k] = state[s].tail[k];
-    }
-    AirRow me;
-    me.in = x + pos - w;
-    me.out = t + AIRSPY_TAIL + pos;
-    me.total = live ? w + len : 0;
-    me.w = w;
-    AirRow* rows = s_rows[warp];
-    rows[lane] = me;
-    int pieces = (me.total + 31) >> 5, P = pieces;
+    const int total = w + len, P = (total + 31) >> 5, p_own = w >> 5;
+    const bool from_state = pos == w;   // a walk that starts on the call's first sample starts from the carried state
+    const int g_from = (c > 0 && w >= AIRSPY_TAIL) ? (w - AIRSPY_TAIL) >> 3 : -1;        // in groups of 8 samples
+    const int g_upto = total >= AIRSPY_TAIL ? (total - AIRSPY_TAIL) >> 3 : -1;
+    const size_t rec = (size_t)s * n_chunks + c;
+    if (c > 0 && g_from < 0) from48[rec] = __uint_as_float(AIR_NO_CHECK);
+
+    float avg = from_state ? state[s].avg : 0.0f;
+    AirHist hs;
+    if (from_state) {
+        float t48[AIRSPY_TAIL];
 #pragma unroll
-    for (int d = 16; d > 0; d >>= 1) P = max(P, __shfl_xor_sync(0xffffffffu, P, d));
-    __syncwarp();
+        for (int k = 0; k < AIRSPY_TAIL; k++) t48[k] = state[s].tail[k];
+        air_hist_from(hs, t48);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 24; k++) hs.e[k] = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 12; k++) hs.o[k] = 0.0f;
+    }
     unsigned char* tin = s_in[warp];
     unsigned char* tout = s_out[warp];
-    const int sub = lane & 3, r0 = lane >> 2;
-    auto issue = [&](int p, int stage) {
+    // loads: lane = (row r0 + (32 / LPR) k, 16-byte part `sub`) of the load piece
+    const int sub = lane % AIRDC_LPR, r0 = lane / AIRDC_LPR;
+    const uint16_t* const src0 = raw + (size_t)(32 * g) * n_real + (pos - w);
+    const unsigned dst0 = (unsigned)__cvta_generic_to_shared(tin + r0 * AIRDC_IN_PITCH + sub * 16);
+    const int L = (total + 32 * AIRDC_SUP - 1) / (32 * AIRDC_SUP);   // load pieces
+    auto issue = [&](int l, int stage) {
+        int off = 32 * AIRDC_SUP * l + 8 * sub;              // samples from the row's first
+        off = min(off, total - 8);                           // past the row's end: re-read its last 16 bytes
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const int r = r0 + 8 * k;
-            const AirRow ri = rows[r];
-            int off = 32 * p + 8 * sub;                      // samples from ri.in
-            if (off > ri.total - 8) off = ri.total - 8;      // past the row's end: re-read its last 16 bytes
-            if (off < 0) off = 0;
-            const unsigned d = (unsigned)__cvta_generic_to_shared(tin + stage * AIRDC_IN_TILE + r * AIRDC_IN_PITCH + sub * 16);
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(ri.in + off) : "memory");
+        for (int k = 0; k < AIRDC_LPR; k++) {
+            const int r = min(r0 + (32 / AIRDC_LPR) * k, rows_live - 1);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst0 + stage * AIRDC_IN_TILE +
+                                                                            (32 / AIRDC_LPR) * k * AIRDC_IN_PITCH),
+                         "l"(src0 + (size_t)r * n_real + off) : "memory");
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
-    for (int k = 0; k < AIRDC_STAGES - 1; k++) {   // one commit group per piece, empty past the end
-        if (k < P) issue(k, k);
+    // stores: instruction i covers rows 4i .. 4i+3, 8 lanes x 16 B along each row
+    const int orow = lane >> 3, col = lane & 7;
+    float* const out0 = iq + (size_t)(32 * g + orow) * n_real + pos + 4 * col;
+    const size_t out_step = 4 * (size_t)n_real;              // floats between the rows of consecutive instructions
+    const unsigned char* const tsrc = tout + orow * AIRDC_OUT_PITCH + col * 16;
+
+    for (int k = 0; k < AIRDC_STAGES - 1; k++) {   // one commit group per load, empty past the end
+        if (k < L) issue(k, k);
         else asm volatile("cp.async.commit_group;" ::: "memory");
     }
     for (int p = 0; p < P; p++) {
-        if (p + AIRDC_STAGES - 1 < P) issue(p + AIRDC_STAGES - 1, (p + AIRDC_STAGES - 1) % AIRDC_STAGES);
-        else asm volatile("cp.async.commit_group;" ::: "memory");
-        asm volatile("cp.async.wait_group %0;" ::"n"(AIRDC_STAGES - 1) : "memory");
-        __syncwarp();
-        if (32 * p == me.w && live) from[id] = avg;          // the run-in ends on a piece boundary
-        const uint4* row = reinterpret_cast<const uint4*>(tin + (p % AIRDC_STAGES) * AIRDC_IN_TILE + lane * AIRDC_IN_PITCH);
-        float4* mine = reinterpret_cast<float4*>(tout + lane * AIRDC_OUT_PITCH);
+        const int l = p / AIRDC_SUP, h = p % AIRDC_SUP;
+        if (h == 0) {
+            if (l + AIRDC_STAGES - 1 < L) issue(l + AIRDC_STAGES - 1, (l + AIRDC_STAGES - 1) % AIRDC_STAGES);
+            else asm volatile("cp.async.commit_group;" ::: "memory");
+            asm volatile("cp.async.wait_group %0;" ::"n"(AIRDC_STAGES - 1) : "memory");
+            __syncwarp();
+        }
+        const uint4* row = reinterpret_cast<const uint4*>(tin + (l % AIRDC_STAGES) * AIRDC_IN_TILE + lane * AIRDC_IN_PITCH + 64 * h);
+        // past the row's end the walk goes on over re-read bytes: nothing it produces there is kept
+        float t[32], aq[4];
 #pragma unroll
         for (int q = 0; q < 4; q++) {
-            if (32 * p + 8 * q < me.total) {
-                const uint4 v = row[q];
-                float4 a, b;
-                a.x = air_step(v.x & 0xffffu, avg, 0); a.y = air_step(v.x >> 16, avg, 1);
-                a.z = air_step(v.y & 0xffffu, avg, 2); a.w = air_step(v.y >> 16, avg, 3);
-                b.x = air_step(v.z & 0xffffu, avg, 0); b.y = air_step(v.z >> 16, avg, 1);
-                b.z = air_step(v.w & 0xffffu, avg, 2); b.w = air_step(v.w >> 16, avg, 3);
-                mine[2 * q] = a;
-                mine[2 * q + 1] = b;
+            aq[q] = avg;
+            air_walk8(row[q], avg, t + 8 * q);
+        }
+        // (lanes past the last stream walk its data and write its records: same values to the same addresses)
+        if (p == (g_from >> 2)) from48[rec] = aq[2];           // g_from = 4 (w / 32) - 6: always the third group
+        if (p == (g_upto >> 2)) {
+            const int q = g_upto & 3;
+            upto48[rec] = q == 0 ? aq[0] : q == 1 ? aq[1] : q == 2 ? aq[2] : aq[3];
+        }
+        if (p >= p_own) {                                      // the chunk's own samples: 16 complex outputs
+            float o[32];
+            air_fir16(hs, t, o);
+            float4* mine = reinterpret_cast<float4*>(tout + lane * AIRDC_OUT_PITCH);
+#pragma unroll
+            for (int q = 0; q < 8; q++) mine[q] = make_float4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+        }
+        if (p + 2 >= p_own) air_shift(hs, t);                  // the history matters from 48 samples before the own ones
+        if (p >= p_own) {
+            __syncwarp();
+            float* dst = out0 + 32 * (p - p_own);
+            if (32 * p + 4 * col < total) {
+                if (rows_live == 32) {
+#pragma unroll
+                    for (int i = 0; i < 8; i++)
+                        *reinterpret_cast<float4*>(dst + i * out_step) =
+                            *reinterpret_cast<const float4*>(tsrc + 4 * i * AIRDC_OUT_PITCH);
+                } else {
+#pragma unroll 1
+                    for (int i = 0; 4 * i + orow < rows_live; i++)
+                        *reinterpret_cast<float4*>(dst + i * out_step) =
+                            *reinterpret_cast<const float4*>(tsrc + 4 * i * AIRDC_OUT_PITCH);
+                }
             }
         }
         __syncwarp();
-        // the tile out: instruction i covers rows 4i .. 4i+3, 8 lanes x 16 B along each row
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-            const int r = 4 * i + (lane >> 3), col = lane & 7;
-            const AirRow ri = rows[r];
-            const int at = 32 * p + 4 * col;                 // samples from ri.in
-            if (at >= ri.w && at < ri.total)
-                *reinterpret_cast<float4*>(ri.out + (at - ri.w)) =
-                    *reinterpret_cast<const float4*>(tout + r * AIRDC_OUT_PITCH + col * 16);
-        }
-        __syncwarp();
     }
-    if (live) upto[id] = avg;
+}
+
+// 48 samples walked in order from `in` (16-byte aligned, a multiple of 4 into the stream) -> t48[]
+__device__ __forceinline__ void air_walk48(const uint16_t* in, float& avg, float* t48) {
+#pragma unroll
+    for (int q = 0; q < 6; q++) air_walk8(__ldg(reinterpret_cast<const uint4*>(in) + q), avg, t48 + 8 * q);
 }
 
 __global__ void __launch_bounds__(32)
-k_airspy_fix(const uint16_t* __restrict__ raw, AirspyStreamState* __restrict__ state, float* __restrict__ T,
-             const float* __restrict__ from, float* __restrict__ upto, int n_streams, long long n_real, int n_chunks,
+k_airspy_fix(const uint16_t* __restrict__ raw, AirspyStreamState* __restrict__ state, float* __restrict__ iq,
+             const float* __restrict__ from48, float* __restrict__ upto48, int n_streams, long long n_real, int n_chunks,
              int chunk) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_streams) return;
-    float* t = T + (size_t)s * (AIRSPY_TAIL + n_real);
     const uint16_t* x = raw + (size_t)s * n_real;
-    const float* fr = from + (size_t)s * n_chunks;
-    float* up = upto + (size_t)s * n_chunks;
+    float* orow = iq + (size_t)s * n_real;
+    const float* fr = from48 + (size_t)s * n_chunks;
+    float* up = upto48 + (size_t)s * n_chunks;
+    AirspyStreamState* st = state + s;
     unsigned redone = 0;
     for (int c = 1; c < n_chunks; c++) {
-        float avg = up[c - 1];
+        float avg = up[c - 1];                                   // the avg at sample pos - 48, exact by induction
         if (__float_as_uint(fr[c]) == __float_as_uint(avg)) continue;
         const long long pos = (long long)c * chunk;
-        const long long len = n_real - pos < chunk ? n_real - pos : chunk;
-        air_walk<true>(reinterpret_cast<const uint4*>(x + pos), reinterpret_cast<float4*>(t + AIRSPY_TAIL + pos), len >> 3, avg);
-        up[c] = avg;
+        const long long len = c == n_chunks - 1 ? n_real - pos : chunk;
+        AirHist hs;
+        {
+            float t48[AIRSPY_TAIL];
+            air_walk48(x + pos - AIRSPY_TAIL, avg, t48);
+            air_hist_from(hs, t48);
+        }
+        for (long long i = 0; i < len; i += 32) {
+            float t[32], o[32];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const long long at = i + 8 * q;
+                if (at < len) {
+                    if (at == len - AIRSPY_TAIL) up[c] = avg;
+                    air_walk8(__ldg(reinterpret_cast<const uint4*>(x + pos + at)), avg, t + 8 * q);
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 8; k++) t[8 * q + k] = 0.0f;
+                }
+            }
+            air_fir16(hs, t, o);
+            air_shift(hs, t);
+#pragma unroll
+            for (int q = 0; q < 8; q++)
+                if (i + 4 * q < len)
+                    *reinterpret_cast<float4*>(orow + pos + i + 4 * q) = make_float4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+        }
         redone++;
     }
-    AirspyStreamState* st = state + s;
-    st->avg = up[n_chunks - 1];
-    st->redone += redone;
-    // the new tail: the last AIRSPY_TAIL translated samples (n_real >= AIRSPY_TAIL, or the tail straddles the
-    // old one: both are in t[])
-#pragma unroll 4
-    for (int k = 0; k < AIRSPY_TAIL; k++) st->tail[k] = t[n_real + k];
-}
-
-constexpr int AIR_TILE = 1024;      // complex outputs per tile: 256 threads x 4 consecutive outputs
-constexpr int AIR_THREADS = 256;
-constexpr int AIR_TILES_PER_CTA = 4;
-constexpr int AIR_HALF = AIR_TILE + AIRSPY_TAIL / 2;   // even (or odd) translated samples a tile needs: 24 of history
-
-// Output j of a stream = { sum_k h[k] * (E[j-k] + E[j-23+k]), O[j-12] } with E / O the even / odd translated
-// samples (E[i] = sample 2i).  A tile de-interleaves its stretch of T into E and O in shared memory on the way
-// in (16-byte loads, 8-byte conflict-free stores); a thread then owns 4 consecutive outputs and reads its 28
-// even samples as seven 16-byte vectors (a quarter-warp reads 128 contiguous bytes: no bank conflicts) instead
-// of 24 scalar loads per output.
-__global__ void __launch_bounds__(AIR_THREADS)
-k_airspy_fir(const float* __restrict__ T, cpx* __restrict__ iq, long long n_real) {
-    __shared__ __align__(16) float E[AIR_HALF];
-    __shared__ __align__(16) float O[AIR_HALF];
-    const int s = blockIdx.y;
-    const long long n_out = n_real >> 1;
-    const float* trow = T + (size_t)s * (AIRSPY_TAIL + n_real);   // trow[0] = translated sample -48 = E[-24]
-    cpx* orow = iq + (size_t)s * n_out;
-    float h[12];
+    // carry: the avg after the call's last sample and the last AIRSPY_TAIL translated samples
+    if (n_real >= AIRSPY_TAIL) {
+        float avg = up[n_chunks - 1];
+        float t48[AIRSPY_TAIL];
+        air_walk48(x + n_real - AIRSPY_TAIL, avg, t48);
+        st->avg = avg;
 #pragma unroll
-    for (int k = 0; k < 12; k++) h[k] = c_hb[k];
-    for (int tile = 0; tile < AIR_TILES_PER_CTA; tile++) {
-        const long long j0 = ((long long)blockIdx.x * AIR_TILES_PER_CTA + tile) * AIR_TILE;
-        if (j0 >= n_out) break;
-        // pairs available from trow + 2*j0: 24 of history + the outputs left in the row
-        const long long pairs = (n_out - j0 < AIR_TILE ? n_out - j0 : AIR_TILE) + AIRSPY_TAIL / 2;
-        const float4* src = reinterpret_cast<const float4*>(trow + 2 * j0);
-        if (tile) __syncthreads();   // the previous tile's readers are done
-        for (int i = threadIdx.x; 2 * i < AIR_HALF; i += AIR_THREADS) {
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (2 * i + 1 < pairs) v = __ldg(src + i);                     // pairs is even (n_out - j0 and 24 are)
-            *reinterpret_cast<float2*>(E + 2 * i) = make_float2(v.x, v.z);
-            *reinterpret_cast<float2*>(O + 2 * i) = make_float2(v.y, v.w);
+        for (int k = 0; k < AIRSPY_TAIL; k++) st->tail[k] = t48[k];
+    } else {
+        // a call shorter than the tail (a lone chunk, walked from the carried state): the old tail slides
+        float avg = st->avg;
+        const int n = (int)n_real;
+        for (int k = 0; k + n < AIRSPY_TAIL; k++) st->tail[k] = st->tail[k + n];
+        for (int i = 0; i < n; i += 8) {
+            float t[8];
+            air_walk8(__ldg(reinterpret_cast<const uint4*>(x + i)), avg, t);
+            for (int k = 0; k < 8; k++) st->tail[AIRSPY_TAIL - n + i + k] = t[k];
         }
-        __syncthreads();
-        const int l = 4 * threadIdx.x;            // local output index of this thread's first output
-        if (j0 + l < n_out) {
-            // E[l .. l+27] in tile coordinates = even samples j-24 .. j+3 of output j = j0 + l
-            float e[28];
-#pragma unroll
-            for (int q = 0; q < 7; q++) {
-                const float4 v = *reinterpret_cast<const float4*>(E + l + 4 * q);
-                e[4 * q] = v.x; e[4 * q + 1] = v.y; e[4 * q + 2] = v.z; e[4 * q + 3] = v.w;
-            }
-            const float4 o = *reinterpret_cast<const float4*>(O + l + 12);   // odd samples j-12 .. j-9
-            const float qv[4] = {o.x, o.y, o.z, o.w};
-            float2 out[4];
-#pragma unroll
-            for (int m = 0; m < 4; m++) {
-                // output j0+l+m: E[j-k] = e[24+m-k], E[j-23+k] = e[1+m+k]; the reference's left-to-right order
-                float acc = __fmul_rn(h[0], __fadd_rn(e[24 + m], e[1 + m]));
-#pragma unroll
-                for (int k = 1; k < 12; k++) acc = __fadd_rn(acc, __fmul_rn(h[k], __fadd_rn(e[24 + m - k], e[1 + m + k])));
-                out[m] = make_float2(acc, qv[m]);
-            }
-            // n_out is even but not always a multiple of 4: the last thread of a row may own 2 outputs
-            float4* dst = reinterpret_cast<float4*>(orow + j0 + l);
-            dst[0] = make_float4(out[0].x, out[0].y, out[1].x, out[1].y);
-            if (j0 + l + 2 < n_out) dst[1] = make_float4(out[2].x, out[2].y, out[3].x, out[3].y);
-        }
+        st->avg = avg;
     }
+    st->redone += redone;
 }
 
 }  // namespace
 
-// Chunking of the DC pass: `chunk` real samples per lane, `warm` samples of run-in before a guessed start.
+// Chunking of the walk: `chunk` real samples per lane, `warm` samples of run-in before a guessed start.
 // Two environment variables are test hooks (a tiny run-in forces the second walk, a huge chunk gives the plain
 // sequential walk); they are read when a context allocates its Airspy buffers.  Without them the chunk follows
-// the call: a lane's walk is a latency-bound chain, so the pass wants ~50 k lanes in flight (a dozen warps per
-// SM), but every lane also pays the 4096-sample run-in, so chunks stay within [2048, 16384].
+// the call: the smallest power of two in [2048, 16384] whose warps (one per 32 streams and chunk) are all resident
+// at once on a B200 (148 SMs x 6 CTAs x 2 warps) - every lane pays the 4096-sample run-in, so a smaller chunk only
+// pays while it fills empty SMs (measured, 256 streams x 1 M samples: 8192 -> 112 GS/s, 4096 -> 103, 16384 -> 96).
 constexpr int AIR_CHUNK_MIN = 2048, AIR_CHUNK_MAX = 16384, AIR_WARM = 4096;
+constexpr long long AIR_RESIDENT_WARPS = 148 * AIRDC_MINB * AIRDC_WARPS;
 void airspy_chunking(int* chunk, int* warm) {
     const char* ce = getenv("SDRB_AIRSPY_CHUNK");
     const char* we = getenv("SDRB_AIRSPY_WARM");
     int c = ce ? atoi(ce) : 0, w = we ? atoi(we) : AIR_WARM;
-    if (ce && c < 32) c = 32;
+    if (ce && c < 64) c = 64;   // a chunk holds the 48 samples its successor is checked against
     if (w < 0) w = 0;
     *chunk = c & ~31;   // pieces of 32 samples: chunk starts and the end of the run-in fall on piece boundaries
     *warm = w & ~31;    // chunk 0 = follow the call
 }
 static int airspy_chunk_for(int fixed, int n_streams, long long n_real) {
     if (fixed > 0) return fixed;
-    const long long want = (long long)n_streams * n_real / 49152;
+    const long long groups = (n_streams + 31) / 32;
     int c = AIR_CHUNK_MIN;
-    while (c < AIR_CHUNK_MAX && 2LL * c <= want) c *= 2;
+    while (c < AIR_CHUNK_MAX && groups * (n_real / c) > AIR_RESIDENT_WARPS) c *= 2;
     return c;
 }
 size_t airspy_work_floats(int n_streams, long long n_real, int chunk) {
@@ -312,23 +357,21 @@ size_t airspy_work_floats(int n_streams, long long n_real, int chunk) {
 
 // raw: [n_streams][n_real] uint16 (n_real = 2 * blocks * N, a multiple of 8); iq: [n_streams][n_real / 2] cf32;
 // d_work: airspy_work_floats(n_streams, n_real, chunk) floats
-cudaError_t launch_airspy_front(const uint16_t* d_raw, AirspyStreamState* d_state, float* d_T, cpx* d_iq, float* d_work,
+cudaError_t launch_airspy_front(const uint16_t* d_raw, AirspyStreamState* d_state, cpx* d_iq, float* d_work,
                                 int chunk, int warm, int n_streams, long long n_real, cudaStream_t st, int* launches) {
     if (n_streams <= 0 || n_real <= 0) return cudaSuccess;
     chunk = airspy_chunk_for(chunk, n_streams, n_real);
-    if (n_real % 8 || chunk < 32 || chunk % 32 || warm % 32) return cudaErrorInvalidValue;
-    const int n_chunks = (int)((n_real + chunk - 1) / chunk);
-    float* from = d_work;
-    float* upto = d_work + (size_t)n_streams * n_chunks;
-    const long long lanes = (long long)n_streams * n_chunks;
-    k_airspy_dc<<<(unsigned)((lanes + 32 * AIRDC_WARPS - 1) / (32 * AIRDC_WARPS)), 32 * AIRDC_WARPS, 0, st>>>(d_raw, d_state, d_T, from, upto, n_streams, n_real, n_chunks,
-                                                             chunk, warm);
-    k_airspy_fix<<<(n_streams + 31) / 32, 32, 0, st>>>(d_raw, d_state, d_T, from, upto, n_streams, n_real, n_chunks, chunk);
-    const long long n_out = n_real / 2;
-    const long long per_cta = (long long)AIR_TILE * AIR_TILES_PER_CTA;
-    dim3 grid((unsigned)((n_out + per_cta - 1) / per_cta), (unsigned)n_streams);
-    k_airspy_fir<<<grid, AIR_THREADS, 0, st>>>(d_T, d_iq, n_real);
-    if (launches) *launches += 3;
+    if (n_real % 8 || chunk < 64 || chunk % 32 || warm % 32) return cudaErrorInvalidValue;
+    const long long whole = n_real / chunk;
+    const int n_chunks = (int)(whole > 0 ? whole : 1);   // the last chunk takes the remainder
+    float* from48 = d_work;
+    float* upto48 = d_work + (size_t)n_streams * n_chunks;
+    const long long tasks = (long long)((n_streams + 31) / 32) * n_chunks;   // one warp per (32 streams, chunk)
+    float* out = reinterpret_cast<float*>(d_iq);
+    k_airspy_front<<<(unsigned)((tasks + AIRDC_WARPS - 1) / AIRDC_WARPS), 32 * AIRDC_WARPS, 0, st>>>(
+        d_raw, d_state, out, from48, upto48, n_streams, n_real, n_chunks, chunk, warm);
+    k_airspy_fix<<<(n_streams + 31) / 32, 32, 0, st>>>(d_raw, d_state, out, from48, upto48, n_streams, n_real, n_chunks, chunk);
+    if (launches) *launches += 2;
     return cudaGetLastError();
 }
 

@@ -126,7 +126,6 @@ struct sdrb_ctx {
     sdrb_pulse_result* d_pulse = nullptr;
     // Airspy real->IQ front end (inputFormat SDRB_RU16)
     AirspyStreamState* d_air_state = nullptr;
-    float* d_air_T = nullptr;
     cpx* d_air_iq = nullptr;
     float* d_ext_work = nullptr;   // extended chain: removeDC output X and mixed samples M (ssb_ext.cu)
     float* d_agc = nullptr;        // post-AGC samples [streams][blocks][N] between k_ssb_agc and k_ssb_fir
@@ -191,7 +190,7 @@ static void free_buffers(sdrb_ctx* c) {
                      (void**)&c->d_sb, (void**)&c->d_est_scratch, (void**)&c->d_inc1, (void**)&c->d_win,
                      (void**)&c->d_front, (void**)&c->d_fb_tables, (void**)&c->d_fbA,
                      (void**)&c->d_sp_state, (void**)&c->d_au_state, (void**)&c->d_sp_e, (void**)&c->d_sp_f,
-                     (void**)&c->d_au_e, (void**)&c->d_pulse, (void**)&c->d_air_state, (void**)&c->d_air_T,
+                     (void**)&c->d_au_e, (void**)&c->d_pulse, (void**)&c->d_air_state,
                      (void**)&c->d_air_iq, (void**)&c->d_air_work, (void**)&c->d_agc, (void**)&c->d_ext_work};
     for (void** p : ptrs) {
         if (*p) cudaFree(*p);
@@ -708,7 +707,6 @@ static int validate_process(sdrb_ctx* ctx, const void* iq, int n_blocks, unsigne
         const size_t S = (size_t)ctx->n_streams, real = 2 * (size_t)ctx->max_blocks * n;
         CK(cudaMalloc(&ctx->d_air_state, S * sizeof(AirspyStreamState)));
         CK(cudaMemset(ctx->d_air_state, 0, S * sizeof(AirspyStreamState)));
-        CK(cudaMalloc(&ctx->d_air_T, S * (AIRSPY_TAIL + real) * sizeof(float)));
         CK(cudaMalloc(&ctx->d_air_iq, S * (real / 2) * sizeof(cpx)));
         airspy_chunking(&ctx->air_chunk, &ctx->air_warm);
         ctx->air_work_per_stream = airspy_work_floats(1, (long long)real, ctx->air_chunk);
@@ -738,8 +736,7 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
         // then the CF32 kernels.  The intermediate is laid out for THIS call's n_blocks.
         const long long real = 2LL * n_blocks * n;
         cpx* iq_out = ctx->d_air_iq + f0s * n;
-        CK(launch_airspy_front(static_cast<const uint16_t*>(d_iq), ctx->d_air_state + s0,
-                               ctx->d_air_T + (size_t)s0 * (AIRSPY_TAIL + real), iq_out,
+        CK(launch_airspy_front(static_cast<const uint16_t*>(d_iq), ctx->d_air_state + s0, iq_out,
                                ctx->d_air_work + (size_t)s0 * ctx->air_work_per_stream, ctx->air_chunk, ctx->air_warm, ns,
                                real, st, &launches));
         d_iq = iq_out;

@@ -119,7 +119,7 @@ void set_global_error(const char* text);
 
 // ---------------------------------------------------------------- launchers
 // airspy.cu : raw 12-bit real samples (uint16, 2 per complex output) -> cf32 [streams][n_real/2]
-cudaError_t launch_airspy_front(const uint16_t* d_raw, AirspyStreamState* d_state, float* d_T, cpx* d_iq, float* d_work,
+cudaError_t launch_airspy_front(const uint16_t* d_raw, AirspyStreamState* d_state, cpx* d_iq, float* d_work,
                                 int chunk, int warm, int n_streams, long long n_real, cudaStream_t st, int* launches);
 void airspy_chunking(int* chunk, int* warm);
 size_t airspy_work_floats(int n_streams, long long n_real, int chunk);
