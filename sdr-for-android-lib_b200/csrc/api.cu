@@ -110,8 +110,10 @@ struct sdrb_ctx {
     int blue_m = 0;
     cpx *d_sa = nullptr, *d_sb = nullptr;
     cpx* d_fb_tables = nullptr;   // four-step twiddle tables
-    cpx* d_fbA = nullptr;         // four-step intermediate A' (fb_group frames)
+    cpx* d_fbA = nullptr;         // four-step intermediate A' (fb_group frames; fused variant: a ring of fb_slots frames)
     int fb_group = 0;
+    unsigned* d_fb_ctl = nullptr; // fused four-step: ticket + per-frame counters
+    int fb_slots = 0;             // > 0: the fused one-kernel variant is in use
     float* d_est_scratch = nullptr;
     int16_t* d_sine = nullptr;
     uint32_t* d_inc1 = nullptr;
@@ -188,7 +190,7 @@ static void free_buffers(sdrb_ctx* c) {
                      (void**)&c->d_fft_state, (void**)&c->d_ssb_state, &c->d_start,
                      (void**)&c->d_a48, (void**)&c->d_pcm, (void**)&c->d_taps, (void**)&c->d_taps_lin, (void**)&c->d_tapsE, (void**)&c->d_tw, (void**)&c->d_chirp, (void**)&c->d_bf, (void**)&c->d_sa,
                      (void**)&c->d_sb, (void**)&c->d_est_scratch, (void**)&c->d_inc1, (void**)&c->d_win,
-                     (void**)&c->d_front, (void**)&c->d_fb_tables, (void**)&c->d_fbA,
+                     (void**)&c->d_front, (void**)&c->d_fb_tables, (void**)&c->d_fbA, (void**)&c->d_fb_ctl,
                      (void**)&c->d_sp_state, (void**)&c->d_au_state, (void**)&c->d_sp_e, (void**)&c->d_sp_f,
                      (void**)&c->d_au_e, (void**)&c->d_pulse, (void**)&c->d_air_state,
                      (void**)&c->d_air_iq, (void**)&c->d_air_work, (void**)&c->d_agc, (void**)&c->d_ext_work};
@@ -598,7 +600,15 @@ static int ensure_fft_buffers(sdrb_ctx* ctx) {
         if (group > frames) group = frames;
         if (group < frames) group = (size_t)fft_big_best_group(n, (int)group);
         ctx->fb_group = (int)group;
-        CK(cudaMalloc(&ctx->d_fbA, group * (size_t)n * sizeof(cpx)));
+        bool fused = false;   // SDRB_FB_FUSED=1: one persistent kernel, intermediate in an L2-resident ring
+        if (const char* e = getenv("SDRB_FB_FUSED")) fused = atoi(e) != 0;
+        size_t a_frames = group;
+        if (fused) {
+            ctx->fb_slots = fft_big_ring_slots(n);
+            a_frames = (size_t)ctx->fb_slots;
+            CK(cudaMalloc(&ctx->d_fb_ctl, (1 + 2 * group) * sizeof(unsigned)));
+        }
+        CK(cudaMalloc(&ctx->d_fbA, a_frames * (size_t)n * sizeof(cpx)));
         if (ctx->front) CK(cudaMalloc(&ctx->d_front, group * (size_t)n * sizeof(cpx)));
     }
     if (ctx->fftPath == 3 && !ctx->d_chirp) {
@@ -846,8 +856,14 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
                     src = ctx->d_front;
                     src_fmt = FMT_CF32;
                 }
-                CK(launch_fft_big(src_fmt, src, power + (size_t)f0 * n, ctx->d_fbA, ctx->d_fb_tables, n, nf, st));
-                fft_launches += 2;
+                if (ctx->fb_slots) {
+                    CK(launch_fft_big_fused(src_fmt, src, power + (size_t)f0 * n, ctx->d_fbA, ctx->fb_slots, ctx->d_fb_ctl,
+                                            ctx->d_fb_tables, n, nf, st));
+                    fft_launches += 1;
+                } else {
+                    CK(launch_fft_big(src_fmt, src, power + (size_t)f0 * n, ctx->d_fbA, ctx->d_fb_tables, n, nf, st));
+                    fft_launches += 2;
+                }
             }
         } else if (ctx->fftPath == 3) {
             size_t chunk = kGenericScratchBytes / ((size_t)ctx->blue_m * sizeof(cpx));

@@ -10,6 +10,8 @@
 //                   passes, |X|^2 and the shifted store (64-byte segments).
 // Frames are processed in groups sized so that A' (8 N bytes per frame) stays within the 126 MB
 // L2 between the two kernels.
+#include <cstdlib>
+
 #include "fft_big.cuh"
 #include "internal.h"
 
@@ -109,6 +111,102 @@ k_fbB(const cpx* __restrict__ A, float* __restrict__ out, const cpx* __restrict_
     }
 }
 
+// ---- fused persistent variant: both passes in ONE kernel, the intermediate in a small ring that stays in L2.
+// Work items are handed out in order by a ticket counter: step s = the column tiles of frame s (pass A), then the
+// row groups of frame s - delay (pass B).  A row group waits until all column tiles of its frame have been
+// written (a counter per frame, release / acquire at gpu scope); a column tile of frame f waits until every row
+// group of frame f - slots, which used the same ring slot, has been read.  Both waits point at EARLIER tickets,
+// and a ticket is only ever held by a running CTA, so the kernel cannot deadlock whatever the number of CTAs
+// resident.  With the delay at about the number of frames in flight the waits are almost never taken; an
+// intermediate line is read back `delay` steps after it was written (tens of MB of traffic later, not the
+// whole batch), so it is still in L2, and the ring is rewritten in place instead of streaming 8 B per sample
+// out to DRAM and back.  The row-group tile comes in with 16-byte cp.async (generic proxy, L2 only): the
+// writers are other CTAs of the same kernel, so the ordering is plain release / acquire.
+template <int R>
+struct FbFused {
+    typedef FbGeom<R> G;
+    static constexpr int kTiles = G::L / 16;                                     // per frame and pass
+    static constexpr int kElems = G::kElemsA > G::kElemsB ? G::kElemsA : G::kElemsB;
+    static constexpr int kSmem = (kElems + G::kTL) * 8 + 16;
+};
+__device__ __forceinline__ unsigned fb_ld_acquire(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void fb_red_release(unsigned* p) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p) : "memory");
+}
+
+template <int R, int FMT>
+__global__ void __launch_bounds__(FbGeom<R>::kThreads, R == 16 ? 4 : 1)
+k_fb_fused(const typename Ingest2<FMT>::raw_t* __restrict__ in, cpx* __restrict__ ring, float* __restrict__ out,
+           const cpx* __restrict__ tables, unsigned* __restrict__ ctl, int n_frames, int delay, int slots) {
+    typedef FbGeom<R> G;
+    typedef FbFused<R> F;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    cpx* S = reinterpret_cast<cpx*>(smem_raw);
+    cpx* TL = S + F::kElems;
+    int* s_item = reinterpret_cast<int*>(TL + G::kTL);
+    const int t = threadIdx.x;
+    constexpr size_t N = (size_t)G::L * G::L;
+    for (int i = t; i < G::kTL; i += G::kThreads) TL[i] = tables[i];
+    const cpx* TLO = tables + G::kTL;
+    const cpx* THI = TLO + G::kTLO;
+    const cpx* TB = THI + G::kTHI;
+    unsigned* adone = ctl + 1;
+    unsigned* bdone = ctl + 1 + n_frames;
+    const int n_items = (n_frames + delay) * 2 * F::kTiles;
+    // thread 0 draws the NEXT ticket while the current item runs (the atomic's round trip hides under the work)
+    if (t == 0) *s_item = (int)atomicAdd(ctl, 1u);
+    for (;;) {
+        __syncthreads();                         // the ticket is there; the previous item is done with S
+        const int item = *s_item;
+        if (item >= n_items) break;
+        unsigned nxt = 0;
+        if (t == 0) nxt = atomicAdd(ctl, 1u);
+        __syncthreads();                         // everyone has read the ticket
+        struct Publish {                         // the next ticket goes to shared memory when the item ends
+            int* slot; unsigned v; bool on;
+            __device__ ~Publish() { if (on) *slot = (int)v; }
+        } publish{s_item, nxt, t == 0};
+        const int step = item / (2 * F::kTiles), r = item - step * 2 * F::kTiles;
+        if (r < F::kTiles) {
+            const int frame = step;
+            if (frame >= n_frames) continue;
+            if (frame >= slots) {                // the ring slot's previous user has been read
+                if (t == 0)
+                    while (fb_ld_acquire(bdone + frame - slots) < (unsigned)F::kTiles) __nanosleep(64);
+                __syncthreads();
+            }
+            const int n2_0 = r * 16;
+            fbA_pass0<R, FMT>(t, in + (size_t)frame * N, n2_0, TL, S);
+            __syncthreads();
+            fbA_pass1<R>(t, S, TLO, THI, TB, n2_0, ring + (size_t)(frame % slots) * N);
+            __syncthreads();                     // every thread's stores are issued ...
+            if (t == 0) {
+                __threadfence();                 // ... and ordered before the count (cumulativity through the barrier)
+                fb_red_release(adone + frame);
+            }
+        } else {
+            const int frame = step - delay, g = r - F::kTiles;
+            if (frame < 0 || frame >= n_frames) continue;
+            if (t == 0)
+                while (fb_ld_acquire(adone + frame) < (unsigned)F::kTiles) __nanosleep(64);
+            __syncthreads();
+            const cpx* src = ring + (size_t)(frame % slots) * N + (size_t)g * G::kElemsB;
+            for (int i = t; i < G::kElemsB / 2; i += G::kThreads)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(fb_smem_u32(S + 2 * i)), "l"(src + 2 * i) : "memory");
+            asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+            __syncthreads();
+            if (t == 0 && frame + slots < n_frames) fb_red_release(bdone + frame);   // the slot may be rewritten
+            fbB_pass0<R>(t, S, TL);
+            __syncthreads();
+            fbB_pass1<R>(t, S, g * 16, out + (size_t)frame * N);
+        }
+    }
+}
+
 template <int R>
 struct FbSmem {
     static constexpr int kA = (FbGeom<R>::kElemsA + FbGeom<R>::kTL) * 8;
@@ -121,7 +219,10 @@ static cudaError_t fb_prepare_r() {
     if ((e = cudaFuncSetAttribute(k_fbA<R, FMT_CU8>, cudaFuncAttributeMaxDynamicSharedMemorySize, FbSmem<R>::kA)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_fbA<R, FMT_CS16>, cudaFuncAttributeMaxDynamicSharedMemorySize, FbSmem<R>::kA)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_fbA<R, FMT_CF32>, cudaFuncAttributeMaxDynamicSharedMemorySize, FbSmem<R>::kA)) != cudaSuccess) return e;
-    return cudaFuncSetAttribute(k_fbB<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, FbSmem<R>::kB);
+    if ((e = cudaFuncSetAttribute(k_fbB<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, FbSmem<R>::kB)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fb_fused<R, FMT_CU8>, cudaFuncAttributeMaxDynamicSharedMemorySize, FbFused<R>::kSmem)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fb_fused<R, FMT_CS16>, cudaFuncAttributeMaxDynamicSharedMemorySize, FbFused<R>::kSmem)) != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k_fb_fused<R, FMT_CF32>, cudaFuncAttributeMaxDynamicSharedMemorySize, FbFused<R>::kSmem);
 }
 
 cudaError_t fft_big_prepare() {
@@ -183,6 +284,59 @@ static int fb_best_group(int max_group) {
 int fft_big_best_group(int n, int max_group) {
     if (max_group <= 1) return 1;
     return n == 65536 ? fb_best_group<16>(max_group) : (n == 1048576 ? fb_best_group<32>(max_group) : max_group);
+}
+
+// ---- fused variant: ring of `slots` frames, ctl = 1 + 2 n_frames counters (zeroed here, on the stream)
+template <int R, int FMT>
+static cudaError_t fb_launch_fused_f(const void* iq, float* power, cpx* ring, int slots, unsigned* ctl, const cpx* tables,
+                                     int n_frames, int delay, cudaStream_t st) {
+    typedef FbGeom<R> G;
+    typedef FbFused<R> F;
+    static int slots_hw = 0;
+    if (!slots_hw) {
+        int dev = 0, sms = 148, cps = 1;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cps, k_fb_fused<R, FMT>, G::kThreads, F::kSmem) != cudaSuccess || cps < 1) cps = 1;
+        slots_hw = sms * cps;
+    }
+    const long long items = (long long)(n_frames + delay) * 2 * F::kTiles;
+    const int grid = (int)(items < slots_hw ? items : slots_hw);
+    cudaError_t e = cudaMemsetAsync(ctl, 0, (1 + 2 * (size_t)n_frames) * sizeof(unsigned), st);
+    if (e != cudaSuccess) return e;
+    k_fb_fused<R, FMT><<<grid, G::kThreads, F::kSmem, st>>>(static_cast<const typename Ingest2<FMT>::raw_t*>(iq), ring, power,
+                                                             tables, ctl, n_frames, delay, slots);
+    return cudaGetLastError();
+}
+template <int R>
+static cudaError_t fb_launch_fused(int fmt, const void* iq, float* power, cpx* ring, int slots, unsigned* ctl,
+                                   const cpx* tables, int n_frames, cudaStream_t st) {
+    // delay: about the frames in flight (R = 16: 888 CTAs over 32 tiles per step; R = 32: 148 over 128)
+    const char* de = getenv("SDRB_FB_DELAY");   // test hook: a short delay and a small ring force both waits
+    const int delay_env = de ? atoi(de) : 0;
+    int delay = delay_env > 0 ? delay_env : (R == 16 ? 32 : 3);
+    if (delay > n_frames) delay = n_frames;
+    if (delay > slots - 1) delay = slots - 1;      // a column tile may only wait on an EARLIER ticket
+    if (delay < 1 || slots < 2) return cudaErrorInvalidValue;
+    switch (fmt) {
+        case FMT_CU8: return fb_launch_fused_f<R, FMT_CU8>(iq, power, ring, slots, ctl, tables, n_frames, delay, st);
+        case FMT_CS16: return fb_launch_fused_f<R, FMT_CS16>(iq, power, ring, slots, ctl, tables, n_frames, delay, st);
+        case FMT_CF32: return fb_launch_fused_f<R, FMT_CF32>(iq, power, ring, slots, ctl, tables, n_frames, delay, st);
+        default: return cudaErrorInvalidValue;
+    }
+}
+int fft_big_ring_slots(int n) {
+    const char* e = getenv("SDRB_FB_SLOTS");
+    const int env = e ? atoi(e) : 0;
+    if (env >= 2) return env;
+    return n == 65536 ? 80 : 8;
+}
+cudaError_t launch_fft_big_fused(int fmt, const void* iq, float* power, cpx* ring, int slots, unsigned* ctl,
+                                 const cpx* tables, int n, int n_frames, cudaStream_t st) {
+    if (n_frames <= 0) return cudaSuccess;
+    if (n == 65536) return fb_launch_fused<16>(fmt, iq, power, ring, slots, ctl, tables, n_frames, st);
+    if (n == 1048576) return fb_launch_fused<32>(fmt, iq, power, ring, slots, ctl, tables, n_frames, st);
+    return cudaErrorInvalidValue;
 }
 
 // n_frames <= the number of frames the intermediate A holds (the caller loops over groups).

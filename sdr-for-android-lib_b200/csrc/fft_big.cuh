@@ -29,14 +29,14 @@ struct RadixReg;
 template <>
 struct RadixReg<16> {
     static constexpr int kLog2 = 4;
-    SDRB_HD static void fft(cpx* v) { fft16(v); }
-    SDRB_HD static constexpr int slot(int k) { return rev16(k); }
+    SDRB_HD static void fft(cpx* v) { fft_dit<4>(v); }   // FMA-form decimation in time (fft_dit.cuh)
+    SDRB_HD static constexpr int slot(int k) { return dit_slot<4>(k); }
 };
 template <>
 struct RadixReg<32> {
     static constexpr int kLog2 = 5;
-    SDRB_HD static void fft(cpx* v) { fft32(v); }
-    SDRB_HD static constexpr int slot(int k) { return slot32(k); }
+    SDRB_HD static void fft(cpx* v) { fft_dit<5>(v); }
+    SDRB_HD static constexpr int slot(int k) { return dit_slot<5>(k); }
 };
 
 template <int R>

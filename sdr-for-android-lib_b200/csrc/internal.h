@@ -147,6 +147,10 @@ int fft_big_table_elems(int n);
 int fft_big_best_group(int n, int max_group);   // frames per L2-resident group that fill whole waves of the rows kernel
 cudaError_t launch_fft_big(int fmt, const void* iq, float* power, cpx* A, const cpx* tables, int n, int n_frames,
                            cudaStream_t st);
+// fused persistent variant (one kernel, intermediate in an L2-resident ring of `slots` frames; ctl: 1 + 2 n_frames words)
+int fft_big_ring_slots(int n);
+cudaError_t launch_fft_big_fused(int fmt, const void* iq, float* power, cpx* ring, int slots, unsigned* ctl,
+                                 const cpx* tables, int n, int n_frames, cudaStream_t st);
 // estimator.cu
 cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, const EstGeometry& h_geo,
                              FrameLocal* d_local, float* scratch, size_t frame0, int cap_frames, int n_frames,

@@ -496,3 +496,31 @@ def test_db_view_of_the_spectrum(sdrb, gpu_ctx):
     gpu_ctx.process_host(iq, B, sdrb.STAGE_FFT, results=r, power=f32, power_format=sdrb.POWER_DB_F32)
     assert np.abs(f32.astype(np.float64) - want).max() < 1e-3
     assert np.array_equal(gpu_ctx.power_all(), lin)
+
+
+@pytest.mark.parametrize("n,fmt,S,B,hooks", [(65536, 1, 3, 5, {}), (65536, 0, 5, 4, {"SDRB_FB_DELAY": "2", "SDRB_FB_SLOTS": "4"}),
+                                             (65536, 2, 2, 3, {"SDRB_FB_DELAY": "1", "SDRB_FB_SLOTS": "2"}),
+                                             (1048576, 2, 2, 2, {}), (1048576, 1, 3, 2, {"SDRB_FB_DELAY": "1", "SDRB_FB_SLOTS": "2"})])
+def test_four_step_fused_kernel_equals_the_pair(sdrb, monkeypatch, n, fmt, S, B, hooks):
+    """SDRB_FB_FUSED=1: both four-step passes in one persistent kernel, the intermediate in a ring that stays in L2,
+    work handed out by tickets with per-frame counters (fft_big.cu).  Same phase functions, so every bit of every
+    spectrum must equal the two-kernel path's - with the default ring and with a ring of 2-4 frames and a delay of
+    1-2 steps, where a column tile has to wait for its ring slot and a row group for its frame."""
+    fs = 30_720_000 if n == 65536 else 10_000_000
+    cfg = sdrb.Config(FC, fs, n, 25, inputFormat=fmt)
+    iq = make_iq(sdrb, fmt, fs, 3, S, B, n)
+    out = []
+    for fused in ("0", "1"):
+        monkeypatch.setenv("SDRB_FB_FUSED", fused)
+        for k, v in hooks.items():
+            monkeypatch.setenv(k, v)
+        ctx = sdrb.Context(0)                # the switch is read when the FFT buffers are allocated
+        try:
+            ctx.configure(cfg, S, B)
+            for call in range(2):            # the ticket and the counters are reset per call
+                ctx.process(iq, B, sdrb.STAGE_FFT)
+            out.append((ctx.power_all().copy().view(np.uint32), ctx.results().copy()))
+        finally:
+            ctx.close()
+    assert out[0][0].size == S * B * n and np.array_equal(out[0][0], out[1][0])
+    assert np.array_equal(out[0][1], out[1][1])
