@@ -65,7 +65,7 @@ WORKLOADS = {
                   S=256, B=32, n=65536, fs=30_720_000, fmt=CS16, stages=F_FFT, extra={}),
     "c4": dict(what="wideband cf32 61.44 MS/s, 256 SSB channels per stream on a 25 kHz raster, SSB only (BASELINE "
                     "configs[3]; extension stage, no reference code)",
-               S=8, B=32, n=16384, fs=61_440_000, fmt=CF32, stages=F_SSB,
+               S=32, B=32, n=16384, fs=61_440_000, fmt=CF32, stages=F_SSB,
                extra={"ssbChannels": 256, "ssbChannelOffsetHz": -3.2e6, "ssbChannelSpacingHz": 25e3}),
     "c5": dict(what="cf32 10 MS/s, 1048576-pt FFT (four-step) + peak tracking (BASELINE configs[4])",
                S=16, B=4, n=1048576, fs=10_000_000, fmt=CF32, stages=F_FFT, extra={}),

@@ -384,11 +384,12 @@ static int upload_ssb(sdrb_ctx* ctx) {
     CK(cudaMalloc(&ctx->d_taps_lin, 256 * sizeof(float)));
     CK(cudaMemcpy(ctx->d_taps_lin, ctx->taps255, 256 * sizeof(float), cudaMemcpyHostToDevice));
     ctx->ssb_any = ((size_t)ctx->cfg.samplesPerReading * sdrb_format_bytes(ctx->cfg.inputFormat == SDRB_RU16 ? (int)SDRB_CF32 : ctx->cfg.inputFormat)) % 64 != 0;
-    // fused AGC + decimator pass (reference-exact chain only): accumulator count and rotated tap table
+    // fused AGC + decimator pass (both chains): accumulator count and rotated tap table
     if (ctx->d_tapsE) { cudaFree(ctx->d_tapsE); ctx->d_tapsE = nullptr; }
     const int kfmt = ctx->cfg.inputFormat == SDRB_RU16 ? (int)FMT_CF32 : ctx->cfg.inputFormat;
     const char* fe = getenv("SDRB_SSB_FUSED");
-    ctx->ssb_sp = (ctx->ssb_ext || ctx->ssb_any || (fe && fe[0] == '0')) ? 0 : ssb_fused_slots(ctx->ssb, kfmt);
+    ctx->ssb_sp = (ctx->ssb_any || (fe && fe[0] == '0')) ? 0
+                  : (ctx->ssb_ext ? ssb_ext_fused_slots(ctx->ssb) : ssb_fused_slots(ctx->ssb, kfmt));
     if (ctx->ssb_sp > 0) {
         const std::vector<float> te = ssb_fused_tap_table(ctx->taps255, ctx->ssb, ctx->ssb_sp);
         CK(cudaMalloc(&ctx->d_tapsE, te.size() * sizeof(float)));
@@ -657,10 +658,10 @@ static int ensure_ssb_buffers(sdrb_ctx* ctx) {
     const size_t m = ctx->ssb.m > 0 ? ctx->ssb.m : 1;
     if (!ctx->d_a48) CK(cudaMalloc(&ctx->d_a48, frames * m * sizeof(float)));
     if (!ctx->d_pcm) CK(cudaMalloc(&ctx->d_pcm, frames * m * sizeof(int16_t)));
-    // scratch of the split AGC / decimator pair: one float per input sample (and per channel of an NCO bank).  The
-    // reference-exact chain needs it only when the fused pass does not take the decimation factor; the extended
-    // chain always, plus its pre-pass buffers (removeDC output and mixed samples).
-    if (!ctx->d_agc && (ctx->ssb_ext || ctx->ssb_sp == 0)) {
+    // scratch of the split AGC / decimator pair: one float per input sample (and per channel of an NCO bank), needed
+    // only when the fused pass does not take the decimation factor.  The extended chain also has its pre-pass
+    // buffers (removeDC output and mixed samples).
+    if (!ctx->d_agc && ctx->ssb_sp == 0) {
         const size_t bytes = frames * (size_t)ctx->cfg.samplesPerReading * sizeof(float);   // frames includes the channels
         if (cudaMalloc(&ctx->d_agc, bytes) != cudaSuccess) {
             cudaGetLastError();
@@ -767,10 +768,11 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
                           ctx->d_agc ? ctx->d_agc + f0s * (size_t)n : nullptr, ns, n_blocks, ctx->sm_count, ss, &launches));
         } else {
             const size_t C = (size_t)ctx->channels;
-            CK(launch_ssb_ext(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_inc1, ctx->inc2, ctx->cfg.ssbTrueSideband != 0,
+            CK(launch_ssb_ext(fmt, d_iq, ctx->ssb, ctx->d_taps, ctx->d_tapsE, ctx->ssb_sp, ctx->d_inc1, ctx->inc2,
+                              ctx->cfg.ssbTrueSideband != 0,
                               static_cast<float4*>(ctx->d_start) + f0s * C, ctx->d_ssb_state + (size_t)s0 * C,
                               ctx->d_a48 + f0s * C * m, ctx->d_pcm + f0s * C * m,
-                              ctx->d_agc + f0s * C * (size_t)n,
+                              ctx->d_agc ? ctx->d_agc + f0s * C * (size_t)n : nullptr,
                               ctx->d_ext_work + ssb_ext_work_floats(n, s0, ctx->channels, n_blocks, ctx->cfg.ssbTrueSideband != 0),
                               ns, ctx->channels, n_blocks, ctx->ssb_samples, ss, &launches));
         }

@@ -165,6 +165,7 @@ cudaError_t launch_power_view(const float* power, void* out, size_t count, int f
 // d_tapsE the rotated table of the fused pass (ssb_fused_tap_table), sp = ssb_fused_slots (0: split pair).
 int ssb_smax(const SsbParams& P);
 int ssb_fused_slots(const SsbParams& P, int fmt);
+int ssb_ext_fused_slots(const SsbParams& P);   // the same for the extended chain's pass (0: split pair)
 int ssb_fused_rows(const SsbParams& P);
 std::vector<float> ssb_fused_tap_table(const float* h, const SsbParams& P, int sp);
 cudaError_t ssb_prepare();
@@ -178,10 +179,11 @@ cudaError_t launch_ssb_audio(const float* d_a48, const SsbParams& P, SsbStreamSt
                              int n_streams, int n_blocks, cudaStream_t st);
 // ssb_ext.cu : NCO channel bank + Weaver sideband selection (extension stages)
 size_t ssb_ext_work_floats(int n, int S, int C, int B, int true_sideband);   // X (removeDC output) + M (mixed samples)
-cudaError_t launch_ssb_ext(int fmt, const void* iq, const SsbParams& P, const float* d_taps, const uint32_t* d_inc1,
-                           uint32_t inc2, int true_sideband, float4* d_start, SsbStreamState* d_state, float* d_a48,
-                           int16_t* d_pcm, float* d_agc, float* d_work, int n_streams, int channels, int n_blocks,
-                           unsigned long long base_samples, cudaStream_t st, int* launches);
+cudaError_t launch_ssb_ext(int fmt, const void* iq, const SsbParams& P, const float* d_taps, const float* d_tapsE, int sp,
+                           const uint32_t* d_inc1, uint32_t inc2, int true_sideband, float4* d_start,
+                           SsbStreamState* d_state, float* d_a48, int16_t* d_pcm, float* d_agc, float* d_work,
+                           int n_streams, int channels, int n_blocks, unsigned long long base_samples, cudaStream_t st,
+                           int* launches);
 // ssb.cu : 255-tap decimator over post-AGC samples [n_frames][P.n] -> [n_frames][P.m]
 cudaError_t launch_ssb_fir(const float* xagc, const float* taps, float* a48, const SsbParams& P, int n_frames,
                            cudaStream_t st);

@@ -391,13 +391,15 @@ k_ssbx_state2(const float* __restrict__ M, const __grid_constant__ SsbParams P, 
 
 // ---------------------------------------------------------------- pass 2: IIR2 from the recorded state, second mix, AGC
 // One lane per (stream, channel, block).  True sideband: Weaver second mix Re{(yI + j yQ) exp(+/- j theta2)}, doubled;
-// otherwise the reference's demodSSB on {y, y} (USB = y + y, LSB = y - y).  AGC in sweeps (ssb_common.cuh); the
-// post-AGC samples go to xagc [unit][block][n] through a shared-memory tile, k_ssb_fir (ssb.cu) decimates them.
-template <bool TSB, bool CHECK>
+// otherwise the reference's demodSSB on {y, y} (USB = y + y, LSB = y - y).  AGC in sweeps (ssb_common.cuh).
+// SP > 0: the 255-tap decimator runs on the lane as well (LaneDecim<SP>, the fused pass of ssb.cu) and the audio-rate
+// samples go straight to a48 [unit][block][m]; SP = 0 (decimation factors the fused pass does not take): the
+// post-AGC samples go to xagc [unit][block][n] through a shared-memory tile and k_ssb_fir (ssb.cu) decimates them.
+template <bool TSB, bool CHECK, int SP>
 __global__ void __launch_bounds__(SSBX_WARPS * 32)
 k_ssbx_agc(const float* __restrict__ M, const __grid_constant__ SsbParams P, uint32_t inc2,
-           const float4* __restrict__ start, float* __restrict__ xagc, size_t n_frames, int n_blocks,
-           unsigned long long base_samples) {
+           const float4* __restrict__ start, float* __restrict__ xagc, const float* __restrict__ tapsE, int rows,
+           float* __restrict__ a48, size_t n_frames, int n_blocks, unsigned long long base_samples) {
     extern __shared__ __align__(16) unsigned char smem[];
     constexpr int E = TSB ? 2 : 1, NS = 16 / E;       // samples per 64-byte chunk of M
     constexpr int OP = NS + 4;
@@ -411,6 +413,9 @@ k_ssbx_agc(const float* __restrict__ M, const __grid_constant__ SsbParams P, uin
     const size_t b = vfc % n_blocks;
     const size_t block_bytes = (size_t)P.n * E * sizeof(float);
     rows_all[warp][lane] = reinterpret_cast<const unsigned char*>(M) + vfc * block_bytes;
+    float* hT = reinterpret_cast<float*>(smem + SSBX_WARPS * SSB_MAIN_STAGES * SSB_TILE_BYTES);
+    if (SP > 0)
+        for (int i = threadIdx.x; i < SP * rows * SP; i += blockDim.x) hT[i] = tapsE[i];
     __syncthreads();
     if (vf0 >= n_frames) return;
     TileStreamX<SSB_MAIN_STAGES> ts = {rows_all[warp], smem + warp * SSB_MAIN_STAGES * SSB_TILE_BYTES, lane};
@@ -423,6 +428,9 @@ k_ssbx_agc(const float* __restrict__ M, const __grid_constant__ SsbParams P, uin
     const float omFast = __fsub_rn(1.0f, P.agcFast), omSlow = __fsub_rn(1.0f, P.agcSlow);
     float* tile = s_out[warp];
     constexpr int LPR = NS / 4, RPI = 32 / LPR;
+    LaneDecim<(SP > 0 ? SP : 1)> dec;
+    dec.init(P);
+    float* out = a48 + vfc * (size_t)P.m;
     ts.prologue(nchunks);
     for (int c = 0; c < nchunks; c++) {
         ts.advance(c, nchunks);
@@ -457,6 +465,13 @@ k_ssbx_agc(const float* __restrict__ M, const __grid_constant__ SsbParams P, uin
             }
         }
         ssb_agc_sweeps<NS, CHECK>(a, P, omFast, omSlow, gain);
+        if (SP > 0) {
+            float v;
+            int j;
+            if (dec.template feed<NS>(a, c, hT, rows, P, v, j) && live && j < P.m) out[j] = v;
+            __syncwarp();
+            continue;
+        }
         float4* mine = reinterpret_cast<float4*>(tile + lane * OP);
 #pragma unroll
         for (int k = 0; k < LPR; k++) mine[k] = make_float4(a[4 * k], a[4 * k + 1], a[4 * k + 2], a[4 * k + 3]);
@@ -480,9 +495,10 @@ size_t ssb_ext_work_floats(int n, int S, int C, int B, int true_sideband) {
 }
 
 template <int FMT, bool TSB>
-static cudaError_t launch_ssbx_f(const void* iq, const SsbParams& P, const float* d_taps, const uint32_t* d_inc1,
-                                 uint32_t inc2, float4* d_start, SsbStreamState* d_state, float* d_a48, float* d_agc,
-                                 float* d_work, int S, int C, int B, unsigned long long base, cudaStream_t st) {
+static cudaError_t launch_ssbx_f(const void* iq, const SsbParams& P, const float* d_taps, const float* d_tapsE, int sp,
+                                 const uint32_t* d_inc1, uint32_t inc2, float4* d_start, SsbStreamState* d_state,
+                                 float* d_a48, float* d_agc, float* d_work, int S, int C, int B, unsigned long long base,
+                                 cudaStream_t st) {
     const size_t nv = (size_t)S * C, nvf = nv * B, span = (size_t)B * P.n;
     float2* X = reinterpret_cast<float2*>(d_work);
     float* M = d_work + (size_t)S * span * 2;
@@ -509,27 +525,47 @@ static cudaError_t launch_ssbx_f(const void* iq, const SsbParams& P, const float
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     if (P.m <= 0) return cudaSuccess;
     constexpr bool CHECK = FMT == FMT_CF32;
-    if ((e = cudaFuncSetAttribute(k_ssbx_agc<TSB, CHECK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem)) != cudaSuccess) return e;
     const unsigned agrid = (unsigned)((nvf + SSBX_WARPS * 32 - 1) / (SSBX_WARPS * 32));
-    k_ssbx_agc<TSB, CHECK><<<agrid, SSBX_WARPS * 32, tsmem, st>>>(M, P, inc2, d_start, d_agc, nvf, B, base);
+    const int rows = ssb_fused_rows(P);
+#define SDRB_AGC(SPV)                                                                                                  \
+    {                                                                                                                  \
+        const size_t sm = tsmem + (size_t)(SPV) * rows * (SPV) * sizeof(float);                                        \
+        if ((e = cudaFuncSetAttribute(k_ssbx_agc<TSB, CHECK, SPV>, cudaFuncAttributeMaxDynamicSharedMemorySize,        \
+                                      (int)sm)) != cudaSuccess)                                                        \
+            return e;                                                                                                  \
+        k_ssbx_agc<TSB, CHECK, SPV><<<agrid, SSBX_WARPS * 32, sm, st>>>(M, P, inc2, d_start, d_agc, d_tapsE, rows, d_a48,  \
+                                                                        nvf, B, base);                                 \
+    }
+    switch (sp) {
+        case 0: SDRB_AGC(0) break;
+        case 1: SDRB_AGC(1) break;
+        case 2: SDRB_AGC(2) break;
+        case 4: SDRB_AGC(4) break;
+        default: return cudaErrorInvalidValue;   // ssb_ext_fused_slots() stops at 4
+    }
+#undef SDRB_AGC
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (sp > 0) return cudaSuccess;
+    if (!d_agc) return cudaErrorMemoryAllocation;
     return launch_ssb_fir(d_agc, d_taps, d_a48, P, (int)nvf, st);
 }
 
-// d_agc: [S * C * B][n] floats, d_work: ssb_ext_work_floats() floats -- both required
-cudaError_t launch_ssb_ext(int fmt, const void* iq, const SsbParams& P, const float* d_taps, const uint32_t* d_inc1,
-                           uint32_t inc2, int true_sideband, float4* d_start, SsbStreamState* d_state, float* d_a48,
-                           int16_t* d_pcm, float* d_agc, float* d_work, int n_streams, int channels, int n_blocks,
-                           unsigned long long base_samples, cudaStream_t st, int* launches) {
+// d_work: ssb_ext_work_floats() floats; sp > 0 (ssb_ext_fused_slots): d_tapsE is the rotated tap table and d_agc is
+// not used; sp = 0: d_agc [S * C * B][n] floats is required
+cudaError_t launch_ssb_ext(int fmt, const void* iq, const SsbParams& P, const float* d_taps, const float* d_tapsE, int sp,
+                           const uint32_t* d_inc1, uint32_t inc2, int true_sideband, float4* d_start,
+                           SsbStreamState* d_state, float* d_a48, int16_t* d_pcm, float* d_agc, float* d_work,
+                           int n_streams, int channels, int n_blocks, unsigned long long base_samples, cudaStream_t st,
+                           int* launches) {
     if (n_streams <= 0 || channels <= 0 || n_blocks <= 0) return cudaSuccess;
-    if (!d_agc || !d_work) return cudaErrorMemoryAllocation;
+    if (!d_work || (sp == 0 && !d_agc) || (sp > 0 && !d_tapsE)) return cudaErrorMemoryAllocation;
     if ((size_t)n_streams * channels * n_blocks >= (1ull << 31)) return cudaErrorInvalidValue;
     cudaError_t e;
 #define SDRB_X(F)                                                                                                      \
-    (true_sideband ? launch_ssbx_f<F, true>(iq, P, d_taps, d_inc1, inc2, d_start, d_state, d_a48, d_agc, d_work, n_streams, \
-                                            channels, n_blocks, base_samples, st)                                      \
-                   : launch_ssbx_f<F, false>(iq, P, d_taps, d_inc1, inc2, d_start, d_state, d_a48, d_agc, d_work, n_streams, \
-                                             channels, n_blocks, base_samples, st))
+    (true_sideband ? launch_ssbx_f<F, true>(iq, P, d_taps, d_tapsE, sp, d_inc1, inc2, d_start, d_state, d_a48, d_agc,  \
+                                            d_work, n_streams, channels, n_blocks, base_samples, st)                   \
+                   : launch_ssbx_f<F, false>(iq, P, d_taps, d_tapsE, sp, d_inc1, inc2, d_start, d_state, d_a48, d_agc, \
+                                             d_work, n_streams, channels, n_blocks, base_samples, st))
     switch (fmt) {
         case FMT_CU8: e = SDRB_X(FMT_CU8); break;
         case FMT_CS16: e = SDRB_X(FMT_CS16); break;
@@ -538,7 +574,7 @@ cudaError_t launch_ssb_ext(int fmt, const void* iq, const SsbParams& P, const fl
     }
 #undef SDRB_X
     if (e != cudaSuccess) return e;
-    if (launches) *launches += P.m > 0 ? 5 : 3;
+    if (launches) *launches += P.m > 0 ? (sp > 0 ? 4 : 5) : 3;
     if (P.m > 0) {
         e = launch_ssb_audio(d_a48, P, d_state, d_pcm, n_streams * channels, n_blocks, st);
         if (launches) (*launches)++;
