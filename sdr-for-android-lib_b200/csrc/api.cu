@@ -1017,6 +1017,14 @@ int sdrb_process_host_ex(sdrb_ctx* ctx, const void* iq_host, int n_blocks, unsig
     cudaStream_t st = ctx->stream;
     CK(cudaStreamSynchronize(st));                                  // earlier work on the compute stream
     ctx->ev_valid = false;
+    // An SSB chain with a carried-state pass (several readings per call, or the extended chain) is not cut into
+    // chunks: that pass is one latency-bound warp per 32 chains and takes the same time for 32 streams as for 256, so
+    // every chunk would pay it in full (C3: 8 chunks, 315 ms per call against 41 ms of kernels).  The chunks carry the
+    // copies and the FFT chain; the SSB chain runs once, over all streams, when the last chunk is in, and its PCM goes
+    // out behind it.  One reading per call has no state pass (the fused kernel carries the state) and stays chunked.
+    const unsigned whole = (ctx->ssb_ext || n_blocks > 1) ? (stages & (SDRB_STAGE_SSB | SDRB_STAGE_AUDIO_PULSE)) : 0u;
+    const unsigned chunk_stages = stages & ~whole;
+    int last_in = -1;
     for (int c = 0; c < chunks; c++) {
         const int s0 = (int)((long long)S * c / chunks), s1 = (int)((long long)S * (c + 1) / chunks);
         const int ns = s1 - s0;
@@ -1026,8 +1034,10 @@ int sdrb_process_host_ex(sdrb_ctx* ctx, const void* iq_host, int n_blocks, unsig
         CK(cudaMemcpyAsync(d_chunk, static_cast<const unsigned char*>(iq_host) + s0 * stream_in, ns * stream_in,
                            cudaMemcpyHostToDevice, ctx->s_in));
         CK(cudaEventRecord(ctx->ev_in[c], ctx->s_in));
+        last_in = c;
+        if (!chunk_stages) continue;
         CK(cudaStreamWaitEvent(st, ctx->ev_in[c], 0));
-        if ((rc = run_streams(ctx, d_chunk, s0, ns, n_blocks, stages, st, false)) != SDRB_OK) return rc;
+        if ((rc = run_streams(ctx, d_chunk, s0, ns, n_blocks, chunk_stages, st, false)) != SDRB_OK) return rc;
         CK(cudaEventRecord(ctx->ev_done[c], st));
         CK(cudaStreamWaitEvent(ctx->s_out, ctx->ev_done[c], 0));
         if ((stages & SDRB_STAGE_FFT) && results_out)
@@ -1045,9 +1055,18 @@ int sdrb_process_host_ex(sdrb_ctx* ctx, const void* iq_host, int n_blocks, unsig
         } else if ((stages & SDRB_STAGE_FFT) && power_out)
             CK(cudaMemcpyAsync(static_cast<float*>(power_out) + f0 * n, ctx->d_power + f0 * n, nf * n * sizeof(float),
                                cudaMemcpyDeviceToHost, ctx->s_out));
-        if ((stages & SDRB_STAGE_SSB) && pcm_out && m)
+        if ((chunk_stages & SDRB_STAGE_SSB) && pcm_out && m)
             CK(cudaMemcpyAsync(pcm_out + f0 * m * ctx->channels, ctx->d_pcm + f0 * m * ctx->channels,
                                nf * m * ctx->channels * sizeof(int16_t), cudaMemcpyDeviceToHost, ctx->s_out));
+    }
+    if (whole && last_in >= 0) {
+        CK(cudaStreamWaitEvent(st, ctx->ev_in[last_in], 0));        // the copies are in order on s_in: all chunks are in
+        if ((rc = run_streams(ctx, ctx->d_in, 0, S, n_blocks, whole, st, false)) != SDRB_OK) return rc;
+        CK(cudaEventRecord(ctx->ev_done[0], st));
+        CK(cudaStreamWaitEvent(ctx->s_out, ctx->ev_done[0], 0));
+        if (pcm_out && m)
+            CK(cudaMemcpyAsync(pcm_out, ctx->d_pcm, (size_t)S * n_blocks * m * ctx->channels * sizeof(int16_t),
+                               cudaMemcpyDeviceToHost, ctx->s_out));
     }
     ctx->last_blocks = n_blocks;
     ctx->last_stages |= stages;

@@ -81,3 +81,35 @@ def test_ssb_extended_state_round_trip(sdrb, gpu_ctx):
     gpu_ctx.load_state(blob)
     gpu_ctx.process(np.ascontiguousarray(iq[:, B:]), B, sdrb.STAGE_SSB)
     assert np.array_equal(gpu_ctx.pcm(), want)
+
+
+@pytest.mark.parametrize("stages", ["both", "ssb"])
+def test_ssb_extended_chain_host_call_equals_plain_call(sdrb, gpu_ctx, stages):
+    """sdrb_process_host with the extended chain: the chunks carry the copies and the FFT chain, the SSB chain runs
+    once over all streams behind the last chunk (its state pass costs the same for 3 streams as for 300) - the
+    payloads must be those of the plain call, over two calls (carried filter state and NCO phase)."""
+    fs, n, S, B, C = 2_000_000, 16384, 11, 3, 3
+    cfg = sdrb.Config(FC, fs, n, 5, inputFormat=0, ssbTrueSideband=1, ssbChannels=C, ssbChannelOffsetHz=-25_000.0,
+                      ssbChannelSpacingHz=25_000.0)
+    st = (sdrb.STAGE_FFT | sdrb.STAGE_SSB) if stages == "both" else sdrb.STAGE_SSB
+    iq = make_iq(sdrb, 0, fs, 70, S, 2 * B, n)
+    gpu_ctx.configure(cfg, S, B)
+    m = gpu_ctx.pcm_per_block
+    want = []
+    for call in range(2):
+        gpu_ctx.process(np.ascontiguousarray(iq[:, call * B:(call + 1) * B]), B, st)
+        want.append((gpu_ctx.pcm().copy(), gpu_ctx.results().copy() if stages == "both" else None,
+                     gpu_ctx.power_all().copy() if stages == "both" else None))
+    gpu_ctx.configure(cfg, S, B)            # fresh state
+    for call in range(2):
+        r2 = np.zeros((S, B), dtype=sdrb.RESULT_DTYPE)
+        p2 = np.zeros((S, B, n), dtype=np.float32)
+        c2 = np.zeros((S, C, B, m), dtype=np.int16)
+        blk = np.ascontiguousarray(iq[:, call * B:(call + 1) * B])
+        if stages == "both":
+            gpu_ctx.process_host(blk, B, st, results=r2, power=p2, pcm=c2)
+            assert np.array_equal(r2, want[call][1]) and np.array_equal(p2.reshape(-1), want[call][2].reshape(-1))
+        else:
+            gpu_ctx.process_host(blk, B, st, pcm=c2)
+        assert np.array_equal(c2.reshape(-1), want[call][0].reshape(-1)), call
+    assert np.abs(c2).max() > 100
