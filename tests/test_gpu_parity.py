@@ -524,3 +524,50 @@ def test_four_step_fused_kernel_equals_the_pair(sdrb, monkeypatch, n, fmt, S, B,
             ctx.close()
     assert out[0][0].size == S * B * n and np.array_equal(out[0][0], out[1][0])
     assert np.array_equal(out[0][1], out[1][1])
+
+
+def test_full_size_properties_default_workload(sdrb):
+    """The bench's default workload at full size (65536 u8 streams x one reading of 16384, FFT + peak + strength + USB
+    demod, the fused one-kernel SSB pass beside the FFT chain): 24 streams spread over the batch against the oracle
+    (records from the GPU's own spectrum, PCM bit for bit), Parseval on the same streams, the first 1000 streams
+    against a 1000-stream context (batch independence at full size), and checksums stable across two runs."""
+    import torch
+    S, n, fs = 65536, 16384, 2_000_000
+    cfg = sdrb.Config(FC, fs, n, 5, inputFormat=0)
+    ctx = sdrb.Context(0)
+    small = sdrb.Context(0)
+    try:
+        ctx.configure(cfg, S, 1)
+        d = torch.empty((S, 1, n, 2), dtype=torch.uint8, device="cuda")
+        ctx.synth_device(0, fs, 0, S, 0, n, d.data_ptr())
+        st = sdrb.STAGE_FFT | sdrb.STAGE_SSB
+        ctx.process(d, 1, st)
+        ctx.sync()
+        res, pcm = ctx.results().copy(), ctx.pcm().copy()
+        m = ctx.pcm_per_block
+        assert pcm.shape == (S, 1, m) and m > 300
+        picks = [(k * 2731 + 5) % S for k in range(24)]
+        for s in picks:
+            raw = d[s, 0].cpu().numpy()
+            x = ol.to_cf32(raw, 0)
+            exp = ol.OracleSsb().process(x, fs, 1, 1)
+            assert np.array_equal(pcm[s, 0], exp), s                       # first block from a zero state: exact
+            p = ctx.power(s, 0)
+            check_results(res[s, 0], ol.OracleFft(FC, fs, n, 5).evaluate(p), 0, ("default", s))
+            e = float((x.astype(np.float64) ** 2).sum()) * n
+            assert abs(float(p.astype(np.float64).sum()) - e) <= 2e-5 * e
+        small.configure(cfg, 1000, 1)
+        small.process(d[:1000], 1, st)
+        small.sync()
+        assert np.array_equal(small.results(), res[:1000]) and np.array_equal(small.pcm(), pcm[:1000])
+        chk = (int(res["peakBin"].astype(np.int64).sum()), int(pcm.astype(np.int64).sum()),
+               int(np.bitwise_xor.reduce(pcm.reshape(-1).view(np.uint16).astype(np.uint32))))
+        ctx.reset_state()
+        ctx.process(d, 1, st)
+        ctx.sync()
+        res2, pcm2 = ctx.results(), ctx.pcm()
+        assert chk == (int(res2["peakBin"].astype(np.int64).sum()), int(pcm2.astype(np.int64).sum()),
+                       int(np.bitwise_xor.reduce(pcm2.reshape(-1).view(np.uint16).astype(np.uint32))))
+    finally:
+        small.close()
+        ctx.close()
