@@ -16,7 +16,7 @@
 // inc * samples-since-reset), so it is hoisted out of the sequential lane:
 //   k_ssbx_dc    : one lane per (stream, block): removeDC (complex, a 2-operation chain) -> X [stream][block][n] cf32
 //   k_ssbx_mix   : one thread per 4 samples of a (stream, channel): NCO + first mix -> M [stream][channel][block][n]
-//                  (re only, or (re, im) pairs with true sideband)
+//                  (re only; with true sideband planar: the re row of a unit, then its im row)
 //   k_ssbx_state : one lane per CHAIN (the I filter of a (stream, channel), and its Q filter with true sideband),
 //                  blocks in order: IIR2 on M only (9 operations per sample, a 20-cycle chain) -- it was 64
 //                  instructions and 89 cycles per sample with DC, NCO and mix on the lane -- records the exact filter
@@ -39,6 +39,7 @@ struct TileStreamX {
     unsigned char* tile;                  // this warp's tiles
     int lane;
     const unsigned char* rp[4];           // the four rows this lane copies, in registers (bind())
+    size_t stride = SSB_ROW_BYTES;        // source bytes between consecutive chunks of a row
     // Fetching the pointers from shared memory at every chunk put four dependent LDS.64 -> LDGSTS pairs (all through
     // one register, so in series) in front of every chunk: ~300 cycles on the lone in-order warp of a state pass.
     __device__ __forceinline__ void bind() {
@@ -51,7 +52,7 @@ struct TileStreamX {
         unsigned char* t = tile + stage * SSB_TILE_BYTES + sub * 16;
 #pragma unroll
         for (int k = 0; k < 4; k++)
-            cp_async16(t + (r0 + 8 * k) * SSB_ROW_PITCH, rp[k] + (size_t)chunk * SSB_ROW_BYTES);
+            cp_async16(t + (r0 + 8 * k) * SSB_ROW_PITCH, rp[k] + (size_t)chunk * stride);
         cp_async_commit();
     }
     __device__ __forceinline__ const uint4* row(int stage) const {
@@ -195,10 +196,9 @@ k_ssbx_mix(const float2* __restrict__ X, const uint32_t* __restrict__ inc1_tab, 
             mr[j] = __fadd_rn(__fmul_rn(xr[j], c1), __fmul_rn(xi[j], s1));
             if (TSB) mi[j] = __fsub_rn(__fmul_rn(xi[j], c1), __fmul_rn(xr[j], s1));
         }
-        if (TSB) {
-            float4* o = reinterpret_cast<float4*>(M + (v * span + k) * 2);
-            o[0] = make_float4(mr[0], mi[0], mr[1], mi[1]);
-            o[1] = make_float4(mr[2], mi[2], mr[3], mi[3]);
+        if (TSB) {   // planar: the I row of a unit, then its Q row -- every chain of the state pass owns a contiguous row
+            *reinterpret_cast<float4*>(M + (2 * v) * span + k) = make_float4(mr[0], mr[1], mr[2], mr[3]);
+            *reinterpret_cast<float4*>(M + (2 * v + 1) * span + k) = make_float4(mi[0], mi[1], mi[2], mi[3]);
         } else {
             *reinterpret_cast<float4*>(M + v * span + k) = make_float4(mr[0], mr[1], mr[2], mr[3]);
         }
@@ -224,8 +224,8 @@ k_ssbx_state(const float* __restrict__ M, const __grid_constant__ SsbParams P, f
     const size_t chc = live ? ch : n_chains - 1;
     const size_t v = chc / E;
     const int comp = (int)(chc % E);
-    const size_t block_bytes = (size_t)P.n * E * sizeof(float);
-    rows[lane] = reinterpret_cast<const unsigned char*>(M) + v * block_bytes * n_blocks;
+    const size_t block_bytes = (size_t)P.n * sizeof(float);                 // of one chain: M is planar (I row, Q row)
+    rows[lane] = reinterpret_cast<const unsigned char*>(M) + chc * block_bytes * n_blocks;
     __syncwarp();
     TileStreamX<SSBX_STATE_STAGES> ts = {rows, smem, lane};
     ts.bind();
@@ -268,13 +268,8 @@ k_ssbx_state(const float* __restrict__ M, const __grid_constant__ SsbParams P, f
         }
 #pragma unroll
         for (int q = 0; q < 4; q++) {
-            if (TSB) {
-                ssbx_iir(P.rf, comp ? d[q].y : d[q].x, z1, z2);
-                ssbx_iir(P.rf, comp ? d[q].w : d[q].z, z1, z2);
-            } else {
-                ssbx_iir(P.rf, d[q].x, z1, z2); ssbx_iir(P.rf, d[q].y, z1, z2);
-                ssbx_iir(P.rf, d[q].z, z1, z2); ssbx_iir(P.rf, d[q].w, z1, z2);
-            }
+            ssbx_iir(P.rf, d[q].x, z1, z2); ssbx_iir(P.rf, d[q].y, z1, z2);
+            ssbx_iir(P.rf, d[q].z, z1, z2); ssbx_iir(P.rf, d[q].w, z1, z2);
         }
         __syncwarp();
         if (++cb == chunks_per_block) cb = 0;
@@ -304,7 +299,7 @@ k_ssbx_state2(const float* __restrict__ M, const __grid_constant__ SsbParams P, 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const size_t n_chains = n_units * E;
     const size_t ch0 = (size_t)blockIdx.x * 32;
-    const size_t block_bytes = (size_t)P.n * E * sizeof(float);
+    const size_t block_bytes = (size_t)P.n * sizeof(float);                 // of one chain: M is planar (I row, Q row)
     const int chunks_per_block = (int)(block_bytes / SSB_ROW_BYTES);
     const int ngroups = chunks_per_block * n_blocks / K;
     if (warp == 0) {
@@ -315,7 +310,7 @@ k_ssbx_state2(const float* __restrict__ M, const __grid_constant__ SsbParams P, 
         for (int j = 0; j < 4; j++) {
             size_t ch = ch0 + r0 + 8 * j;
             if (ch >= n_chains) ch = n_chains - 1;
-            rp[j] = reinterpret_cast<const unsigned char*>(M) + (ch / E) * block_bytes * n_blocks + sub * 16;
+            rp[j] = reinterpret_cast<const unsigned char*>(M) + ch * block_bytes * n_blocks + sub * 16;
         }
         for (int gi = 0; gi < ngroups + D; gi++) {
             if (gi < ngroups) {
@@ -338,7 +333,18 @@ k_ssbx_state2(const float* __restrict__ M, const __grid_constant__ SsbParams P, 
             }
         }
     } else {
-        // ---- chain
+        // ---- chain.  Everything that is not one of the nine operations per sample costs this in-order warp issue
+        // cycles the chain cannot use (ncu, round 2: 9.5 of its 28.4 cycles per sample were the per-chunk block-start
+        // test with its convergence barriers, the re / im select per sample, constant-bank reloads of the
+        // coefficients and the wait for the group's shared-memory loads).  So: blocks are the outer loop (a block is a
+        // whole number of group pairs: checked by the launcher), M is planar so a Q chain reads its own row (no select,
+        // and a scalar load per sample would cost ~4 issue cycles each), the NEXT group's values are loaded before the
+        // current group's chain runs
+        // (two register sets, loop unrolled by two), and the coefficients come from shared memory once.
+        __shared__ float s_coef[5];
+        if (lane == 0) { s_coef[0] = P.rf.a0; s_coef[1] = P.rf.a1; s_coef[2] = P.rf.a2; s_coef[3] = P.rf.b1; s_coef[4] = P.rf.b2; }
+        __syncwarp();
+        const BiquadCoef rf = {s_coef[0], s_coef[1], s_coef[2], s_coef[3], s_coef[4]};
         const size_t ch = ch0 + lane;
         const bool live = ch < n_chains;
         const size_t chc = live ? ch : n_chains - 1;
@@ -346,40 +352,46 @@ k_ssbx_state2(const float* __restrict__ M, const __grid_constant__ SsbParams P, 
         const int comp = (int)(chc % E);
         float z1 = comp ? state[v].pad0 : state[v].rf_z1, z2 = comp ? state[v].pad1 : state[v].rf_z2;
         float2* sp = reinterpret_cast<float2*>(start) + (v * n_blocks) * 2 + comp;
-        int cb = 0;
-        for (int gi = 0; gi < ngroups; gi++) {
+        constexpr int NV = K * 16;                                          // samples of a group on this lane
+        const unsigned lane_base = (unsigned)__cvta_generic_to_shared(smem) + lane * SSB_ROW_PITCH;
+        auto take = [&](int gi, float (&x)[NV]) {                           // group gi: wait, load, hand the slot back
             const int slot = gi & (G - 1);
             named_bar_sync_x(1 + slot, 64);                                 // slot full
-            const unsigned char* t = smem + (size_t)slot * K * SSB_TILE_BYTES + lane * SSB_ROW_PITCH;
-            float4 d[K][4];
+            const unsigned t = lane_base + (unsigned)slot * K * SSB_TILE_BYTES;
 #pragma unroll
-            for (int k = 0; k < K; k++)
+            for (int k = 0; k < K; k++) {
 #pragma unroll
-                for (int q = 0; q < 4; q++) d[k][q] = lds128_now(reinterpret_cast<const float4*>(t + k * SSB_TILE_BYTES) + q);
+                for (int q = 0; q < 4; q++)
+                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                 : "=f"(x[16 * k + 4 * q]), "=f"(x[16 * k + 4 * q + 1]), "=f"(x[16 * k + 4 * q + 2]),
+                                   "=f"(x[16 * k + 4 * q + 3])
+                                 : "r"(t + k * SSB_TILE_BYTES + 16 * q));
+            }
             if (gi + G < ngroups) {
                 __threadfence_block();                                      // the loads are done before the slot is handed back
                 named_bar_arrive_x(1 + G + slot, 64);
             }
+        };
+        auto run = [&](const float (&x)[NV]) {
 #pragma unroll
-            for (int k = 0; k < K; k++) {
-                if (cb == 0) {
-                    if (live) {
-                        sp[0] = make_float2(z1, z2);
-                        if (!TSB) sp[1] = make_float2(0.0f, 0.0f);
-                    }
-                    sp += 2;
-                }
-#pragma unroll
-                for (int q = 0; q < 4; q++) {
-                    if (TSB) {
-                        ssbx_iir(P.rf, comp ? d[k][q].y : d[k][q].x, z1, z2);
-                        ssbx_iir(P.rf, comp ? d[k][q].w : d[k][q].z, z1, z2);
-                    } else {
-                        ssbx_iir(P.rf, d[k][q].x, z1, z2); ssbx_iir(P.rf, d[k][q].y, z1, z2);
-                        ssbx_iir(P.rf, d[k][q].z, z1, z2); ssbx_iir(P.rf, d[k][q].w, z1, z2);
-                    }
-                }
-                if (++cb == chunks_per_block) cb = 0;
+            for (int i = 0; i < NV; i++) ssbx_iir(rf, x[i], z1, z2);
+        };
+        const int pairs_per_block = chunks_per_block / (2 * K);
+        float xa[NV], xb[NV];
+        int gi = 0;
+        take(0, xa);
+        for (int b = 0; b < n_blocks; b++) {
+            if (live) {
+                sp[0] = make_float2(z1, z2);                                // the exact state at the block's first sample
+                if (!TSB) sp[1] = make_float2(0.0f, 0.0f);
+            }
+            sp += 2;
+            for (int pr = 0; pr < pairs_per_block; pr++) {
+                take(gi + 1, xb);                                           // (a block is a whole number of pairs)
+                run(xa);
+                if (gi + 2 < ngroups) take(gi + 2, xa);
+                run(xb);
+                gi += 2;
             }
         }
         if (live) {
@@ -411,8 +423,10 @@ k_ssbx_agc(const float* __restrict__ M, const __grid_constant__ SsbParams P, uin
     const bool live = vf < n_frames;
     const size_t vfc = live ? vf : n_frames - 1;
     const size_t b = vfc % n_blocks;
-    const size_t block_bytes = (size_t)P.n * E * sizeof(float);
-    rows_all[warp][lane] = reinterpret_cast<const unsigned char*>(M) + vfc * block_bytes;
+    const size_t block_bytes = (size_t)P.n * E * sizeof(float);   // input bytes per (unit, block)
+    // true sideband: M is planar per unit (I row, then Q row, each n_blocks * n floats); the lane's I block starts at
+    // row 2 u, block b = element (2 vf - b) n; its Q block lies one row (n_blocks * n floats) further
+    rows_all[warp][lane] = reinterpret_cast<const unsigned char*>(M) + (TSB ? 2 * vfc - b : vfc) * (size_t)P.n * sizeof(float);
     float* hT = reinterpret_cast<float*>(smem + SSBX_WARPS * SSB_MAIN_STAGES * SSB_TILE_BYTES);
     if (SP > 0)
         for (int i = threadIdx.x; i < SP * rows * SP; i += blockDim.x) hT[i] = tapsE[i];
@@ -420,6 +434,13 @@ k_ssbx_agc(const float* __restrict__ M, const __grid_constant__ SsbParams P, uin
     if (vf0 >= n_frames) return;
     TileStreamX<SSB_MAIN_STAGES> ts = {rows_all[warp], smem + warp * SSB_MAIN_STAGES * SSB_TILE_BYTES, lane};
     ts.bind();
+    if (TSB) {   // a chunk = 32 bytes of the I row (tile bytes 0..31) + 32 bytes of the Q row (32..63)
+        const int sub = lane & 3, r0 = lane >> 2;
+        const size_t qoff = (size_t)n_blocks * P.n * sizeof(float);
+#pragma unroll
+        for (int k = 0; k < 4; k++) ts.rp[k] = rows_all[warp][r0 + 8 * k] + (sub >> 1) * qoff + (sub & 1) * 16;
+        ts.stride = SSB_ROW_BYTES / 2;
+    }
     const int nchunks = (int)(block_bytes / SSB_ROW_BYTES);
     const float4 s0 = start[vfc];
     float iz1 = s0.x, iz2 = s0.y, qz1 = s0.z, qz2 = s0.w;
@@ -440,21 +461,25 @@ k_ssbx_agc(const float* __restrict__ M, const __grid_constant__ SsbParams P, uin
 #pragma unroll
         for (int q = 0; q < 4; q++) dd[q] = lds128_now(row + q);
         float a[NS];
+        if (TSB) {
+            const float xi[8] = {dd[0].x, dd[0].y, dd[0].z, dd[0].w, dd[1].x, dd[1].y, dd[1].z, dd[1].w};
+            const float xq[8] = {dd[2].x, dd[2].y, dd[2].z, dd[2].w, dd[3].x, dd[3].y, dd[3].z, dd[3].w};
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const float yi = ssbx_iir(P.rf, xi[j], iz1, iz2);
+                const float yq = ssbx_iir(P.rf, xq[j], qz1, qz2);
+                float c2, s2;
+                nco_cs(ph2, c2, s2);
+                ph2 += inc2;
+                const float p = __fmul_rn(yi, c2), w = __fmul_rn(yq, s2);
+                const float u = P.upper ? __fsub_rn(p, w) : __fadd_rn(p, w);
+                a[j < NS ? j : 0] = __fadd_rn(u, u);
+            }
+        }
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             const float4 d = dd[q];
             if (TSB) {
-#pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    const float yi = ssbx_iir(P.rf, h ? d.z : d.x, iz1, iz2);
-                    const float yq = ssbx_iir(P.rf, h ? d.w : d.y, qz1, qz2);
-                    float c2, s2;
-                    nco_cs(ph2, c2, s2);
-                    ph2 += inc2;
-                    const float p = __fmul_rn(yi, c2), w = __fmul_rn(yq, s2);
-                    const float u = P.upper ? __fsub_rn(p, w) : __fadd_rn(p, w);
-                    a[2 * q + h] = __fadd_rn(u, u);
-                }
             } else {
                 const float m4[4] = {d.x, d.y, d.z, d.w};
 #pragma unroll
@@ -511,9 +536,9 @@ static cudaError_t launch_ssbx_f(const void* iq, const SsbParams& P, const float
     const unsigned mgrid = (unsigned)(threads / 256 + 1 < 148u * 32u ? threads / 256 + 1 : 148u * 32u);
     k_ssbx_mix<TSB><<<mgrid, 256, 0, st>>>(X, d_inc1, M, C, span, nv, base);
     const size_t chains = nv * (TSB ? 2 : 1);
-    const long long nchunks = (long long)((size_t)P.n * (TSB ? 2 : 1) * sizeof(float) / SSB_ROW_BYTES) * B;
     static const bool one_warp = getenv("SDRB_SSBX_STATE") && getenv("SDRB_SSBX_STATE")[0] == '1';
-    if (nchunks % 4 == 0 && !one_warp) {
+    const long long chunks_per_block = (long long)((size_t)P.n * sizeof(float) / SSB_ROW_BYTES);   // of one chain's row
+    if (chunks_per_block % 8 == 0 && !one_warp) {   // a block = whole pairs of groups of K = 4 chunks
         constexpr int K = 4;
         k_ssbx_state2<TSB, K><<<(unsigned)((chains + 31) / 32), 64, (size_t)SSBX_RING_G * K * SSB_TILE_BYTES, st>>>(
             M, P, d_start, d_state, nv, B);
