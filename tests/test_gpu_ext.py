@@ -41,6 +41,9 @@ def test_fft_front_end(sdrb, gpu_ctx, fmt, n, fs, window, remove_dc):
     (0, 16384, 2_000_000, 1, 1, 1, 1, 0.0, 0.0, 6),               # true USB at the centre
     (1, 65536, 30_720_000, 1, 0, 1, 2, 100_000.0, 50_000.0, 3),   # C3-like: cs16, 64K blocks, true LSB
     (2, 16384, 2_000_000, 2, 0, 1, 5, -50_000.0, 25_000.0, 33),   # cf32, true LSB, 5 channels, > 32 blocks
+    (0, 16384, 4_800_000, 1, 1, 1, 2, 30_000.0, 40_000.0, 3),     # decim 100: fused decimator, four accumulators
+    (2, 16384, 9_600_000, 1, 1, 0, 2, -60_000.0, 80_000.0, 3),    # decim 200: two accumulators, reference demod
+    (1, 16384, 2_000_000, 1, 1, 1, 1, 5_000.0, 0.0, 3),           # cs16 at decim 41: the split AGC / decimator pair
 ])
 def test_ssb_extended_chain(sdrb, gpu_ctx, fmt, n, fs, mode, upper, tsb, C, off, spacing, B):
     S = 3

@@ -139,7 +139,9 @@ def test_tracking_follows_center_change(sdrb, gpu_ctx):
                                                    (0, 16384, 2_500_000, 2, 1, 4), (0, 16384, 2_000_000, 1, 0, 3),
                                                    (1, 65536, 30_720_000, 1, 1, 5), (2, 16384, 2_000_000, 1, 1, 4),
                                                    (2, 4096, 250_000, 1, 1, 6), (1, 16384, 1_024_000, 1, 1, 3),
-                                                   (0, 128, 2_000_000, 1, 1, 3)])
+                                                   (0, 128, 2_000_000, 1, 1, 3),
+                                                   (0, 160, 2_000_000, 1, 1, 5),    # not a multiple of 128: per-chunk state pass
+                                                   (1, 4000, 2_000_000, 1, 1, 4)])
 def test_ssb_pcm_parity(sdrb, gpu_ctx, fmt, n, fs, mode, upper, B):
     S = 5
     cfg = sdrb.Config(FC, fs, n, 5, soundMode=mode, inputFormat=fmt, upperSideband=upper)
