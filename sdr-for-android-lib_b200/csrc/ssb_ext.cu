@@ -171,36 +171,44 @@ k_ssbx_dc(const void* __restrict__ iq, const __grid_constant__ SsbParams P, floa
 
 // ---------------------------------------------------------------- pre-pass 2: NCO + first mix, sample-parallel
 // m = (x_r + j x_i) * exp(-j theta): re = x_r c + x_i s, im = x_i c - x_r s, theta = inc1 * (samples since reset);
-// the expressions and their order are those of oracle/sdr_oracle_ext.c.  One thread = 4 consecutive samples of one
-// (stream, channel); span = n_blocks * n samples per stream in this call.
+// the expressions and their order are those of oracle/sdr_oracle_ext.c.  span = n_blocks * n samples per stream in
+// this call.
+// A thread takes 4 consecutive samples of a stream and runs them through a group of up to SSBX_MIX_CPT channels: the
+// samples are loaded once, a channel's phase is one 32-bit multiply (inc * samples-since-reset, modulo 2^32), and no
+// index is ever divided (the first version derived (unit, sample) from a flat index with two 64-bit divisions per
+// four samples - more instructions than the NCO itself).  grid.x = (stream, channel group), grid.y strides over the
+// span in blocks of 1024 samples.
+constexpr int SSBX_MIX_CPT = 16;
 template <bool TSB>
 __global__ void __launch_bounds__(256)
 k_ssbx_mix(const float2* __restrict__ X, const uint32_t* __restrict__ inc1_tab, float* __restrict__ M, int channels,
-           size_t span, size_t n_units, unsigned long long base_samples) {
-    const size_t q4 = span / 4;
-    const size_t total = n_units * q4;
-    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-        const size_t v = idx / q4, k = (idx - v * q4) * 4;
-        const size_t s = v / channels;
-        const uint32_t inc1 = inc1_tab[v % channels];
-        uint32_t ph = (uint32_t)((unsigned long long)inc1 * (base_samples + k));
-        const float4* x4 = reinterpret_cast<const float4*>(X + s * span + k);
+           size_t span, int groups, unsigned long long base_samples) {
+    const unsigned s = blockIdx.x / (unsigned)groups, cg = blockIdx.x - s * (unsigned)groups;
+    const int c0 = (int)cg * SSBX_MIX_CPT, c1 = min(channels, c0 + SSBX_MIX_CPT);
+    for (size_t k = ((size_t)blockIdx.y * 256 + threadIdx.x) * 4; k < span; k += (size_t)gridDim.y * 1024) {
+        const float4* x4 = reinterpret_cast<const float4*>(X + (size_t)s * span + k);
         const float4 a = x4[0], b = x4[1];
         const float xr[4] = {a.x, a.z, b.x, b.z}, xi[4] = {a.y, a.w, b.y, b.w};
-        float mr[4], mi[4];
+        const uint32_t t0 = (uint32_t)(base_samples + k);
+        for (int c = c0; c < c1; c++) {
+            const uint32_t inc1 = inc1_tab[c];
+            uint32_t ph = inc1 * t0;
+            const size_t v = (size_t)s * channels + c;
+            float mr[4], mi[4];
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            float c1, s1;
-            nco_cs(ph, c1, s1);
-            ph += inc1;
-            mr[j] = __fadd_rn(__fmul_rn(xr[j], c1), __fmul_rn(xi[j], s1));
-            if (TSB) mi[j] = __fsub_rn(__fmul_rn(xi[j], c1), __fmul_rn(xr[j], s1));
-        }
-        if (TSB) {   // planar: the I row of a unit, then its Q row -- every chain of the state pass owns a contiguous row
-            *reinterpret_cast<float4*>(M + (2 * v) * span + k) = make_float4(mr[0], mr[1], mr[2], mr[3]);
-            *reinterpret_cast<float4*>(M + (2 * v + 1) * span + k) = make_float4(mi[0], mi[1], mi[2], mi[3]);
-        } else {
-            *reinterpret_cast<float4*>(M + v * span + k) = make_float4(mr[0], mr[1], mr[2], mr[3]);
+            for (int j = 0; j < 4; j++) {
+                float cs, sn;
+                nco_cs(ph, cs, sn);
+                ph += inc1;
+                mr[j] = __fadd_rn(__fmul_rn(xr[j], cs), __fmul_rn(xi[j], sn));
+                if (TSB) mi[j] = __fsub_rn(__fmul_rn(xi[j], cs), __fmul_rn(xr[j], sn));
+            }
+            if (TSB) {   // planar: the I row of a unit, then its Q row -- every chain of the state pass owns a contiguous row
+                *reinterpret_cast<float4*>(M + (2 * v) * span + k) = make_float4(mr[0], mr[1], mr[2], mr[3]);
+                *reinterpret_cast<float4*>(M + (2 * v + 1) * span + k) = make_float4(mi[0], mi[1], mi[2], mi[3]);
+            } else {
+                *reinterpret_cast<float4*>(M + v * span + k) = make_float4(mr[0], mr[1], mr[2], mr[3]);
+            }
         }
     }
 }
@@ -532,9 +540,10 @@ static cudaError_t launch_ssbx_f(const void* iq, const SsbParams& P, const float
     if ((e = cudaFuncSetAttribute(k_ssbx_dc<FMT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem)) != cudaSuccess) return e;
     const int frames = S * B;
     k_ssbx_dc<FMT><<<(frames + SSBX_WARPS * 32 - 1) / (SSBX_WARPS * 32), SSBX_WARPS * 32, tsmem, st>>>(iq, P, X, frames);
-    const size_t threads = nv * (span / 4);
-    const unsigned mgrid = (unsigned)(threads / 256 + 1 < 148u * 32u ? threads / 256 + 1 : 148u * 32u);
-    k_ssbx_mix<TSB><<<mgrid, 256, 0, st>>>(X, d_inc1, M, C, span, nv, base);
+    const int groups = (C + SSBX_MIX_CPT - 1) / SSBX_MIX_CPT;
+    const size_t kblocks = (span + 1023) / 1024;
+    const dim3 mgrid((unsigned)S * (unsigned)groups, (unsigned)(kblocks < 65535 ? kblocks : 65535));
+    k_ssbx_mix<TSB><<<mgrid, 256, 0, st>>>(X, d_inc1, M, C, span, groups, base);
     const size_t chains = nv * (TSB ? 2 : 1);
     static const bool one_warp = getenv("SDRB_SSBX_STATE") && getenv("SDRB_SSBX_STATE")[0] == '1';
     const long long chunks_per_block = (long long)((size_t)P.n * sizeof(float) / SSB_ROW_BYTES);   // of one chain's row
