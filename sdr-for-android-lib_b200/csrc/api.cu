@@ -110,6 +110,7 @@ struct sdrb_ctx {
     int blue_m = 0;
     cpx *d_sa = nullptr, *d_sb = nullptr;
     cpx* d_fb_tables = nullptr;   // four-step twiddle tables
+    cpx* d_fs_tables = nullptr;   // small one-CTA kernel's twiddle tables (fft_small.cu)
     cpx* d_fbA = nullptr;         // four-step intermediate A' (fb_group frames; fused variant: a ring of fb_slots frames)
     int fb_group = 0;
     unsigned* d_fb_ctl = nullptr; // fused four-step: ticket + per-frame counters
@@ -190,7 +191,7 @@ static void free_buffers(sdrb_ctx* c) {
                      (void**)&c->d_fft_state, (void**)&c->d_ssb_state, &c->d_start,
                      (void**)&c->d_a48, (void**)&c->d_pcm, (void**)&c->d_taps, (void**)&c->d_taps_lin, (void**)&c->d_tapsE, (void**)&c->d_tw, (void**)&c->d_chirp, (void**)&c->d_bf, (void**)&c->d_sa,
                      (void**)&c->d_sb, (void**)&c->d_est_scratch, (void**)&c->d_inc1, (void**)&c->d_win,
-                     (void**)&c->d_front, (void**)&c->d_fb_tables, (void**)&c->d_fbA, (void**)&c->d_fb_ctl,
+                     (void**)&c->d_front, (void**)&c->d_fb_tables, (void**)&c->d_fs_tables, (void**)&c->d_fbA, (void**)&c->d_fb_ctl,
                      (void**)&c->d_sp_state, (void**)&c->d_au_state, (void**)&c->d_sp_e, (void**)&c->d_sp_f,
                      (void**)&c->d_au_e, (void**)&c->d_pulse, (void**)&c->d_air_state,
                      (void**)&c->d_air_iq, (void**)&c->d_air_work, (void**)&c->d_agc, (void**)&c->d_ext_work};
@@ -226,7 +227,8 @@ int sdrb_create(int device, sdrb_ctx** out) {
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
-        (e = fft_big_prepare()) != cudaSuccess || (e = estimator_prepare()) != cudaSuccess ||
+        (e = fft_big_prepare()) != cudaSuccess || (e = fft_small_prepare()) != cudaSuccess ||
+        (e = estimator_prepare()) != cudaSuccess ||
         (e = ssb_prepare()) != cudaSuccess) {
         fail(nullptr, SDRB_ERR_CUDA, "context setup: %s", cudaGetErrorString(e));
         delete ctx;
@@ -314,8 +316,14 @@ static int check_config(sdrb_ctx* ctx, const sdrb_config* cfg) {
     return SDRB_OK;
 }
 
-// 1: one-CTA 16K kernel, 2: multi-CTA four-step (64K, 1M), 0: multi-pass power of two, 3: any other length (Bluestein)
-static int fft_path_for(int n) { return n == F2_N ? 1 : (fft_big_supports(n) ? 2 : (is_pow2(n) && n >= 2 ? 0 : 3)); }
+// 1: one-CTA 16K kernel, 4: one-CTA kernel for 256 .. 8192 points, 2: multi-CTA four-step (64K, 1M), 0: multi-pass power
+// of two, 3: any other length (Bluestein)
+static int fft_path_for(int n) {
+    static const bool no_small = getenv("SDRB_FFT_SMALL") && getenv("SDRB_FFT_SMALL")[0] == '0';   // test hook: Stockham passes instead
+    if (n == F2_N) return 1;
+    if (fft_small_supports(n) && !no_small) return 4;
+    return fft_big_supports(n) ? 2 : (is_pow2(n) && n >= 2 ? 0 : 3);
+}
 constexpr int kMaxBluesteinN = 1 << 22;   // convolution length 2^23: 64 MiB per transform and scratch buffer
 
 extern "C" int sdrb_plan_config(const sdrb_config* cfg, sdrb_plan* out) {
@@ -631,7 +639,12 @@ static int ensure_fft_buffers(sdrb_ctx* ctx) {
         CK(cudaMalloc(&ctx->d_sb, chunk * (size_t)m * sizeof(cpx)));
         if (ctx->front) CK(cudaMalloc(&ctx->d_front, chunk * (size_t)n * sizeof(cpx)));
     }
-    if (ctx->fftPath == 0 && ctx->front && !ctx->d_front) {
+    if (ctx->fftPath == 4 && !ctx->d_fs_tables) {
+        const std::vector<cpx> tb = make_fs_tables(n);
+        CK(cudaMalloc(&ctx->d_fs_tables, tb.size() * sizeof(cpx)));
+        CK(cudaMemcpy(ctx->d_fs_tables, tb.data(), tb.size() * sizeof(cpx), cudaMemcpyHostToDevice));
+    }
+    if ((ctx->fftPath == 0 || ctx->fftPath == 4) && ctx->front && !ctx->d_front) {
         size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
         if (chunk < 1) chunk = 1;
         if (chunk > frames) chunk = frames;
@@ -884,8 +897,11 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
                                         ctx->d_tw, n, ctx->blue_m, nf, st, &fft_launches));
             }
         } else {
+            // multi-pass Stockham (scratch-sized chunks), or the small one-CTA kernel (4): whole call unless the
+            // extension front end needs its cf32 pre-pass buffer
             size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
             if (chunk < 1) chunk = 1;
+            if (ctx->fftPath == 4 && !ctx->front) chunk = (size_t)frames;
             for (size_t f0 = 0; f0 < (size_t)frames; f0 += chunk) {
                 const int nf = (int)((size_t)frames - f0 < chunk ? (size_t)frames - f0 : chunk);
                 const void* src = static_cast<const unsigned char*>(d_iq) + f0 * n * bps;
@@ -896,8 +912,13 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
                     src = ctx->d_front;
                     src_fmt = FMT_CF32;
                 }
-                CK(launch_fft_generic(src_fmt, src, power + f0 * n, ctx->d_sa, ctx->d_sb, ctx->d_tw, n, nf, st,
-                                      &fft_launches));
+                if (ctx->fftPath == 4) {
+                    CK(launch_fft_small(src_fmt, src, power + f0 * n, ctx->d_fs_tables, n, nf, ctx->sm_count, st));
+                    fft_launches++;
+                } else {
+                    CK(launch_fft_generic(src_fmt, src, power + f0 * n, ctx->d_sa, ctx->d_sb, ctx->d_tw, n, nf, st,
+                                          &fft_launches));
+                }
             }
         }
         if (time_fft && ctx->fftPath != 1) { CK(cudaEventRecord(ctx->ev1, st)); ctx->ev_valid = true; ctx->last_fft_frames = frames; }

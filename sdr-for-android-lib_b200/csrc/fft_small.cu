@@ -1,0 +1,99 @@
+// fft_small.cu — one-CTA-per-transform shared-memory FFT kernels for 256 .. 8192 points (sm_100a).
+// See fft_small.cuh for the decomposition and the phase functions.  Ingest convert, |X|^2 and fftshift are fused as
+// in the 16K kernel (reference: src/dsp/fft_process.cpp:62-97); before this kernel these lengths went through the
+// radix-16 Stockham passes over global memory (16 B per sample and pass: 59-74 GS/s against 372 at 16384 points).
+//
+//   k_fft_small<FMT, C>: persistent, 256 threads (512 for 8192 points), 256 / (16 C) transforms per CTA and round;
+//   raw IQ straight into registers (a warp reads 32 consecutive samples per load), two in-place exchanges through
+//   shared memory (16 C + 1 complex per plane), twiddle tables in shared memory, spectra out 128 bytes per warp store.
+#include "fft_small.cuh"
+#include "internal.h"
+
+namespace sdrb {
+
+template <int FMT, int C>
+__global__ void __launch_bounds__(FsGeom<C>::kThreads)
+k_fft_small(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict__ out, const cpx* __restrict__ tables,
+            int n_frames) {
+    typedef FsGeom<C> G;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cpx* Eall = reinterpret_cast<cpx*>(smem_raw);
+    cpx* TP = Eall + G::kPerCta * G::kE;
+    cpx* T2 = TP + G::kTP;
+    for (int i = threadIdx.x; i < G::kTables; i += G::kThreads) TP[i] = tables[i];
+    const int sub = threadIdx.x / G::T, t = threadIdx.x % G::T;
+    cpx* E = Eall + sub * G::kE;
+    __syncthreads();
+    for (long long f0 = (long long)blockIdx.x * G::kPerCta; f0 < n_frames; f0 += (long long)gridDim.x * G::kPerCta) {
+        const long long f = f0 + sub;
+        const bool live = f < n_frames;
+        if (live) fs_phase1<FMT, C>(t, in + (size_t)f * G::N, TP, E);
+        __syncthreads();
+        if (live) fs_phase2<C>(t, E);
+        __syncthreads();
+        if (live) fs_phase3<C>(t, E, T2, out + (size_t)f * G::N);
+        __syncthreads();   // the next round's phase 1 overwrites E
+    }
+}
+
+template <int C>
+static constexpr int fs_smem() { return (FsGeom<C>::kPerCta * FsGeom<C>::kE + FsGeom<C>::kTables) * (int)sizeof(cpx); }
+
+template <int C>
+static cudaError_t fs_prepare_c() {
+    cudaError_t e;
+    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CU8, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CS16, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k_fft_small<FMT_CF32, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>());
+}
+cudaError_t fft_small_prepare() {
+    cudaError_t e;
+    if ((e = fs_prepare_c<1>()) != cudaSuccess) return e;
+    if ((e = fs_prepare_c<2>()) != cudaSuccess) return e;
+    if ((e = fs_prepare_c<4>()) != cudaSuccess) return e;
+    if ((e = fs_prepare_c<8>()) != cudaSuccess) return e;
+    if ((e = fs_prepare_c<16>()) != cudaSuccess) return e;
+    return fs_prepare_c<32>();
+}
+
+bool fft_small_supports(int n) { return n >= 256 && n <= 8192 && (n & (n - 1)) == 0; }
+int fft_small_table_elems(int n) { return fft_small_supports(n) ? 80 * (n / 256) : 0; }
+
+template <int FMT, int C>
+static cudaError_t fs_launch_fc(const void* iq, float* power, const cpx* tables, int n_frames, int sm_count, cudaStream_t st) {
+    typedef FsGeom<C> G;
+    static int per_sm = 0;
+    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fft_small<FMT, C>, G::kThreads, fs_smem<C>()) != cudaSuccess || per_sm < 1))
+        per_sm = 1;
+    const long long rounds = ((long long)n_frames + G::kPerCta - 1) / G::kPerCta;
+    const long long slots = (long long)per_sm * (sm_count > 0 ? sm_count : 148);
+    const int grid = (int)(rounds < slots ? rounds : slots);
+    k_fft_small<FMT, C><<<grid, G::kThreads, fs_smem<C>(), st>>>(static_cast<const typename Ingest2<FMT>::raw_t*>(iq), power, tables,
+                                                                  n_frames);
+    return cudaGetLastError();
+}
+template <int C>
+static cudaError_t fs_launch_c(int fmt, const void* iq, float* power, const cpx* tables, int n_frames, int sm_count,
+                               cudaStream_t st) {
+    switch (fmt) {
+        case FMT_CU8: return fs_launch_fc<FMT_CU8, C>(iq, power, tables, n_frames, sm_count, st);
+        case FMT_CS16: return fs_launch_fc<FMT_CS16, C>(iq, power, tables, n_frames, sm_count, st);
+        case FMT_CF32: return fs_launch_fc<FMT_CF32, C>(iq, power, tables, n_frames, sm_count, st);
+        default: return cudaErrorInvalidValue;
+    }
+}
+cudaError_t launch_fft_small(int fmt, const void* iq, float* power, const cpx* tables, int n, int n_frames, int sm_count,
+                             cudaStream_t st) {
+    if (n_frames <= 0) return cudaSuccess;
+    switch (n) {
+        case 256: return fs_launch_c<1>(fmt, iq, power, tables, n_frames, sm_count, st);
+        case 512: return fs_launch_c<2>(fmt, iq, power, tables, n_frames, sm_count, st);
+        case 1024: return fs_launch_c<4>(fmt, iq, power, tables, n_frames, sm_count, st);
+        case 2048: return fs_launch_c<8>(fmt, iq, power, tables, n_frames, sm_count, st);
+        case 4096: return fs_launch_c<16>(fmt, iq, power, tables, n_frames, sm_count, st);
+        case 8192: return fs_launch_c<32>(fmt, iq, power, tables, n_frames, sm_count, st);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace sdrb

@@ -1,0 +1,106 @@
+// fft_small.cuh — one-CTA-per-transform shared-memory FFT for N = 256 C, C in {1, 2, 4, 8, 16, 32} (256 .. 8192 points):
+// the 16K kernel's structure for the other power-of-two block lengths up to 8192
+// (reference: src/dsp/fft_process.cpp:62-97 — copy, fftwf_execute of samplesPerReading points, power, fftshift).
+//
+//   n = 16 C a + C b + c          k = ka + 16 kb + 256 kc          (a, b, ka, kb < 16; c, kc < C)
+//   phase 1: DFT16 over a   thread t = C b + c  (T = 16 C threads)   twiddle W_N^(t ka)
+//   phase 2: DFT16 over b   thread t = C ka + c                      (twiddle W_16C^(c kb) applied by phase 3 on load)
+//   phase 3: DFT_C over c   pairs p = ka + 16 kb: thread u takes p = u + T j, j < 16 / C  (C = 32: threads u < 256, one
+//            32-point transform each), then |X|^2, fftshift folded into the store index: for a fixed kc a warp's 32
+//            pairs are 32 consecutive bins
+// Exchange buffer E[ka][16 C + 1]: phase-1 stores and phase-2 accesses of a half-warp fall on distinct 8-byte bank
+// pairs for C >= 16, phase-3 loads (16 consecutive ka) for every C because the pitch is odd; for C < 16 phase 2 is
+// two-way conflicted (a half-warp spans 16 / C planes one element apart).
+// Every thread holds 16 points in every phase; small transforms share a CTA (256 / T of them).
+// The register codelets are the FMA-form decimation-in-time ones of fft_dit.cuh.
+// Phase functions are __host__ __device__ so that tests/cpp/fft_small_sim.cpp runs them thread by thread.
+#pragma once
+#include <stdint.h>
+
+#include "fft16k2.cuh"
+#include "fft_core.cuh"
+#include "fft_dit.cuh"
+
+namespace sdrb {
+
+template <int C>
+struct FsGeom {
+    static constexpr int N = 256 * C;
+    static constexpr int T = 16 * C;                     // threads per transform
+    static constexpr int kPitch = 16 * C + 1;            // complex elements per ka plane
+    static constexpr int kE = 16 * kPitch;               // exchange buffer of one transform
+    static constexpr int kPerCta = T >= 256 ? 1 : 256 / T;   // transforms per CTA
+    static constexpr int kThreads = T * kPerCta;         // 256, or 512 for C = 32
+    static constexpr int kTP = 4 * T;                    // [j][t]   W_N^(t 2^j)
+    static constexpr int kT2 = 16 * C;                   // [kb][c]  W_16C^(c kb)
+    static constexpr int kTables = kTP + kT2;
+    static constexpr int kLogC = C == 1 ? 0 : C == 2 ? 1 : C == 4 ? 2 : C == 8 ? 3 : C == 16 ? 4 : 5;
+};
+
+// ---- phase 1: load + convert, DFT16 over a, twiddle W_N^(t ka), store E[ka][t]
+template <int FMT, int C>
+SDRB_HD void fs_phase1(int t, const typename Ingest2<FMT>::raw_t* in, const cpx* TP, cpx* E) {
+    typedef FsGeom<C> G;
+    cpx v[16];
+#pragma unroll
+    for (int a = 0; a < 16; a++) v[a] = Ingest2<FMT>::cvt(in[G::T * a + t]);
+    fft_dit<4>(v);
+    // W_N^(t ka) from W_N^(t 2^j): w[k] = w[k with lowest set bit cleared] * P[ctz k]
+    cpx P[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) P[j] = TP[j * G::T + t];
+    cpx w[16];
+    E[t] = v[0];
+#pragma unroll
+    for (int k = 1; k < 16; k++) {
+        const int low = k & (-k);
+        const int j = low == 1 ? 0 : (low == 2 ? 1 : (low == 4 ? 2 : 3));
+        w[k] = (k == low) ? P[j] : cmul(w[k - low], P[j]);
+        E[k * G::kPitch + t] = cmul(v[dit_slot<4>(k)], w[k]);
+    }
+}
+
+// ---- phase 2: DFT16 over b for (ka, c), in place
+template <int C>
+SDRB_HD void fs_phase2(int t, cpx* E) {
+    typedef FsGeom<C> G;
+    const int ka = t / C, c = t % C;
+    cpx* base = E + ka * G::kPitch + c;
+    cpx v[16];
+#pragma unroll
+    for (int b = 0; b < 16; b++) v[b] = base[b * C];
+    fft_dit<4>(v);
+#pragma unroll
+    for (int k = 0; k < 16; k++) base[k * C] = v[dit_slot<4>(k)];
+}
+
+// ---- phase 3: twiddle W_16C^(c kb) on load, DFT_C over c, power, fftshift, store
+template <int C>
+SDRB_HD void fs_phase3_pair(int p, const cpx* E, const cpx* T2, float* __restrict__ out) {
+    typedef FsGeom<C> G;
+    const int ka = p & 15, kb = p >> 4;
+    const cpx* base = E + ka * G::kPitch + kb * C;
+    cpx v[C];
+    v[0] = base[0];
+#pragma unroll
+    for (int c = 1; c < C; c++) v[c] = cmul(base[c], T2[kb * C + c]);
+    if constexpr (G::kLogC > 0) fft_dit<G::kLogC>(v);
+#pragma unroll
+    for (int kc = 0; kc < C; kc++) {
+        const cpx x = v[dit_slot<G::kLogC>(kc)];
+        // re*re + im*im (src/dsp/fft_process.cpp:85); bin k lands at (k + N/2) mod N (:92-97)
+        out[(p + 256 * kc + G::N / 2) & (G::N - 1)] = x.x * x.x + x.y * x.y;
+    }
+}
+template <int C>
+SDRB_HD void fs_phase3(int t, const cpx* E, const cpx* T2, float* __restrict__ out) {
+    typedef FsGeom<C> G;
+    if (C == 32) {
+        if (t < 256) fs_phase3_pair<C>(t, E, T2, out);
+    } else {
+#pragma unroll
+        for (int j = 0; j < (C >= 16 ? 1 : 16 / C); j++) fs_phase3_pair<C>(t + G::T * j, E, T2, out);
+    }
+}
+
+}  // namespace sdrb

@@ -28,6 +28,17 @@ inline std::vector<cpx> make_f2_tables() {
     return t;
 }
 
+// Small one-CTA kernel (fft_small.cuh), N = 256 C: TP[j][t] = W_N^(t 2^j) (j < 4, t < 16 C), then T2[kb][c] = W_16C^(c kb)
+inline std::vector<cpx> make_fs_tables(int n) {
+    const int C = n / 256, T = 16 * C;
+    std::vector<cpx> t((size_t)4 * T + 16 * C);
+    for (int j = 0; j < 4; j++)
+        for (int r = 0; r < T; r++) t[(size_t)j * T + r] = twiddle((long long)r << j, n);
+    for (int kb = 0; kb < 16; kb++)
+        for (int c = 0; c < C; c++) t[(size_t)4 * T + kb * C + c] = twiddle((long long)c * kb, 16 * C);
+    return t;
+}
+
 // Layout: TL | TLO | THI | TB  (FbGeom<R>::kTables entries), see fft_big.cuh
 template <int R>
 inline std::vector<cpx> make_fb_tables() {

@@ -129,6 +129,12 @@ cudaError_t launch_fft16k2(int fmt, const void* iq, float* power, const cpx* tab
                            int* ticket = nullptr);
 cudaError_t fft16k2_prepare(const cpx* host_tables);   // make_f2_tables() layout; T2 goes to the constant bank
 // fft_any.cu : generic power-of-two path (N != 16384)
+// fft_small.cu : one-CTA shared-memory kernel for 256 .. 8192 points (tables: make_fs_tables, fft_tables.h)
+cudaError_t fft_small_prepare();
+bool fft_small_supports(int n);
+int fft_small_table_elems(int n);
+cudaError_t launch_fft_small(int fmt, const void* iq, float* power, const cpx* tables, int n, int n_frames, int sm_count,
+                             cudaStream_t st);
 cudaError_t launch_fft_generic(int fmt, const void* iq, float* power, cpx* scratch_a, cpx* scratch_b,
                                const cpx* twiddles, int n, int n_frames, cudaStream_t st, int* launches);
 int fft_generic_passes(int n);
