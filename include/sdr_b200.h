@@ -146,7 +146,7 @@ typedef struct {
     int32_t winLo[10], winHi[10];
     float   freqPerBin, nyquist;
     int32_t decim, nTaps, pcmPerBlock;
-    int32_t fftPath;               /* 0 generic multi-pass, 1 single-CTA 16K kernel, 2 four-step, 3 chirp-z, 4 single-CTA 256..8192 */
+    int32_t fftPath;               /* 0 generic multi-pass, 1 single-CTA 16K kernel, 2 four-step, 3 chirp-z, 4 single-CTA 256..8192, 5 two-pass 32768/131072/262144 */
     float   rf[5], hp[5], bp[5];   /* a0,a1,a2,b1,b2 of struct IIR2 / Biquad (src/ssb/ssb_demod_opt.h:14-26) */
     float   agcTarget, agcFast, agcSlow, gain, transientCoeff, dcAlpha;
     float   firTaps[255];

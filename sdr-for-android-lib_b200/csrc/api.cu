@@ -47,6 +47,7 @@ struct EventTrace : sdrb::TraceSink {
 };
 
 constexpr size_t kGenericScratchBytes = 256u << 20;  // per ping-pong buffer of the generic FFT
+constexpr size_t kTwoPassScratchBytes = 1024u << 20; // intermediate of the two-pass scheme (32768 .. 262144 points)
 // Four-step intermediate per launch pair.  Round 1 kept it within 96 MB "so that it stays in L2"; ncu showed it did not
 // (kernel B read 97 MB per group from DRAM, 16 % L2 hits) and a sweep on the B200 is monotonic in the other direction:
 // 24 MB 0.99 ms, 96 MB 0.665 ms, 384 MB 0.603 ms, whole batch 0.600 ms (256 x 8 x 65536 cs16); 1M points 0.608 -> 0.491 ms.
@@ -322,6 +323,7 @@ static int fft_path_for(int n) {
     static const bool no_small = getenv("SDRB_FFT_SMALL") && getenv("SDRB_FFT_SMALL")[0] == '0';   // test hook: Stockham passes instead
     if (n == F2_N) return 1;
     if (fft_small_supports(n) && !no_small) return 4;
+    if (fft_twopass_supports(n) && !no_small) return 5;   // radix-A columns + the one-CTA kernel on 4096 / 8192-point rows
     return fft_big_supports(n) ? 2 : (is_pow2(n) && n >= 2 ? 0 : 3);
 }
 constexpr int kMaxBluesteinN = 1 << 22;   // convolution length 2^23: 64 MiB per transform and scratch buffer
@@ -639,12 +641,22 @@ static int ensure_fft_buffers(sdrb_ctx* ctx) {
         CK(cudaMalloc(&ctx->d_sb, chunk * (size_t)m * sizeof(cpx)));
         if (ctx->front) CK(cudaMalloc(&ctx->d_front, chunk * (size_t)n * sizeof(cpx)));
     }
+    if (ctx->fftPath == 5 && !ctx->d_fs_tables) {
+        const int B = n == 262144 ? 8192 : 4096, loga = n == 32768 ? 3 : 5;
+        const std::vector<cpx> tb = make_tp_tables(n, B, loga);
+        CK(cudaMalloc(&ctx->d_fs_tables, tb.size() * sizeof(cpx)));
+        CK(cudaMemcpy(ctx->d_fs_tables, tb.data(), tb.size() * sizeof(cpx), cudaMemcpyHostToDevice));
+        size_t chunk = kTwoPassScratchBytes / ((size_t)n * sizeof(cpx));
+        if (chunk < 1) chunk = 1;
+        if (chunk > frames) chunk = frames;
+        CK(cudaMalloc(&ctx->d_sa, chunk * (size_t)n * sizeof(cpx)));
+    }
     if (ctx->fftPath == 4 && !ctx->d_fs_tables) {
         const std::vector<cpx> tb = make_fs_tables(n);
         CK(cudaMalloc(&ctx->d_fs_tables, tb.size() * sizeof(cpx)));
         CK(cudaMemcpy(ctx->d_fs_tables, tb.data(), tb.size() * sizeof(cpx), cudaMemcpyHostToDevice));
     }
-    if ((ctx->fftPath == 0 || ctx->fftPath == 4) && ctx->front && !ctx->d_front) {
+    if ((ctx->fftPath == 0 || ctx->fftPath == 4 || ctx->fftPath == 5) && ctx->front && !ctx->d_front) {
         size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
         if (chunk < 1) chunk = 1;
         if (chunk > frames) chunk = frames;
@@ -902,6 +914,7 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
             size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
             if (chunk < 1) chunk = 1;
             if (ctx->fftPath == 4 && !ctx->front) chunk = (size_t)frames;
+            if (ctx->fftPath == 5 && !ctx->front) chunk = kTwoPassScratchBytes / ((size_t)n * sizeof(cpx));
             for (size_t f0 = 0; f0 < (size_t)frames; f0 += chunk) {
                 const int nf = (int)((size_t)frames - f0 < chunk ? (size_t)frames - f0 : chunk);
                 const void* src = static_cast<const unsigned char*>(d_iq) + f0 * n * bps;
@@ -915,6 +928,9 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
                 if (ctx->fftPath == 4) {
                     CK(launch_fft_small(src_fmt, src, power + f0 * n, ctx->d_fs_tables, n, nf, ctx->sm_count, st));
                     fft_launches++;
+                } else if (ctx->fftPath == 5) {
+                    CK(launch_fft_twopass(src_fmt, src, power + f0 * n, ctx->d_sa, ctx->d_fs_tables, n, nf, ctx->sm_count, st));
+                    fft_launches += 2;
                 } else {
                     CK(launch_fft_generic(src_fmt, src, power + f0 * n, ctx->d_sa, ctx->d_sb, ctx->d_tw, n, nf, st,
                                           &fft_launches));

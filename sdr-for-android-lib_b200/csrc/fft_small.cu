@@ -11,10 +11,12 @@
 
 namespace sdrb {
 
-template <int FMT, int C>
+// ROWS = 0: n_frames independent N-point frames.  ROWS = A > 0 (the rows pass of the two-pass scheme): n_frames counts
+// ROWS, row r = (big frame r / A, ka = r % A), spectra interleaved into the big frame.
+template <int FMT, int C, bool STRIDED>
 __global__ void __launch_bounds__(FsGeom<C>::kThreads)
 k_fft_small(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict__ out, const cpx* __restrict__ tables,
-            int n_frames) {
+            int n_frames, int rows_per_frame) {
     typedef FsGeom<C> G;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     cpx* Eall = reinterpret_cast<cpx*>(smem_raw);
@@ -31,7 +33,15 @@ k_fft_small(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restri
         __syncthreads();
         if (live) fs_phase2<C>(t, E);
         __syncthreads();
-        if (live) fs_phase3<C>(t, E, T2, out + (size_t)f * G::N);
+        if (live) {
+            if (STRIDED) {
+                const long long big = f / rows_per_frame;
+                const FsOutStrided where = {rows_per_frame, (int)(f - big * rows_per_frame)};
+                fs_phase3<C>(t, E, T2, out + (size_t)big * rows_per_frame * G::N, where);
+            } else {
+                fs_phase3<C>(t, E, T2, out + (size_t)f * G::N, FsOutPlain());
+            }
+        }
         __syncthreads();   // the next round's phase 1 overwrites E
     }
 }
@@ -42,9 +52,11 @@ static constexpr int fs_smem() { return (FsGeom<C>::kPerCta * FsGeom<C>::kE + Fs
 template <int C>
 static cudaError_t fs_prepare_c() {
     cudaError_t e;
-    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CU8, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CS16, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
-    return cudaFuncSetAttribute(k_fft_small<FMT_CF32, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>());
+    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CU8, C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CS16, C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CF32, C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
+    if (C >= 16) return cudaFuncSetAttribute(k_fft_small<FMT_CF32, C, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>());
+    return cudaSuccess;
 }
 cudaError_t fft_small_prepare() {
     cudaError_t e;
@@ -63,13 +75,13 @@ template <int FMT, int C>
 static cudaError_t fs_launch_fc(const void* iq, float* power, const cpx* tables, int n_frames, int sm_count, cudaStream_t st) {
     typedef FsGeom<C> G;
     static int per_sm = 0;
-    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fft_small<FMT, C>, G::kThreads, fs_smem<C>()) != cudaSuccess || per_sm < 1))
+    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fft_small<FMT, C, false>, G::kThreads, fs_smem<C>()) != cudaSuccess || per_sm < 1))
         per_sm = 1;
     const long long rounds = ((long long)n_frames + G::kPerCta - 1) / G::kPerCta;
     const long long slots = (long long)per_sm * (sm_count > 0 ? sm_count : 148);
     const int grid = (int)(rounds < slots ? rounds : slots);
-    k_fft_small<FMT, C><<<grid, G::kThreads, fs_smem<C>(), st>>>(static_cast<const typename Ingest2<FMT>::raw_t*>(iq), power, tables,
-                                                                  n_frames);
+    k_fft_small<FMT, C, false><<<grid, G::kThreads, fs_smem<C>(), st>>>(static_cast<const typename Ingest2<FMT>::raw_t*>(iq), power,
+                                                                         tables, n_frames, 1);
     return cudaGetLastError();
 }
 template <int C>
@@ -94,6 +106,61 @@ cudaError_t launch_fft_small(int fmt, const void* iq, float* power, const cpx* t
         case 8192: return fs_launch_c<32>(fmt, iq, power, tables, n_frames, sm_count, st);
         default: return cudaErrorInvalidValue;
     }
+}
+
+// ---------------------------------------------------------------- two-pass scheme, 32768 .. 262144 points
+template <int FMT, int LOGA>
+__global__ void __launch_bounds__(256)
+k_fs_cols(const typename Ingest2<FMT>::raw_t* __restrict__ in, cpx* __restrict__ Y, const cpx* __restrict__ TPc, int B) {
+    const int b = blockIdx.x * 256 + threadIdx.x;           // B is a multiple of 256
+    const size_t frame = blockIdx.y, N = (size_t)B << LOGA;
+    fs_cols<FMT, LOGA>(b, B, in + frame * N, TPc, Y + frame * N);
+}
+
+bool fft_twopass_supports(int n) { return n == 32768 || n == 131072 || n == 262144; }
+static int twopass_b(int n) { return n == 262144 ? 8192 : 4096; }
+static int twopass_loga(int n) { return n == 32768 ? 3 : 5; }
+// tables: TPc[j][b] = W_N^(b 2^j), j < log2 A, then the small kernel's tables for B points (make_tp_tables)
+int fft_twopass_table_elems(int n) { return fft_twopass_supports(n) ? twopass_loga(n) * twopass_b(n) + fft_small_table_elems(twopass_b(n)) : 0; }
+
+template <int FMT, int LOGA>
+static void tp_cols(const void* iq, cpx* Y, const cpx* TPc, int B, int n_frames, cudaStream_t st) {
+    const dim3 grid((unsigned)(B / 256), (unsigned)n_frames);
+    k_fs_cols<FMT, LOGA><<<grid, 256, 0, st>>>(static_cast<const typename Ingest2<FMT>::raw_t*>(iq), Y, TPc, B);
+}
+template <int C>
+static cudaError_t tp_rows(const cpx* Y, float* power, const cpx* tables, int n_rows, int A, int sm_count, cudaStream_t st) {
+    typedef FsGeom<C> G;
+    static int per_sm = 0;
+    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fft_small<FMT_CF32, C, true>, G::kThreads, fs_smem<C>()) != cudaSuccess || per_sm < 1))
+        per_sm = 1;
+    const long long slots = (long long)per_sm * (sm_count > 0 ? sm_count : 148);
+    const int grid = (int)(n_rows < slots ? n_rows : slots);
+    k_fft_small<FMT_CF32, C, true><<<grid, G::kThreads, fs_smem<C>(), st>>>(Y, power, tables, n_rows, A);
+    return cudaGetLastError();
+}
+// Y: n_frames * n complex of scratch.  n_frames <= 65535 per call (the caller's chunks are far smaller).
+cudaError_t launch_fft_twopass(int fmt, const void* iq, float* power, cpx* Y, const cpx* tables, int n, int n_frames,
+                               int sm_count, cudaStream_t st) {
+    if (n_frames <= 0) return cudaSuccess;
+    if (!fft_twopass_supports(n) || n_frames > 65535) return cudaErrorInvalidValue;
+    const int B = twopass_b(n), loga = twopass_loga(n), A = 1 << loga;
+    const cpx* TPc = tables;
+    const cpx* small = tables + (size_t)loga * B;
+#define SDRB_COLS(F)                                                                   \
+    if (loga == 3) tp_cols<F, 3>(iq, Y, TPc, B, n_frames, st);                         \
+    else tp_cols<F, 5>(iq, Y, TPc, B, n_frames, st);
+    switch (fmt) {
+        case FMT_CU8: SDRB_COLS(FMT_CU8) break;
+        case FMT_CS16: SDRB_COLS(FMT_CS16) break;
+        case FMT_CF32: SDRB_COLS(FMT_CF32) break;
+        default: return cudaErrorInvalidValue;
+    }
+#undef SDRB_COLS
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    return B == 4096 ? tp_rows<16>(Y, power, small, n_frames * A, A, sm_count, st)
+                     : tp_rows<32>(Y, power, small, n_frames * A, A, sm_count, st);
 }
 
 }  // namespace sdrb

@@ -75,8 +75,19 @@ SDRB_HD void fs_phase2(int t, cpx* E) {
 }
 
 // ---- phase 3: twiddle W_16C^(c kb) on load, DFT_C over c, power, fftshift, store
-template <int C>
-SDRB_HD void fs_phase3_pair(int p, const cpx* E, const cpx* T2, float* __restrict__ out) {
+// Where bin k of the transform goes.  Plain: the fft-shifted spectrum of an N-point frame.  Strided (the rows pass of
+// the two-pass scheme below): the transform is row `off` of `stride` rows, its bin k is bin off + stride k of the big
+// frame of stride N points.
+struct FsOutPlain {
+    SDRB_HD int operator()(int k, int n) const { return (k + n / 2) & (n - 1); }
+};
+struct FsOutStrided {
+    int stride, off;
+    SDRB_HD int operator()(int k, int n) const { return (off + stride * k + (stride * n) / 2) & (stride * n - 1); }
+};
+
+template <int C, class OUT>
+SDRB_HD void fs_phase3_pair(int p, const cpx* E, const cpx* T2, float* __restrict__ out, OUT where) {
     typedef FsGeom<C> G;
     const int ka = p & 15, kb = p >> 4;
     const cpx* base = E + ka * G::kPitch + kb * C;
@@ -89,17 +100,42 @@ SDRB_HD void fs_phase3_pair(int p, const cpx* E, const cpx* T2, float* __restric
     for (int kc = 0; kc < C; kc++) {
         const cpx x = v[dit_slot<G::kLogC>(kc)];
         // re*re + im*im (src/dsp/fft_process.cpp:85); bin k lands at (k + N/2) mod N (:92-97)
-        out[(p + 256 * kc + G::N / 2) & (G::N - 1)] = x.x * x.x + x.y * x.y;
+        out[where(p + 256 * kc, G::N)] = x.x * x.x + x.y * x.y;
     }
 }
-template <int C>
-SDRB_HD void fs_phase3(int t, const cpx* E, const cpx* T2, float* __restrict__ out) {
+template <int C, class OUT>
+SDRB_HD void fs_phase3(int t, const cpx* E, const cpx* T2, float* __restrict__ out, OUT where) {
     typedef FsGeom<C> G;
     if (C == 32) {
-        if (t < 256) fs_phase3_pair<C>(t, E, T2, out);
+        if (t < 256) fs_phase3_pair<C>(t, E, T2, out, where);
     } else {
 #pragma unroll
-        for (int j = 0; j < (C >= 16 ? 1 : 16 / C); j++) fs_phase3_pair<C>(t + G::T * j, E, T2, out);
+        for (int j = 0; j < (C >= 16 ? 1 : 16 / C); j++) fs_phase3_pair<C>(t + G::T * j, E, T2, out, where);
+    }
+}
+
+// ---- two-pass scheme for N = A B, B = 4096 or 8192, A = 2^LOGA <= 32 (32768 .. 262144 points):
+//   n = B a + b,  k = ka + A kb        X[ka + A kb] = sum_b W_B^(b kb) [ W_N^(b ka) sum_a x[B a + b] W_A^(a ka) ]
+//   columns pass: one thread per (frame, b): DFT_A over a in registers, twiddle W_N^(b ka), Y[frame][ka][b] (cf32)
+//   rows pass   : the one-CTA kernel above on the A rows of every frame, bin kb of row ka stored at ka + A kb
+template <int FMT, int LOGA>
+SDRB_HD void fs_cols(int b, int B, const typename Ingest2<FMT>::raw_t* frame, const cpx* TPc, cpx* __restrict__ Yframe) {
+    constexpr int A = 1 << LOGA;
+    cpx v[A];
+#pragma unroll
+    for (int a = 0; a < A; a++) v[a] = Ingest2<FMT>::cvt(frame[(size_t)B * a + b]);
+    fft_dit<LOGA>(v);
+    cpx P[LOGA];
+#pragma unroll
+    for (int j = 0; j < LOGA; j++) P[j] = TPc[(size_t)j * B + b];
+    cpx w[A];
+    Yframe[b] = v[0];
+#pragma unroll
+    for (int k = 1; k < A; k++) {
+        const int low = k & (-k);
+        const int j = low == 1 ? 0 : (low == 2 ? 1 : (low == 4 ? 2 : (low == 8 ? 3 : 4)));
+        w[k] = (k == low) ? P[j] : cmul(w[k - low], P[j]);
+        Yframe[(size_t)k * B + b] = cmul(v[dit_slot<LOGA>(k)], w[k]);
     }
 }
 

@@ -39,6 +39,16 @@ inline std::vector<cpx> make_fs_tables(int n) {
     return t;
 }
 
+// Two-pass scheme (fft_small.cu), N = A B: TPc[j][b] = W_N^(b 2^j), j < log2 A, then the small kernel's tables for B points
+inline std::vector<cpx> make_tp_tables(int n, int B, int loga) {
+    std::vector<cpx> t((size_t)loga * B);
+    for (int j = 0; j < loga; j++)
+        for (int b = 0; b < B; b++) t[(size_t)j * B + b] = twiddle((long long)b << j, n);
+    const std::vector<cpx> s = make_fs_tables(B);
+    t.insert(t.end(), s.begin(), s.end());
+    return t;
+}
+
 // Layout: TL | TLO | THI | TB  (FbGeom<R>::kTables entries), see fft_big.cuh
 template <int R>
 inline std::vector<cpx> make_fb_tables() {

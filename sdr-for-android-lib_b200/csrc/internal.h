@@ -135,6 +135,12 @@ bool fft_small_supports(int n);
 int fft_small_table_elems(int n);
 cudaError_t launch_fft_small(int fmt, const void* iq, float* power, const cpx* tables, int n, int n_frames, int sm_count,
                              cudaStream_t st);
+// two-pass scheme for 32768 / 131072 / 262144 points: radix-A columns pass + the one-CTA kernel on the rows
+// (tables: make_tp_tables(n, B, log2 A) with B = 4096 (8192 for 262144); Y: n_frames * n complex of scratch)
+bool fft_twopass_supports(int n);
+int fft_twopass_table_elems(int n);
+cudaError_t launch_fft_twopass(int fmt, const void* iq, float* power, cpx* Y, const cpx* tables, int n, int n_frames,
+                               int sm_count, cudaStream_t st);
 cudaError_t launch_fft_generic(int fmt, const void* iq, float* power, cpx* scratch_a, cpx* scratch_b,
                                const cpx* twiddles, int n, int n_frames, cudaStream_t st, int* launches);
 int fft_generic_passes(int n);
