@@ -8,9 +8,9 @@
 //   phase 3: DFT_C over c   pairs p = ka + 16 kb: thread u takes p = u + T j, j < 16 / C  (C = 32: threads u < 256, one
 //            32-point transform each), then |X|^2, fftshift folded into the store index: for a fixed kc a warp's 32
 //            pairs are 32 consecutive bins
-// Exchange buffer E[ka][16 C + 1]: phase-1 stores and phase-2 accesses of a half-warp fall on distinct 8-byte bank
-// pairs for C >= 16, phase-3 loads (16 consecutive ka) for every C because the pitch is odd; for C < 16 phase 2 is
-// two-way conflicted (a half-warp spans 16 / C planes one element apart).
+// Exchange buffer E[ka][16 C + 1]: the 8-byte accesses of a half-warp fall on 16 distinct bank pairs in every phase
+// and for every C (phase 3 reads 16 consecutive planes: the pitch is odd; phase 2 picks its planes accordingly);
+// audited in tests/cpp/fft_small_sim.cpp.
 // Every thread holds 16 points in every phase; small transforms share a CTA (256 / T of them).
 // The register codelets are the FMA-form decimation-in-time ones of fft_dit.cuh.
 // Phase functions are __host__ __device__ so that tests/cpp/fft_small_sim.cpp runs them thread by thread.
@@ -64,7 +64,18 @@ SDRB_HD void fs_phase1(int t, const typename Ingest2<FMT>::raw_t* in, const cpx*
 template <int C>
 SDRB_HD void fs_phase2(int t, cpx* E) {
     typedef FsGeom<C> G;
-    const int ka = t / C, c = t % C;
+    // which (ka, c) a thread takes is free (the pass is in place per pair).  For C < 16 a half-warp spans 16 / C planes:
+    // lane l of half-warp h takes c = l % C and plane ka = (l / C) C + h, so that (ka + c) mod 16 = (l + h) mod 16 runs
+    // over all 16 bank pairs (consecutive planes would fall on top of each other: four-way conflicts at C = 4)
+    int ka, c;
+    if (C < 16) {
+        const int h = t >> 4, l = t & 15;
+        c = l % C;
+        ka = (l / C) * C + h;
+    } else {
+        ka = t / C;
+        c = t % C;
+    }
     cpx* base = E + ka * G::kPitch + c;
     cpx v[16];
 #pragma unroll

@@ -26,3 +26,11 @@ def test_four_step_phase_functions(tmp_path, radix):
     r = subprocess.run([_build(tmp_path, "fft_big_sim"), str(radix)], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "0 bad bins" in r.stdout
+
+
+def test_small_fft_phase_functions(tmp_path):
+    """256 .. 8192 points through the one-CTA kernel's phase functions, 32768 points through the two-pass scheme
+    built on it, and the bank-pair audit of its exchange buffer."""
+    r = subprocess.run([_build(tmp_path, "fft_small_sim")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "all sizes ok" in r.stdout
