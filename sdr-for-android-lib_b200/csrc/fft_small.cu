@@ -3,7 +3,8 @@
 // in the 16K kernel (reference: src/dsp/fft_process.cpp:62-97); before this kernel these lengths went through the
 // radix-16 Stockham passes over global memory (16 B per sample and pass: 59-74 GS/s against 372 at 16384 points).
 //
-//   k_fft_small<FMT, C>: persistent, 256 threads (512 for 8192 points), 256 / (16 C) transforms per CTA and round;
+//   k_fft_small<FMT, C> (256 .. 4096 points), k_fft_8k<FMT> (8192): persistent, 256 threads, 256 / (16 C) transforms per CTA
+//   and round;
 //   raw IQ straight into registers (a warp reads 32 consecutive samples per load), two in-place exchanges through
 //   shared memory (16 C + 1 complex per plane), twiddle tables in shared memory, spectra out 128 bytes per warp store.
 #include "fft_small.cuh"
@@ -46,6 +47,47 @@ k_fft_small(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restri
     }
 }
 
+// 8192 points: the 32 * 16 * 16 shape (fft_small.cuh: Fs8k), 256 threads x 32 points, every thread busy in every phase
+template <int FMT, bool STRIDED>
+__global__ void __launch_bounds__(256, 2)
+k_fft_8k(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict__ out, const cpx* __restrict__ tables,
+         int n_frames, int rows_per_frame) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cpx* E = reinterpret_cast<cpx*>(smem_raw);
+    cpx* TP = E + Fs8k::kE;
+    cpx* T2 = TP + Fs8k::kTP;
+    const int t = threadIdx.x;
+    for (int i = t; i < Fs8k::kTables; i += 256) TP[i] = tables[i];
+    __syncthreads();
+    for (long long f = blockIdx.x; f < n_frames; f += gridDim.x) {
+        fs8k_phase1<FMT>(t, in + (size_t)f * Fs8k::N, TP, E);
+        __syncthreads();
+        fs8k_phase2(t, E);
+        __syncthreads();
+        if (STRIDED) {
+            const long long big = f / rows_per_frame;
+            const FsOutStrided where = {rows_per_frame, (int)(f - big * rows_per_frame)};
+            fs8k_phase3(t, E, T2, out + (size_t)big * rows_per_frame * Fs8k::N, where);
+        } else {
+            fs8k_phase3(t, E, T2, out + (size_t)f * Fs8k::N, FsOutPlain());
+        }
+        __syncthreads();
+    }
+}
+constexpr int kSmem8k = (Fs8k::kE + Fs8k::kTables) * (int)sizeof(cpx);
+template <int FMT, bool STRIDED>
+static cudaError_t launch_8k(const void* iq, float* power, const cpx* tables, int n_frames, int rows_per_frame, int sm_count,
+                             cudaStream_t st) {
+    static int per_sm = 0;
+    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fft_8k<FMT, STRIDED>, 256, kSmem8k) != cudaSuccess || per_sm < 1))
+        per_sm = 1;
+    const long long slots = (long long)per_sm * (sm_count > 0 ? sm_count : 148);
+    const int grid = (int)(n_frames < slots ? n_frames : slots);
+    k_fft_8k<FMT, STRIDED><<<grid, 256, kSmem8k, st>>>(static_cast<const typename Ingest2<FMT>::raw_t*>(iq), power, tables, n_frames,
+                                                       rows_per_frame);
+    return cudaGetLastError();
+}
+
 template <int C>
 static constexpr int fs_smem() { return (FsGeom<C>::kPerCta * FsGeom<C>::kE + FsGeom<C>::kTables) * (int)sizeof(cpx); }
 
@@ -55,7 +97,7 @@ static cudaError_t fs_prepare_c() {
     if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CU8, C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CS16, C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CF32, C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
-    if (C >= 16) return cudaFuncSetAttribute(k_fft_small<FMT_CF32, C, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>());
+    if (C == 16) return cudaFuncSetAttribute(k_fft_small<FMT_CF32, C, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>());
     return cudaSuccess;
 }
 cudaError_t fft_small_prepare() {
@@ -65,11 +107,14 @@ cudaError_t fft_small_prepare() {
     if ((e = fs_prepare_c<4>()) != cudaSuccess) return e;
     if ((e = fs_prepare_c<8>()) != cudaSuccess) return e;
     if ((e = fs_prepare_c<16>()) != cudaSuccess) return e;
-    return fs_prepare_c<32>();
+    if ((e = cudaFuncSetAttribute(k_fft_8k<FMT_CU8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem8k)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fft_8k<FMT_CS16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem8k)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fft_8k<FMT_CF32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem8k)) != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k_fft_8k<FMT_CF32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem8k);
 }
 
 bool fft_small_supports(int n) { return n >= 256 && n <= 8192 && (n & (n - 1)) == 0; }
-int fft_small_table_elems(int n) { return fft_small_supports(n) ? 80 * (n / 256) : 0; }
+int fft_small_table_elems(int n) { return !fft_small_supports(n) ? 0 : (n == 8192 ? Fs8k::kTables : 80 * (n / 256)); }
 
 template <int FMT, int C>
 static cudaError_t fs_launch_fc(const void* iq, float* power, const cpx* tables, int n_frames, int sm_count, cudaStream_t st) {
@@ -103,7 +148,13 @@ cudaError_t launch_fft_small(int fmt, const void* iq, float* power, const cpx* t
         case 1024: return fs_launch_c<4>(fmt, iq, power, tables, n_frames, sm_count, st);
         case 2048: return fs_launch_c<8>(fmt, iq, power, tables, n_frames, sm_count, st);
         case 4096: return fs_launch_c<16>(fmt, iq, power, tables, n_frames, sm_count, st);
-        case 8192: return fs_launch_c<32>(fmt, iq, power, tables, n_frames, sm_count, st);
+        case 8192:
+            switch (fmt) {
+                case FMT_CU8: return launch_8k<FMT_CU8, false>(iq, power, tables, n_frames, 1, sm_count, st);
+                case FMT_CS16: return launch_8k<FMT_CS16, false>(iq, power, tables, n_frames, 1, sm_count, st);
+                case FMT_CF32: return launch_8k<FMT_CF32, false>(iq, power, tables, n_frames, 1, sm_count, st);
+                default: return cudaErrorInvalidValue;
+            }
         default: return cudaErrorInvalidValue;
     }
 }
@@ -160,7 +211,7 @@ cudaError_t launch_fft_twopass(int fmt, const void* iq, float* power, cpx* Y, co
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     return B == 4096 ? tp_rows<16>(Y, power, small, n_frames * A, A, sm_count, st)
-                     : tp_rows<32>(Y, power, small, n_frames * A, A, sm_count, st);
+                     : launch_8k<FMT_CF32, true>(Y, power, small, n_frames * A, A, sm_count, st);
 }
 
 }  // namespace sdrb

@@ -30,6 +30,14 @@ inline std::vector<cpx> make_f2_tables() {
 
 // Small one-CTA kernel (fft_small.cuh), N = 256 C: TP[j][t] = W_N^(t 2^j) (j < 4, t < 16 C), then T2[kb][c] = W_16C^(c kb)
 inline std::vector<cpx> make_fs_tables(int n) {
+    if (n == 8192) {   // the 32 * 16 * 16 kernel (Fs8k): TP[j][t] = W_N^(t 2^j), j < 5, t < 256; T2[kb][c] = W_256^(c kb)
+        std::vector<cpx> t(5 * 256 + 256);
+        for (int j = 0; j < 5; j++)
+            for (int r = 0; r < 256; r++) t[(size_t)j * 256 + r] = twiddle((long long)r << j, n);
+        for (int kb = 0; kb < 16; kb++)
+            for (int c = 0; c < 16; c++) t[5 * 256 + kb * 16 + c] = twiddle((long long)c * kb, 256);
+        return t;
+    }
     const int C = n / 256, T = 16 * C;
     std::vector<cpx> t((size_t)4 * T + 16 * C);
     for (int j = 0; j < 4; j++)
