@@ -574,3 +574,22 @@ def test_full_size_properties_default_workload(sdrb):
     finally:
         small.close()
         ctx.close()
+
+
+@pytest.mark.parametrize("n,S,B", [(512, 4001, 3), (4096, 2500, 2), (8192, 1300, 1), (32768, 150, 2)])
+def test_small_fft_kernels_over_many_rounds(sdrb, gpu_ctx, n, S, B):
+    """The persistent one-CTA kernels (256 .. 8192 points) and the two-pass scheme on batches that take every CTA
+    through many rounds, with a frame count that is not a multiple of the transforms per CTA: 24 frames spread over
+    the batch against the oracle, and every frame against the Parseval sum."""
+    fs = 2_000_000
+    iq = make_iq(sdrb, 0, fs, 5, S, B, n)
+    gpu_ctx.configure(sdrb.Config(FC, fs, n, 5, inputFormat=0), S, B)
+    gpu_ctx.process(iq, B, sdrb.STAGE_FFT)
+    pw = gpu_ctx.power_all().reshape(S, B, n)
+    x = (iq.astype(np.float64) - 127.4) / 128.0
+    energy = (x * x).sum(axis=(2, 3)) * n
+    assert np.allclose(pw.astype(np.float64).sum(axis=2), energy, rtol=2e-5)
+    for k in range(24):
+        s, b = (k * 977 + 3) % S, k % B
+        ref = ol.oracle_power(ol.to_cf32(iq[s, b], 0))
+        assert np.all(np.abs(pw[s, b] - ref) <= power_tolerance(ref)), (s, b)
