@@ -7,6 +7,8 @@
 //   and round;
 //   raw IQ straight into registers (a warp reads 32 consecutive samples per load), two in-place exchanges through
 //   shared memory (16 C + 1 complex per plane), twiddle tables in shared memory, spectra out 128 bytes per warp store.
+#include <cstdlib>
+
 #include "fft_small.cuh"
 #include "internal.h"
 
@@ -88,6 +90,48 @@ static cudaError_t launch_8k(const void* iq, float* power, const cpx* tables, in
     return cudaGetLastError();
 }
 
+// Rows pass with FOUR rows of a big frame per CTA (4096-point rows, A a multiple of 4): the powers of the four
+// spectra are gathered in shared memory and bin kb of rows 4g .. 4g + 3 goes out as ONE 16-byte store at 4g + A kb.
+// With one row per CTA (k_fft_small<.., true>) every float of a warp store lands in its own sector.
+__global__ void __launch_bounds__(1024, 1)
+k_fft_rows4(const cpx* __restrict__ Y, float* __restrict__ out, const cpx* __restrict__ tables, int n_groups, int A) {
+    typedef FsGeom<16> G;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cpx* Eall = reinterpret_cast<cpx*>(smem_raw);
+    cpx* TP = Eall + 4 * G::kE;
+    cpx* T2 = TP + G::kTP;
+    float* S = reinterpret_cast<float*>(smem_raw);          // [4][4096] powers, over the exchange buffers
+    for (int i = threadIdx.x; i < G::kTables; i += 1024) TP[i] = tables[i];
+    const int sub = threadIdx.x >> 8, t = threadIdx.x & 255;
+    cpx* E = Eall + sub * G::kE;
+    const int N = A * G::N;
+    __syncthreads();
+    for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+        fs_phase1<FMT_CF32, 16>(t, Y + ((size_t)4 * grp + sub) * G::N, TP, E);
+        __syncthreads();
+        fs_phase2<16>(t, E);
+        __syncthreads();
+        float pw[16];
+        fs_phase3<16>(t, E, T2, pw, FsOutKc());
+        __syncthreads();                                    // every thread holds its bins: the buffers are free
+#pragma unroll
+        for (int kc = 0; kc < 16; kc++) S[sub * G::N + t + 256 * kc] = pw[kc];
+        __syncthreads();
+        const long long row0 = (long long)4 * grp;
+        const long long big = row0 / A;
+        const int ka0 = (int)(row0 - big * A);
+        float* o = out + (size_t)big * N;
+#pragma unroll
+        for (int it = 0; it < 4; it++) {
+            const int k = it * 1024 + threadIdx.x;
+            const float4 v = make_float4(S[k], S[G::N + k], S[2 * G::N + k], S[3 * G::N + k]);
+            *reinterpret_cast<float4*>(o + ((ka0 + A * k + N / 2) & (N - 1))) = v;
+        }
+        __syncthreads();                                    // the next group's phase 1 overwrites S
+    }
+}
+constexpr int kSmemRows4 = (4 * FsGeom<16>::kE + FsGeom<16>::kTables) * (int)sizeof(cpx);
+
 template <int C>
 static constexpr int fs_smem() { return (FsGeom<C>::kPerCta * FsGeom<C>::kE + FsGeom<C>::kTables) * (int)sizeof(cpx); }
 
@@ -110,7 +154,8 @@ cudaError_t fft_small_prepare() {
     if ((e = cudaFuncSetAttribute(k_fft_8k<FMT_CU8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem8k)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_fft_8k<FMT_CS16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem8k)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_fft_8k<FMT_CF32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem8k)) != cudaSuccess) return e;
-    return cudaFuncSetAttribute(k_fft_8k<FMT_CF32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem8k);
+    if ((e = cudaFuncSetAttribute(k_fft_8k<FMT_CF32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem8k)) != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k_fft_rows4, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemRows4);
 }
 
 bool fft_small_supports(int n) { return n >= 256 && n <= 8192 && (n & (n - 1)) == 0; }
@@ -210,8 +255,15 @@ cudaError_t launch_fft_twopass(int fmt, const void* iq, float* power, cpx* Y, co
 #undef SDRB_COLS
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    return B == 4096 ? tp_rows<16>(Y, power, small, n_frames * A, A, sm_count, st)
-                     : launch_8k<FMT_CF32, true>(Y, power, small, n_frames * A, A, sm_count, st);
+    if (B == 4096) {
+        static const bool one_row = getenv("SDRB_FFT_ROWS1") && getenv("SDRB_FFT_ROWS1")[0] == '1';   // test hook
+        if (one_row) return tp_rows<16>(Y, power, small, n_frames * A, A, sm_count, st);
+        const int n_groups = n_frames * A / 4;
+        const int slots = sm_count > 0 ? sm_count : 148;
+        k_fft_rows4<<<n_groups < slots ? n_groups : slots, 1024, kSmemRows4, st>>>(Y, power, small, n_groups, A);
+        return cudaGetLastError();
+    }
+    return launch_8k<FMT_CF32, true>(Y, power, small, n_frames * A, A, sm_count, st);
 }
 
 }  // namespace sdrb

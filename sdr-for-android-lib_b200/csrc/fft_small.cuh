@@ -98,6 +98,10 @@ struct FsOutStrided {
     SDRB_HD int operator()(int k, int n) const { return (off + stride * k + (stride * n) / 2) & (stride * n - 1); }
 };
 
+struct FsOutKc {   // 4096 points, one pair per thread: bin p + 256 kc goes to slot kc of the thread's own array
+    SDRB_HD int operator()(int k, int) const { return k >> 8; }
+};
+
 template <int C, class OUT>
 SDRB_HD void fs_phase3_pair(int p, const cpx* E, const cpx* T2, float* __restrict__ out, OUT where) {
     typedef FsGeom<C> G;
