@@ -10,6 +10,7 @@ no data-path collective ("scaling": "weak": per-GPU work is fixed as N grows).
 
     python bench.py [--gpus N --steps K --warmup W]            # our arm, default workload
     python bench.py --config c2|c1|c3|c3ref|c3fft|c4|c5|c5ru16  # the other BASELINE configurations
+    python bench.py --config n1024|n4096|n8192|n32768|n4096ssb  # other block lengths
     python bench.py --impl reference [...]                     # the reference's CPU path, host cores
 
 Prints ONE JSON line (rank 0).  `value` is device-timed (CUDA events on the launching stream) with the
@@ -71,6 +72,17 @@ WORKLOADS = {
                S=16, B=4, n=1048576, fs=10_000_000, fmt=CF32, stages=F_FFT, extra={}),
     "c5ru16": dict(what="raw Airspy 12-bit ADC words (real->IQ on the GPU), 65536-pt FFT + peak tracking",
                    S=256, B=8, n=65536, fs=10_000_000, fmt=RU16, stages=F_FFT, extra={}),
+    # other block lengths (samplesPerReading is a run-time setting of the reference): the same number of samples per call
+    "n1024": dict(what="u8 streams, 1024-pt FFT + peak + strength (one-CTA shared-memory kernel)",
+                  S=16384, B=16, n=1024, fs=2_000_000, fmt=CU8, stages=F_FFT, extra={}),
+    "n4096": dict(what="u8 streams, 4096-pt FFT + peak + strength (one-CTA shared-memory kernel)",
+                  S=8192, B=8, n=4096, fs=2_000_000, fmt=CU8, stages=F_FFT, extra={}),
+    "n8192": dict(what="u8 streams, 8192-pt FFT + peak + strength (one-CTA shared-memory kernel, 32 x 16 x 16)",
+                  S=4096, B=8, n=8192, fs=2_000_000, fmt=CU8, stages=F_FFT, extra={}),
+    "n32768": dict(what="u8 streams, 32768-pt FFT + peak + strength (two passes: radix-8 columns + 4096-point rows)",
+                   S=1024, B=8, n=32768, fs=2_000_000, fmt=CU8, stages=F_FFT, extra={}),
+    "n4096ssb": dict(what="u8 streams, 2 MS/s, 4096-pt FFT + peak + strength + USB demod, one reading per call",
+                     S=65536, B=1, n=4096, fs=2_000_000, fmt=CU8, stages=F_FFT | F_SSB, extra={}),
 }
 
 
@@ -458,7 +470,9 @@ def run_ours(args):
             fft_ms.append(ctx.last_fft_kernel_ms()[0])
         k_ms = float(np.median(fft_ms))
         k_name = {16384: f"k_fft16k2<{FMT_NAME[CF32 if fmt == RU16 else fmt].upper()}>", 65536: "k_fbA<16>+k_fbB<16>",
-                  1048576: "k_fbA<32>+k_fbB<32>"}.get(n, "k_stockham passes")
+                  1048576: "k_fbA<32>+k_fbB<32>", 8192: "k_fft_8k", 32768: "k_fs_cols<3>+k_fft_rows4",
+                  131072: "k_fs_cols<5>+k_fft_rows4", 262144: "k_fs_cols<5>+k_fft_8k"}.get(
+                      n, "k_fft_small" if 256 <= n <= 4096 and n & (n - 1) == 0 else "k_stockham passes")
         k_bytes = (FMT_BYTES[CF32 if fmt == RU16 else fmt] + 4) * fft_frames * n
         k_ach = k_bytes / (k_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "achieved": k_ach, "peak": peak, "unit": "GB/s", "frac": k_ach / peak,
