@@ -235,6 +235,9 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
             const float* Pw = P + plo[j];
             float* sw = stage + cum[j];
             const int lenj = cum[j + 1] - cum[j];
+            // (unrolled: with one warp per frame and few frames in flight every iteration's load + log10f latency
+            // was exposed; eight independent iterations in flight hide it.  The per-lane order of the sum is unchanged.)
+#pragma unroll 8
             for (int i = lane; i < lenj; i += 32) {
                 const float d = db10_fast(__ldg(Pw + i));
                 sw[i] = d;
@@ -248,6 +251,7 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
     // the staging loop above indexes lanes relative to each window's start, the loop below absolutely: a lane reads
     // what another lane wrote, so the writes have to be ordered before the reads (shared or global scratch alike)
     __syncwarp();
+#pragma unroll 8
     for (int i = lane; i < pooledN; i += 32) stage[i] = fabsf(__fsub_rn(stage[i], perBinMean));   // :265-266
     __syncwarp();
     // ---- :267-268 median of the gaps: 4-pass radix select on the bit pattern; each lane owns 8 of
@@ -259,6 +263,7 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
 #pragma unroll
         for (int j = 0; j < 8; j++) hist[lane + 32 * j] = 0;
         __syncwarp();
+#pragma unroll 8
         for (int i = lane; i < pooledN; i += 32) {
             const unsigned bits = __float_as_uint(stage[i]);
             if ((bits & mask) == prefix) atomicAdd(&hist[(bits >> shift) & 255u], 1);
