@@ -131,7 +131,8 @@ __device__ __forceinline__ float mad4(const float* x, int nb, float mean) {
     return m == 0 ? g[0] : (m == 1 ? g[1] : g[2]);
 }
 
-template <bool USE_SMEM>
+// U: unroll factor of the pooled-bin loops (8 when many bins are pooled per frame, 1 otherwise; see the launcher)
+template <bool USE_SMEM, int U>
 __global__ void __launch_bounds__(EST_WARPS * 32)
 k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo_p, const BandStat* __restrict__ stats,
             FrameLocal* __restrict__ local, float* __restrict__ gscratch, int pooled_cap, int n_frames) {
@@ -235,9 +236,9 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
             const float* Pw = P + plo[j];
             float* sw = stage + cum[j];
             const int lenj = cum[j + 1] - cum[j];
-            // (unrolled: with one warp per frame and few frames in flight every iteration's load + log10f latency
-            // was exposed; eight independent iterations in flight hide it.  The per-lane order of the sum is unchanged.)
-#pragma unroll 8
+            // (U = 8: with one warp per frame and long pooled stretches every iteration's load + log10f latency was
+            // exposed; eight independent iterations in flight hide it.  The per-lane order of the sum is unchanged.)
+#pragma unroll U
             for (int i = lane; i < lenj; i += 32) {
                 const float d = db10_fast(__ldg(Pw + i));
                 sw[i] = d;
@@ -251,7 +252,7 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
     // the staging loop above indexes lanes relative to each window's start, the loop below absolutely: a lane reads
     // what another lane wrote, so the writes have to be ordered before the reads (shared or global scratch alike)
     __syncwarp();
-#pragma unroll 8
+#pragma unroll U
     for (int i = lane; i < pooledN; i += 32) stage[i] = fabsf(__fsub_rn(stage[i], perBinMean));   // :265-266
     __syncwarp();
     // ---- :267-268 median of the gaps: 4-pass radix select on the bit pattern; each lane owns 8 of
@@ -263,7 +264,7 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
 #pragma unroll
         for (int j = 0; j < 8; j++) hist[lane + 32 * j] = 0;
         __syncwarp();
-#pragma unroll 8
+#pragma unroll U
         for (int i = lane; i < pooledN; i += 32) {
             const unsigned bits = __float_as_uint(stage[i]);
             if ((bits & mask) == prefix) atomicAdd(&hist[(bits >> shift) & 255u], 1);
@@ -443,7 +444,10 @@ static int pooled_cap_of(const EstGeometry& g) {
 cudaError_t estimator_prepare() {
     cudaError_t e = cudaFuncSetAttribute(k_band_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(k_estimator<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    if ((e = cudaFuncSetAttribute(k_estimator<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  EST_WARPS * EST_SMEM_POOL_FLOATS * (int)sizeof(float))) != cudaSuccess)
+        return e;
+    return cudaFuncSetAttribute(k_estimator<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 EST_WARPS * EST_SMEM_POOL_FLOATS * (int)sizeof(float));
 }
 
@@ -486,12 +490,16 @@ cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, const
     }
     const int cap = pooled_cap_of(h_geo);
     const int grid = (n_frames + EST_WARPS - 1) / EST_WARPS;
+    // Unrolled pooled-bin loops pay when a lane walks many bins (1 M points, 25 kHz focus: ~250 per lane, C5 +11 %) and
+    // cost instructions when it walks a handful (1024-point frames: -8 %): measured, the switch is around 32 per lane.
+    const bool deep = cap >= 1024;
     if (cap <= EST_SMEM_POOL_FLOATS) {
-        k_estimator<true><<<grid, EST_WARPS * 32, (size_t)EST_WARPS * cap * sizeof(float), st>>>(
-            power, d_geo, stats, d_local, nullptr, cap, n_frames);
+        const size_t sm = (size_t)EST_WARPS * cap * sizeof(float);
+        if (deep) k_estimator<true, 8><<<grid, EST_WARPS * 32, sm, st>>>(power, d_geo, stats, d_local, nullptr, cap, n_frames);
+        else k_estimator<true, 1><<<grid, EST_WARPS * 32, sm, st>>>(power, d_geo, stats, d_local, nullptr, cap, n_frames);
     } else {
         float* gs = scratch + band_floats(cap_frames) + frame0 * (size_t)cap;
-        k_estimator<false><<<grid, EST_WARPS * 32, 0, st>>>(power, d_geo, stats, d_local, gs, cap, n_frames);
+        k_estimator<false, 8><<<grid, EST_WARPS * 32, 0, st>>>(power, d_geo, stats, d_local, gs, cap, n_frames);
     }
     return cudaGetLastError();
 }
