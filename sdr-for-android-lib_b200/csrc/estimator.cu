@@ -166,14 +166,20 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
     const int len = lane <= nWin ? g.segOff[lane + 1] - g.segOff[lane] : 1;
     // dB figures of the bands, one lane per band (:149-155, :203-213)
     float dbA = 0.0f, dbB = 0.0f;   // focus: (absPeakDb candidate, signalPowerDb); window: (meanDb, best1kDb)
+    const float focusSum = __shfl_sync(FULL, bs.sum, 0), focusBestRun = __shfl_sync(FULL, bs.bestRun, 0);
+    // the focus band's best-1 kHz mean (:310-318), whose dB figure is needed at the very end: lane 31 (never a window)
+    // takes it through the same pair of log10 calls instead of a third, divergent one
+    const float fb = g.focusLen < W ? __fdiv_rn(focusSum, (float)g.focusLen) : __fdiv_rn(focusBestRun, (float)W);
+    float dbFb;
     {   // arguments first, then ONE pair of log10 calls for the whole warp (the double log10 is ~130 instructions;
         // under a lane-0 / window branch it would run four times)
         const bool want = lane == 0 || (isWin && valid);
         const float meanP = __fdiv_rn(bs.sum, (float)(lane == 0 ? g.focusLen : len));
-        const float argA = lane == 0 ? bs.maxP : meanP;
+        const float argA = lane == 31 ? fb : (lane == 0 ? bs.maxP : meanP);
         const float argB = (lane == 0 || len < W) ? meanP : __fdiv_rn(bs.bestRun, (float)W);
-        const float a = db10(want ? argA : 1.0f), b = db10(want ? argB : 1.0f);
+        const float a = db10((want || lane == 31) ? argA : 1.0f), b = db10(want ? argB : 1.0f);
         if (want) { dbA = a; dbB = b; }
+        dbFb = __shfl_sync(FULL, a, 31);
     }
     FrameLocal o = {};
     {   // ---- :142-155 focus band
@@ -185,7 +191,6 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
         o.valid = valid ? 1 : 0;
         o.best1kStart = -1;
     }
-    const float focusSum = __shfl_sync(FULL, bs.sum, 0), focusBestRun = __shfl_sync(FULL, bs.bestRun, 0);
     const int focusBestStart = __shfl_sync(FULL, bs.bestStart, 0);
     if (!valid) {
         if (lane == 0) local[frame] = o;
@@ -308,9 +313,8 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
         // :299-327 best-1 kHz SNR
         const float sigmaFloor1k = __fdiv_rn(sigmaBin, g.sqrtWin1k);
         const float sigma1k = fmaxf(fmaxf(mad1k, sigmaFloor1k), 0.5f);
-        const float fb = g.focusLen < W ? __fdiv_rn(focusSum, (float)g.focusLen) : __fdiv_rn(focusBestRun, (float)W);
         if (fb > 0.0f) {
-            o.best1kHzSnrDb = __fsub_rn(db10(fb), mean1k);
+            o.best1kHzSnrDb = __fsub_rn(dbFb, mean1k);
             o.best1kHzSnrSigma = __fdiv_rn(o.best1kHzSnrDb, sigma1k);
             o.best1kStart = g.focusLo + focusBestStart;
         } else {
