@@ -38,7 +38,8 @@ def test_synth_device_matches_host(sdrb, gpu_ctx):
 @pytest.mark.parametrize("fmt", [0, 1, 2])
 @pytest.mark.parametrize("n,fs", [(16384, 2_000_000), (4096, 2_000_000), (65536, 30_720_000), (256, 250_000),
                                   (32768, 2_500_000), (2, 250_000), (8, 250_000), (512, 250_000), (1024, 1_000_000),
-                                  (2048, 2_000_000), (8192, 2_000_000), (128, 250_000), (131072, 10_000_000)])
+                                  (2048, 2_000_000), (8192, 2_000_000), (128, 250_000), (131072, 10_000_000),
+                                  (262144, 10_000_000), (524288, 10_000_000)])
 def test_power_spectrum_parity(sdrb, gpu_ctx, fmt, n, fs):
     S, B = 3, 2
     iq = make_iq(sdrb, fmt, fs, 11, S, B, n)
