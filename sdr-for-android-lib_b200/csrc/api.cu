@@ -656,7 +656,7 @@ static int ensure_fft_buffers(sdrb_ctx* ctx) {
         CK(cudaMalloc(&ctx->d_fs_tables, tb.size() * sizeof(cpx)));
         CK(cudaMemcpy(ctx->d_fs_tables, tb.data(), tb.size() * sizeof(cpx), cudaMemcpyHostToDevice));
     }
-    if ((ctx->fftPath == 0 || ctx->fftPath == 4 || ctx->fftPath == 5) && ctx->front && !ctx->d_front) {
+    if ((ctx->fftPath == 0 || ctx->fftPath == 5) && ctx->front && !ctx->d_front) {   // (path 4 fuses the front end)
         size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
         if (chunk < 1) chunk = 1;
         if (chunk > frames) chunk = frames;
@@ -913,20 +913,21 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
             // extension front end needs its cf32 pre-pass buffer
             size_t chunk = kGenericScratchBytes / ((size_t)n * sizeof(cpx));
             if (chunk < 1) chunk = 1;
-            if (ctx->fftPath == 4 && !ctx->front) chunk = (size_t)frames;
+            if (ctx->fftPath == 4) chunk = (size_t)frames;
             if (ctx->fftPath == 5 && !ctx->front) chunk = kTwoPassScratchBytes / ((size_t)n * sizeof(cpx));
             for (size_t f0 = 0; f0 < (size_t)frames; f0 += chunk) {
                 const int nf = (int)((size_t)frames - f0 < chunk ? (size_t)frames - f0 : chunk);
                 const void* src = static_cast<const unsigned char*>(d_iq) + f0 * n * bps;
                 int src_fmt = fmt;
-                if (ctx->front) {   // extension front end as a pre-pass: raw IQ -> (x - mean) * w in cf32
+                if (ctx->front && ctx->fftPath != 4) {   // extension front end as a pre-pass: raw IQ -> (x - mean) * w in cf32
                     CK(launch_fft_front(fmt, src, ctx->d_front, ctx->d_win, n, nf, ctx->front, st));
                     fft_launches++;
                     src = ctx->d_front;
                     src_fmt = FMT_CF32;
                 }
                 if (ctx->fftPath == 4) {
-                    CK(launch_fft_small(src_fmt, src, power + f0 * n, ctx->d_fs_tables, n, nf, ctx->sm_count, st));
+                    CK(launch_fft_small(src_fmt, src, power + f0 * n, ctx->d_fs_tables, n, nf, ctx->sm_count, st, ctx->front,
+                                        ctx->d_win));
                     fft_launches++;
                 } else if (ctx->fftPath == 5) {
                     CK(launch_fft_twopass(src_fmt, src, power + f0 * n, ctx->d_sa, ctx->d_fs_tables, n, nf, ctx->sm_count, st));

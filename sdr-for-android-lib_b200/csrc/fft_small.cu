@@ -14,14 +14,54 @@
 
 namespace sdrb {
 
+// Extension front end between load and transform (no reference code: FFTProcessor::process feeds the raw block to FFTW,
+// src/dsp/fft_process.cpp:62-79; definition: oracle/sdr_oracle_ext.c).  front bit 1: subtract the block mean (per-thread
+// sum, shuffle tree over the transform's lanes of a warp, then over its warps through shared memory); bit 0: multiply by
+// the window table.  P points per thread at stride T; a transform owns T consecutive threads (T = 16 shares a warp with
+// another transform: the shuffle tree stays inside its 16 lanes).  Every thread of the CTA calls it (barrier inside).
+template <int P, int T>
+__device__ __forceinline__ void fs_front(int front, int t, int sub, cpx* v, const float* __restrict__ win, cpx* red) {
+    if (front & 2) {
+        cpx s = mk(0.f, 0.f);
+#pragma unroll
+        for (int a = 0; a < P; a++) s = cadd(s, v[a]);
+#pragma unroll
+        for (int d = (T < 32 ? T : 32) / 2; d > 0; d >>= 1) {
+            s.x += __shfl_xor_sync(0xffffffffu, s.x, d);
+            s.y += __shfl_xor_sync(0xffffffffu, s.y, d);
+        }
+        constexpr int W = T > 32 ? T / 32 : 1;               // warps per transform
+        if (T > 32) {
+            if ((t & 31) == 0) red[sub * W + (t >> 5)] = s;
+            __syncthreads();
+            s = mk(0.f, 0.f);
+#pragma unroll
+            for (int w = 0; w < W; w++) s = cadd(s, red[sub * W + w]);
+            __syncthreads();                                 // red is reused by the next round
+        }
+        const cpx m = mk(s.x * (1.0f / (float)(P * T)), s.y * (1.0f / (float)(P * T)));
+#pragma unroll
+        for (int a = 0; a < P; a++) v[a] = csub(v[a], m);
+    }
+    if (front & 1) {
+#pragma unroll
+        for (int a = 0; a < P; a++) {
+            const float w = __ldg(win + T * a + t);
+            v[a].x *= w;
+            v[a].y *= w;
+        }
+    }
+}
+
 // ROWS = 0: n_frames independent N-point frames.  ROWS = A > 0 (the rows pass of the two-pass scheme): n_frames counts
 // ROWS, row r = (big frame r / A, ka = r % A), spectra interleaved into the big frame.
-template <int FMT, int C, bool STRIDED>
+template <int FMT, int C, bool STRIDED, bool FRONT>
 __global__ void __launch_bounds__(FsGeom<C>::kThreads)
 k_fft_small(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict__ out, const cpx* __restrict__ tables,
-            int n_frames, int rows_per_frame) {
+            int n_frames, int rows_per_frame, int front, const float* __restrict__ win) {
     typedef FsGeom<C> G;
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ cpx red[8];
     cpx* Eall = reinterpret_cast<cpx*>(smem_raw);
     cpx* TP = Eall + G::kPerCta * G::kE;
     cpx* T2 = TP + G::kTP;
@@ -32,7 +72,18 @@ k_fft_small(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restri
     for (long long f0 = (long long)blockIdx.x * G::kPerCta; f0 < n_frames; f0 += (long long)gridDim.x * G::kPerCta) {
         const long long f = f0 + sub;
         const bool live = f < n_frames;
-        if (live) fs_phase1<FMT, C>(t, in + (size_t)f * G::N, TP, E);
+        if (FRONT) {
+            cpx v[16];
+            if (live) fs_phase1_load<FMT, C>(t, in + (size_t)f * G::N, v);
+            else {
+#pragma unroll
+                for (int a = 0; a < 16; a++) v[a] = mk(0.f, 0.f);
+            }
+            fs_front<16, G::T>(front, t, sub, v, win, red);
+            if (live) fs_phase1_finish<C>(t, v, TP, E);
+        } else if (live) {
+            fs_phase1<FMT, C>(t, in + (size_t)f * G::N, TP, E);
+        }
         __syncthreads();
         if (live) fs_phase2<C>(t, E);
         __syncthreads();
@@ -50,11 +101,12 @@ k_fft_small(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restri
 }
 
 // 8192 points: the 32 * 16 * 16 shape (fft_small.cuh: Fs8k), 256 threads x 32 points, every thread busy in every phase
-template <int FMT, bool STRIDED>
+template <int FMT, bool STRIDED, bool FRONT>
 __global__ void __launch_bounds__(256, 2)
 k_fft_8k(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict__ out, const cpx* __restrict__ tables,
-         int n_frames, int rows_per_frame) {
+         int n_frames, int rows_per_frame, int front, const float* __restrict__ win) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ cpx red[8];
     cpx* E = reinterpret_cast<cpx*>(smem_raw);
     cpx* TP = E + Fs8k::kE;
     cpx* T2 = TP + Fs8k::kTP;
@@ -62,7 +114,14 @@ k_fft_8k(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict_
     for (int i = t; i < Fs8k::kTables; i += 256) TP[i] = tables[i];
     __syncthreads();
     for (long long f = blockIdx.x; f < n_frames; f += gridDim.x) {
-        fs8k_phase1<FMT>(t, in + (size_t)f * Fs8k::N, TP, E);
+        if (FRONT) {
+            cpx v[32];
+            fs8k_phase1_load<FMT>(t, in + (size_t)f * Fs8k::N, v);
+            fs_front<32, 256>(front, t, 0, v, win, red);
+            fs8k_phase1_finish(t, v, TP, E);
+        } else {
+            fs8k_phase1<FMT>(t, in + (size_t)f * Fs8k::N, TP, E);
+        }
         __syncthreads();
         fs8k_phase2(t, E);
         __syncthreads();
@@ -79,14 +138,15 @@ k_fft_8k(const typename Ingest2<FMT>::raw_t* __restrict__ in, float* __restrict_
 constexpr int kSmem8k = (Fs8k::kE + Fs8k::kTables) * (int)sizeof(cpx);
 template <int FMT, bool STRIDED>
 static cudaError_t launch_8k(const void* iq, float* power, const cpx* tables, int n_frames, int rows_per_frame, int sm_count,
-                             cudaStream_t st) {
+                             cudaStream_t st, int front = 0, const float* win = nullptr) {
     static int per_sm = 0;
-    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fft_8k<FMT, STRIDED>, 256, kSmem8k) != cudaSuccess || per_sm < 1))
+    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fft_8k<FMT, STRIDED, false>, 256, kSmem8k) != cudaSuccess || per_sm < 1))
         per_sm = 1;
     const long long slots = (long long)per_sm * (sm_count > 0 ? sm_count : 148);
     const int grid = (int)(n_frames < slots ? n_frames : slots);
-    k_fft_8k<FMT, STRIDED><<<grid, 256, kSmem8k, st>>>(static_cast<const typename Ingest2<FMT>::raw_t*>(iq), power, tables, n_frames,
-                                                       rows_per_frame);
+    const typename Ingest2<FMT>::raw_t* src = static_cast<const typename Ingest2<FMT>::raw_t*>(iq);
+    if (front && !STRIDED) k_fft_8k<FMT, false, true><<<grid, 256, kSmem8k, st>>>(src, power, tables, n_frames, rows_per_frame, front, win);
+    else k_fft_8k<FMT, STRIDED, false><<<grid, 256, kSmem8k, st>>>(src, power, tables, n_frames, rows_per_frame, 0, nullptr);
     return cudaGetLastError();
 }
 
@@ -138,10 +198,13 @@ static constexpr int fs_smem() { return (FsGeom<C>::kPerCta * FsGeom<C>::kE + Fs
 template <int C>
 static cudaError_t fs_prepare_c() {
     cudaError_t e;
-    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CU8, C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CS16, C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CF32, C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
-    if (C == 16) return cudaFuncSetAttribute(k_fft_small<FMT_CF32, C, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>());
+    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CU8, C, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CS16, C, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CF32, C, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CU8, C, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CS16, C, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fft_small<FMT_CF32, C, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>())) != cudaSuccess) return e;
+    if (C == 16) return cudaFuncSetAttribute(k_fft_small<FMT_CF32, C, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fs_smem<C>());
     return cudaSuccess;
 }
 cudaError_t fft_small_prepare() {
@@ -151,10 +214,12 @@ cudaError_t fft_small_prepare() {
     if ((e = fs_prepare_c<4>()) != cudaSuccess) return e;
     if ((e = fs_prepare_c<8>()) != cudaSuccess) return e;
     if ((e = fs_prepare_c<16>()) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_fft_8k<FMT_CU8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem8k)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_fft_8k<FMT_CS16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem8k)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_fft_8k<FMT_CF32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem8k)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_fft_8k<FMT_CF32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem8k)) != cudaSuccess) return e;
+#define SDRB_8K_ATTR(F, S, R)                                                                                          \
+    if ((e = cudaFuncSetAttribute(k_fft_8k<F, S, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem8k)) != cudaSuccess) return e;
+    SDRB_8K_ATTR(FMT_CU8, false, false) SDRB_8K_ATTR(FMT_CS16, false, false) SDRB_8K_ATTR(FMT_CF32, false, false)
+    SDRB_8K_ATTR(FMT_CU8, false, true) SDRB_8K_ATTR(FMT_CS16, false, true) SDRB_8K_ATTR(FMT_CF32, false, true)
+    SDRB_8K_ATTR(FMT_CF32, true, false)
+#undef SDRB_8K_ATTR
     return cudaFuncSetAttribute(k_fft_rows4, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemRows4);
 }
 
@@ -162,42 +227,45 @@ bool fft_small_supports(int n) { return n >= 256 && n <= 8192 && (n & (n - 1)) =
 int fft_small_table_elems(int n) { return !fft_small_supports(n) ? 0 : (n == 8192 ? Fs8k::kTables : 80 * (n / 256)); }
 
 template <int FMT, int C>
-static cudaError_t fs_launch_fc(const void* iq, float* power, const cpx* tables, int n_frames, int sm_count, cudaStream_t st) {
+static cudaError_t fs_launch_fc(const void* iq, float* power, const cpx* tables, int n_frames, int sm_count, cudaStream_t st,
+                                int front, const float* win) {
     typedef FsGeom<C> G;
     static int per_sm = 0;
-    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fft_small<FMT, C, false>, G::kThreads, fs_smem<C>()) != cudaSuccess || per_sm < 1))
+    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fft_small<FMT, C, false, false>, G::kThreads, fs_smem<C>()) != cudaSuccess || per_sm < 1))
         per_sm = 1;
     const long long rounds = ((long long)n_frames + G::kPerCta - 1) / G::kPerCta;
     const long long slots = (long long)per_sm * (sm_count > 0 ? sm_count : 148);
     const int grid = (int)(rounds < slots ? rounds : slots);
-    k_fft_small<FMT, C, false><<<grid, G::kThreads, fs_smem<C>(), st>>>(static_cast<const typename Ingest2<FMT>::raw_t*>(iq), power,
-                                                                         tables, n_frames, 1);
+    const typename Ingest2<FMT>::raw_t* src = static_cast<const typename Ingest2<FMT>::raw_t*>(iq);
+    if (front) k_fft_small<FMT, C, false, true><<<grid, G::kThreads, fs_smem<C>(), st>>>(src, power, tables, n_frames, 1, front, win);
+    else k_fft_small<FMT, C, false, false><<<grid, G::kThreads, fs_smem<C>(), st>>>(src, power, tables, n_frames, 1, 0, nullptr);
     return cudaGetLastError();
 }
 template <int C>
 static cudaError_t fs_launch_c(int fmt, const void* iq, float* power, const cpx* tables, int n_frames, int sm_count,
-                               cudaStream_t st) {
+                               cudaStream_t st, int front, const float* win) {
     switch (fmt) {
-        case FMT_CU8: return fs_launch_fc<FMT_CU8, C>(iq, power, tables, n_frames, sm_count, st);
-        case FMT_CS16: return fs_launch_fc<FMT_CS16, C>(iq, power, tables, n_frames, sm_count, st);
-        case FMT_CF32: return fs_launch_fc<FMT_CF32, C>(iq, power, tables, n_frames, sm_count, st);
+        case FMT_CU8: return fs_launch_fc<FMT_CU8, C>(iq, power, tables, n_frames, sm_count, st, front, win);
+        case FMT_CS16: return fs_launch_fc<FMT_CS16, C>(iq, power, tables, n_frames, sm_count, st, front, win);
+        case FMT_CF32: return fs_launch_fc<FMT_CF32, C>(iq, power, tables, n_frames, sm_count, st, front, win);
         default: return cudaErrorInvalidValue;
     }
 }
 cudaError_t launch_fft_small(int fmt, const void* iq, float* power, const cpx* tables, int n, int n_frames, int sm_count,
-                             cudaStream_t st) {
+                             cudaStream_t st, int front, const float* win) {
     if (n_frames <= 0) return cudaSuccess;
+    if ((front & 1) && !win) return cudaErrorInvalidValue;
     switch (n) {
-        case 256: return fs_launch_c<1>(fmt, iq, power, tables, n_frames, sm_count, st);
-        case 512: return fs_launch_c<2>(fmt, iq, power, tables, n_frames, sm_count, st);
-        case 1024: return fs_launch_c<4>(fmt, iq, power, tables, n_frames, sm_count, st);
-        case 2048: return fs_launch_c<8>(fmt, iq, power, tables, n_frames, sm_count, st);
-        case 4096: return fs_launch_c<16>(fmt, iq, power, tables, n_frames, sm_count, st);
+        case 256: return fs_launch_c<1>(fmt, iq, power, tables, n_frames, sm_count, st, front, win);
+        case 512: return fs_launch_c<2>(fmt, iq, power, tables, n_frames, sm_count, st, front, win);
+        case 1024: return fs_launch_c<4>(fmt, iq, power, tables, n_frames, sm_count, st, front, win);
+        case 2048: return fs_launch_c<8>(fmt, iq, power, tables, n_frames, sm_count, st, front, win);
+        case 4096: return fs_launch_c<16>(fmt, iq, power, tables, n_frames, sm_count, st, front, win);
         case 8192:
             switch (fmt) {
-                case FMT_CU8: return launch_8k<FMT_CU8, false>(iq, power, tables, n_frames, 1, sm_count, st);
-                case FMT_CS16: return launch_8k<FMT_CS16, false>(iq, power, tables, n_frames, 1, sm_count, st);
-                case FMT_CF32: return launch_8k<FMT_CF32, false>(iq, power, tables, n_frames, 1, sm_count, st);
+                case FMT_CU8: return launch_8k<FMT_CU8, false>(iq, power, tables, n_frames, 1, sm_count, st, front, win);
+                case FMT_CS16: return launch_8k<FMT_CS16, false>(iq, power, tables, n_frames, 1, sm_count, st, front, win);
+                case FMT_CF32: return launch_8k<FMT_CF32, false>(iq, power, tables, n_frames, 1, sm_count, st, front, win);
                 default: return cudaErrorInvalidValue;
             }
         default: return cudaErrorInvalidValue;
@@ -228,11 +296,11 @@ template <int C>
 static cudaError_t tp_rows(const cpx* Y, float* power, const cpx* tables, int n_rows, int A, int sm_count, cudaStream_t st) {
     typedef FsGeom<C> G;
     static int per_sm = 0;
-    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fft_small<FMT_CF32, C, true>, G::kThreads, fs_smem<C>()) != cudaSuccess || per_sm < 1))
+    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fft_small<FMT_CF32, C, true, false>, G::kThreads, fs_smem<C>()) != cudaSuccess || per_sm < 1))
         per_sm = 1;
     const long long slots = (long long)per_sm * (sm_count > 0 ? sm_count : 148);
     const int grid = (int)(n_rows < slots ? n_rows : slots);
-    k_fft_small<FMT_CF32, C, true><<<grid, G::kThreads, fs_smem<C>(), st>>>(Y, power, tables, n_rows, A);
+    k_fft_small<FMT_CF32, C, true, false><<<grid, G::kThreads, fs_smem<C>(), st>>>(Y, power, tables, n_rows, A, 0, nullptr);
     return cudaGetLastError();
 }
 // Y: n_frames * n complex of scratch.  n_frames <= 65535 per call (the caller's chunks are far smaller).

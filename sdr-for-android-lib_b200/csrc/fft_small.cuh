@@ -39,12 +39,16 @@ struct FsGeom {
 };
 
 // ---- phase 1: load + convert, DFT16 over a, twiddle W_N^(t ka), store E[ka][t]
+// (in two halves so that a kernel can put the extension front end - block mean, window - between them)
 template <int FMT, int C>
-SDRB_HD void fs_phase1(int t, const typename Ingest2<FMT>::raw_t* in, const cpx* TP, cpx* E) {
+SDRB_HD void fs_phase1_load(int t, const typename Ingest2<FMT>::raw_t* in, cpx* v) {
     typedef FsGeom<C> G;
-    cpx v[16];
 #pragma unroll
     for (int a = 0; a < 16; a++) v[a] = Ingest2<FMT>::cvt(in[G::T * a + t]);
+}
+template <int C>
+SDRB_HD void fs_phase1_finish(int t, cpx* v, const cpx* TP, cpx* E) {
+    typedef FsGeom<C> G;
     fft_dit<4>(v);
     // W_N^(t ka) from W_N^(t 2^j): w[k] = w[k with lowest set bit cleared] * P[ctz k]
     cpx P[4];
@@ -59,6 +63,13 @@ SDRB_HD void fs_phase1(int t, const typename Ingest2<FMT>::raw_t* in, const cpx*
         w[k] = (k == low) ? P[j] : cmul(w[k - low], P[j]);
         E[k * G::kPitch + t] = cmul(v[dit_slot<4>(k)], w[k]);
     }
+}
+
+template <int FMT, int C>
+SDRB_HD void fs_phase1(int t, const typename Ingest2<FMT>::raw_t* in, const cpx* TP, cpx* E) {
+    cpx v[16];
+    fs_phase1_load<FMT, C>(t, in, v);
+    fs_phase1_finish<C>(t, v, TP, E);
 }
 
 // ---- phase 2: DFT16 over b for (ka, c), in place
@@ -139,10 +150,11 @@ struct Fs8k {
     static constexpr int kTables = kTP + kT2;
 };
 template <int FMT>
-SDRB_HD void fs8k_phase1(int t, const typename Ingest2<FMT>::raw_t* in, const cpx* TP, cpx* E) {
-    cpx v[32];
+SDRB_HD void fs8k_phase1_load(int t, const typename Ingest2<FMT>::raw_t* in, cpx* v) {
 #pragma unroll
     for (int a = 0; a < 32; a++) v[a] = Ingest2<FMT>::cvt(in[256 * a + t]);
+}
+SDRB_HD void fs8k_phase1_finish(int t, cpx* v, const cpx* TP, cpx* E) {
     fft_dit<5>(v);
     cpx P[5];
 #pragma unroll
@@ -156,6 +168,12 @@ SDRB_HD void fs8k_phase1(int t, const typename Ingest2<FMT>::raw_t* in, const cp
         w[k] = (k == low) ? P[j] : cmul(w[k - low], P[j]);
         E[k * Fs8k::kPitch + t] = cmul(v[dit_slot<5>(k)], w[k]);
     }
+}
+template <int FMT>
+SDRB_HD void fs8k_phase1(int t, const typename Ingest2<FMT>::raw_t* in, const cpx* TP, cpx* E) {
+    cpx v[32];
+    fs8k_phase1_load<FMT>(t, in, v);
+    fs8k_phase1_finish(t, v, TP, E);
 }
 SDRB_HD void fs8k_phase2(int t, cpx* E) {
 #pragma unroll

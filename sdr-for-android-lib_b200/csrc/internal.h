@@ -133,8 +133,9 @@ cudaError_t fft16k2_prepare(const cpx* host_tables);   // make_f2_tables() layou
 cudaError_t fft_small_prepare();
 bool fft_small_supports(int n);
 int fft_small_table_elems(int n);
+// front / win: the extension front end (bit 1: subtract the block mean, bit 0: window table of n floats), fused into phase 1
 cudaError_t launch_fft_small(int fmt, const void* iq, float* power, const cpx* tables, int n, int n_frames, int sm_count,
-                             cudaStream_t st);
+                             cudaStream_t st, int front = 0, const float* win = nullptr);
 // two-pass scheme for 32768 / 131072 / 262144 points: radix-A columns pass + the one-CTA kernel on the rows
 // (tables: make_tp_tables(n, B, log2 A) with B = 4096 (8192 for 262144); Y: n_frames * n complex of scratch)
 bool fft_twopass_supports(int n);

@@ -12,7 +12,8 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("fmt", [0, 1, 2])
-@pytest.mark.parametrize("n,fs", [(16384, 2_000_000), (4096, 2_000_000), (65536, 30_720_000)])
+@pytest.mark.parametrize("n,fs", [(16384, 2_000_000), (4096, 2_000_000), (65536, 30_720_000), (256, 250_000), (1024, 1_000_000),
+                                  (8192, 2_000_000), (32768, 2_500_000)])
 @pytest.mark.parametrize("window,remove_dc", [(1, 0), (0, 1), (1, 1)])
 def test_fft_front_end(sdrb, gpu_ctx, fmt, n, fs, window, remove_dc):
     S, B = 2, 3
