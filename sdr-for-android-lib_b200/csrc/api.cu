@@ -857,7 +857,7 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
                     }
                     CK(launch_estimator(power + (size_t)f0 * n, ctx->d_geo, ctx->geo, ctx->d_local + f0s + f0,
                                         ctx->d_est_scratch, f0s + f0, ctx->n_streams * ctx->max_blocks, nf, es));
-                    launches += ctx->geo.focusLen > 0 ? 2 : 1;
+                    launches += (ctx->geo.focusLen > 0 && !estimator_inline_scan(ctx->geo)) ? 2 : 1;
                     if (overlap) {
                         CK(launch_tracker(ctx->d_local + f0s + f0, ctx->d_geo, ctx->d_fft_state + s0 + f0 / n_blocks,
                                           ctx->d_results + f0s + f0, nf / n_blocks, n_blocks, es));
@@ -944,7 +944,7 @@ static int run_streams(sdrb_ctx* ctx, const void* d_iq, int s0, int ns, int n_bl
         if (!estimator_done) {
             CK(launch_estimator(power, ctx->d_geo, ctx->geo, ctx->d_local + f0s, ctx->d_est_scratch, f0s,
                                 ctx->n_streams * ctx->max_blocks, frames, st));
-            launches += ctx->geo.focusLen > 0 ? 2 : 1;
+            launches += (ctx->geo.focusLen > 0 && !estimator_inline_scan(ctx->geo)) ? 2 : 1;
         }
         if (!estimator_done) trace_mark("band scan + estimator", st);
         if (!tracker_done) {

@@ -45,6 +45,36 @@ struct BandStat {
     int bestStart;   // offset of the first window that reaches bestRun
 };
 
+// One band in order: sum + arg-max (:146-155 focus, :198-202 windows) and the best run of W bins (:163-180 / :310-318:
+// run-sum with +new -old updates, strict >).  Shared by k_band_scan and by the estimator's inline scan of short bands.
+__device__ __forceinline__ BandStat scan_band(const float* __restrict__ p, int len, int W, bool focus) {
+    float sum = 0.0f, maxP = focus ? -1.0f : 0.0f;
+    int maxIdx = 0;
+#pragma unroll 32
+    for (int i = 0; i < len; i++) {   // 32 loads in flight: the scan is bound by memory latency, not by the adds
+        const float v = p[i];
+        sum = __fadd_rn(sum, v);
+        if (v > maxP) { maxP = v; maxIdx = i; }
+    }
+    BandStat r;
+    r.sum = sum; r.maxP = maxP; r.maxIdx = maxIdx;
+    if (len < W) {
+        r.bestRun = sum; r.bestStart = 0;
+    } else {
+        float run = 0.0f;
+        for (int i = 0; i < W; i++) run = __fadd_rn(run, p[i]);
+        float best = run;
+        int bestStart = 0;
+#pragma unroll 16
+        for (int s = 1; s + W - 1 < len; s++) {
+            run = __fadd_rn(run, __fsub_rn(p[s + W - 1], p[s - 1]));
+            if (run > best) { best = run; bestStart = s; }
+        }
+        r.bestRun = best; r.bestStart = bestStart;
+    }
+    return r;
+}
+
 // ---------------------------------------------------------------- k_band_scan
 // Mirrors :146-155 (sum + arg-max), :198-202 (sum + max) and best1kHzMean :163-180 / :310-318
 // (run-sum with +new -old updates, strict >).
@@ -92,31 +122,7 @@ k_band_scan(const float* __restrict__ power, const EstGeometry* __restrict__ geo
     const int len = g.segOff[seg + 1] - g.segOff[seg];
     const int W = g.winBins1k;
     const float* __restrict__ p = STAGED ? band_smem + (size_t)id * pitch : power + (size_t)frame * g.n + lo;
-    float sum = 0.0f, maxP = seg == 0 ? -1.0f : 0.0f;
-    int maxIdx = 0;
-#pragma unroll 32
-    for (int i = 0; i < len; i++) {   // 32 loads in flight: the scan is bound by memory latency, not by the adds
-        const float v = p[i];
-        sum = __fadd_rn(sum, v);
-        if (v > maxP) { maxP = v; maxIdx = i; }
-    }
-    BandStat r;
-    r.sum = sum; r.maxP = maxP; r.maxIdx = maxIdx;
-    if (len < W) {
-        r.bestRun = sum; r.bestStart = 0;
-    } else {
-        float run = 0.0f;
-        for (int i = 0; i < W; i++) run = __fadd_rn(run, p[i]);
-        float best = run;
-        int bestStart = 0;
-#pragma unroll 16
-        for (int s = 1; s + W - 1 < len; s++) {
-            run = __fadd_rn(run, __fsub_rn(p[s + W - 1], p[s - 1]));
-            if (run > best) { best = run; bestStart = s; }
-        }
-        r.bestRun = best; r.bestStart = bestStart;
-    }
-    stats[(size_t)frame * EST_MAX_BANDS + seg] = r;
+    stats[(size_t)frame * EST_MAX_BANDS + seg] = scan_band(p, len, W, seg == 0);
 }
 
 // ---------------------------------------------------------------- k_estimator
@@ -132,7 +138,9 @@ __device__ __forceinline__ float mad4(const float* x, int nb, float mean) {
 }
 
 // U: unroll factor of the pooled-bin loops (8 when many bins are pooled per frame, 1 otherwise; see the launcher)
-template <bool USE_SMEM, int U>
+// INLINE: the bands are short (<= 32 bins): lanes 0 .. nWin scan their own band here, no k_band_scan launch, no round
+// trip of the band statistics (short frames: the band scan was a fifth of the whole FFT stage at 1024 points)
+template <bool USE_SMEM, int U, bool INLINE>
 __global__ void __launch_bounds__(EST_WARPS * 32)
 k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo_p, const BandStat* __restrict__ stats,
             FrameLocal* __restrict__ local, float* __restrict__ gscratch, int pooled_cap, int n_frames) {
@@ -162,8 +170,11 @@ k_estimator(const float* __restrict__ power, const EstGeometry* __restrict__ geo
     const bool valid = nWin >= 2;  // :218
     const bool isWin = lane >= 1 && lane <= nWin;
     BandStat bs = {};
-    if (lane <= nWin) bs = stats[(size_t)frame * EST_MAX_BANDS + lane];
     const int len = lane <= nWin ? g.segOff[lane + 1] - g.segOff[lane] : 1;
+    if (lane <= nWin) {
+        if (INLINE) bs = scan_band(power + (size_t)frame * g.n + (lane == 0 ? g.focusLo : g.winLo[lane - 1]), len, W, lane == 0);
+        else bs = stats[(size_t)frame * EST_MAX_BANDS + lane];
+    }
     // dB figures of the bands, one lane per band (:149-155, :203-213)
     float dbA = 0.0f, dbB = 0.0f;   // focus: (absPeakDb candidate, signalPowerDb); window: (meanDb, best1kDb)
     const float focusSum = __shfl_sync(FULL, bs.sum, 0), focusBestRun = __shfl_sync(FULL, bs.bestRun, 0);
@@ -448,10 +459,13 @@ static int pooled_cap_of(const EstGeometry& g) {
 cudaError_t estimator_prepare() {
     cudaError_t e = cudaFuncSetAttribute(k_band_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     if (e != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_estimator<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    if ((e = cudaFuncSetAttribute(k_estimator<true, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   EST_WARPS * EST_SMEM_POOL_FLOATS * (int)sizeof(float))) != cudaSuccess)
         return e;
-    return cudaFuncSetAttribute(k_estimator<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    if ((e = cudaFuncSetAttribute(k_estimator<true, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  EST_WARPS * EST_SMEM_POOL_FLOATS * (int)sizeof(float))) != cudaSuccess)
+        return e;
+    return cudaFuncSetAttribute(k_estimator<true, 8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 EST_WARPS * EST_SMEM_POOL_FLOATS * (int)sizeof(float));
 }
 
@@ -463,6 +477,15 @@ size_t estimator_scratch_floats(const EstGeometry& g, int n_frames) {
     return band_floats(n_frames) + (cap > EST_SMEM_POOL_FLOATS ? (size_t)cap * (size_t)n_frames : 0);
 }
 
+// Bands of at most 32 bins (short frames, narrow focus) are scanned inside the estimator kernel: one launch, not two.
+bool estimator_inline_scan(const EstGeometry& g) {
+    static const bool off = getenv("SDRB_EST_INLINE") && getenv("SDRB_EST_INLINE")[0] == '0';   // test hook
+    if (g.focusLen <= 0 || off) return false;
+    int maxLen = 0;
+    for (int i = 0; i <= g.nWin; i++) maxLen = std::max(maxLen, g.segOff[i + 1] - g.segOff[i]);
+    return maxLen <= 32 && pooled_cap_of(g) <= EST_SMEM_POOL_FLOATS;
+}
+
 // scratch = base of the context's scratch (sized for cap_frames); frame0 = index of this call's
 // first frame inside the context (power / d_local are already offset by the caller).
 cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, const EstGeometry& h_geo,
@@ -472,7 +495,8 @@ cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, const
     if (!scratch) return cudaErrorInvalidValue;
     BandStat* stats = reinterpret_cast<BandStat*>(scratch) + frame0 * EST_MAX_BANDS;
     const int nSeg = h_geo.nWin + 1;
-    if (h_geo.focusLen > 0) {
+    const bool inline_scan = estimator_inline_scan(h_geo);
+    if (h_geo.focusLen > 0 && !inline_scan) {
         // frames per CTA: one thread per band (<= 128 threads); staged when one frame's slots fit 96 KiB of
         // shared memory (measured on B200, 37888 frames of the bench geometry: 143 us walking global memory)
         int fpc = 128 / nSeg;
@@ -499,11 +523,12 @@ cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, const
     const bool deep = cap >= 1024;
     if (cap <= EST_SMEM_POOL_FLOATS) {
         const size_t sm = (size_t)EST_WARPS * cap * sizeof(float);
-        if (deep) k_estimator<true, 8><<<grid, EST_WARPS * 32, sm, st>>>(power, d_geo, stats, d_local, nullptr, cap, n_frames);
-        else k_estimator<true, 1><<<grid, EST_WARPS * 32, sm, st>>>(power, d_geo, stats, d_local, nullptr, cap, n_frames);
+        if (inline_scan) k_estimator<true, 1, true><<<grid, EST_WARPS * 32, sm, st>>>(power, d_geo, stats, d_local, nullptr, cap, n_frames);
+        else if (deep) k_estimator<true, 8, false><<<grid, EST_WARPS * 32, sm, st>>>(power, d_geo, stats, d_local, nullptr, cap, n_frames);
+        else k_estimator<true, 1, false><<<grid, EST_WARPS * 32, sm, st>>>(power, d_geo, stats, d_local, nullptr, cap, n_frames);
     } else {
         float* gs = scratch + band_floats(cap_frames) + frame0 * (size_t)cap;
-        k_estimator<false, 8><<<grid, EST_WARPS * 32, 0, st>>>(power, d_geo, stats, d_local, gs, cap, n_frames);
+        k_estimator<false, 8, false><<<grid, EST_WARPS * 32, 0, st>>>(power, d_geo, stats, d_local, gs, cap, n_frames);
     }
     return cudaGetLastError();
 }

@@ -165,6 +165,7 @@ int fft_big_ring_slots(int n);
 cudaError_t launch_fft_big_fused(int fmt, const void* iq, float* power, cpx* ring, int slots, unsigned* ctl,
                                  const cpx* tables, int n, int n_frames, cudaStream_t st);
 // estimator.cu
+bool estimator_inline_scan(const EstGeometry& g);   // true: launch_estimator is ONE kernel (short bands scanned inline)
 cudaError_t launch_estimator(const float* power, const EstGeometry* d_geo, const EstGeometry& h_geo,
                              FrameLocal* d_local, float* scratch, size_t frame0, int cap_frames, int n_frames,
                              cudaStream_t st);
